@@ -1,0 +1,283 @@
+"""CPU oracle for the Zero-DCE / Zero-DCE++ / SCI inference forward.
+
+TEST INFRASTRUCTURE ONLY.  Nothing in the product path
+(`etss_07_imageenhance_b200/`) may import this module; only `tests/`,
+`__graft_entry__.smoke()` and `bench.py`'s `cpu_baseline` / `--impl reference`
+legs use it, and only as the checker / the timed CPU baseline.
+
+This is a plain-torch (ATen on CPU, fp32) restatement of the reference's own
+arithmetic.  Citations are relative to /root/reference/:
+
+* `zero_dce_forward`   follows src/mon/vision/enhance/llie/zero_dce/zero_dce.py:173-191
+  (layers :133-139) == upstream src/mon_extra/vision/enhance/llie/zero_dce/model.py:27-50
+* `zero_dcepp_forward` follows src/mon/vision/enhance/llie/zero_dce/zero_dcepp.py:182-208
+  (layers :140-146, DSConv2d = src/mon/nn/modules/conv/dsconv.py:106-149); for
+  scale_factor != 1 the reference class raises (zero_dcepp.py:139 passes the
+  factor as `size`), so the *intended* semantics are taken from upstream
+  src/mon_extra/vision/enhance/llie/zero_dce++/model.py:39,64-82.
+* `sci_forward`        follows src/mon_extra/vision/enhance/llie/sci/model.py:36-45,155-159
+  (BatchNorm2d in eval mode).
+
+Parity pin: the reference holds no tests / golden vectors for this path
+("parity unpinned" by the reference's own tests).  The pin we
+create is `oracle/pin_against_reference.py`: it executes the reference's own
+source files (the `mon` classes under a stub `mon` package, and the upstream
+`mon_extra` model files unmodified) in the build container, asserts bit
+equality with this restatement on CPU, and writes tests/golden/*.npz.
+
+`bilinear_down_ref` / `bilinear_up_ref` are independent explicit-index numpy
+restatements of ATen's `upsample_bilinear2d` index math
+(area_pixel_compute_source_index, fp32) used to pin the kernels' index logic.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+# --------------------------------------------------------------------------- #
+# state_dict layouts
+# --------------------------------------------------------------------------- #
+DCE_CHANNELS = [(3, 32), (32, 32), (32, 32), (32, 32), (64, 32), (64, 32), (64, 24)]
+DCEPP_CHANNELS = [(3, 32), (32, 32), (32, 32), (32, 32), (64, 32), (64, 32), (64, 3)]
+
+
+def make_dce_state_dict(seed: int, regime: str = "init", num_channels: int = 32, num_iters: int = 8,
+                        in_channels: int = 3) -> dict:
+    """Seeded Zero-DCE weights.  regime="init": the reference's random init
+    (conv weights N(0,0.02), zero_dce.py:152-158; biases torch-default-like
+    U(-1/sqrt(fan_in), 1/sqrt(fan_in))).  regime="stress": weights scaled so the
+    curve maps span roughly (-0.9, 0.9) and indexing/sign bugs are visible."""
+    g = torch.Generator().manual_seed(seed)
+    nc = num_channels
+    chans = [(in_channels, nc), (nc, nc), (nc, nc), (nc, nc), (2 * nc, nc), (2 * nc, nc),
+             (2 * nc, in_channels * num_iters)]
+    sd = {}
+    for i, (ci, co) in enumerate(chans, 1):
+        fan_in = ci * 9
+        if regime == "init":
+            w = torch.randn(co, ci, 3, 3, generator=g) * 0.02
+        else:
+            w = torch.randn(co, ci, 3, 3, generator=g) * (1.6 / fan_in ** 0.5)
+        bound = 1.0 / fan_in ** 0.5
+        b = (torch.rand(co, generator=g) * 2 - 1) * bound
+        sd[f"e_conv{i}.weight"] = w
+        sd[f"e_conv{i}.bias"] = b
+    return sd
+
+
+def make_dcepp_state_dict(seed: int, regime: str = "init", num_channels: int = 32,
+                          in_channels: int = 3) -> dict:
+    """Seeded Zero-DCE++ weights in the `mon` key layout
+    (e_conv{i}.dw_conv/pw_conv.{weight,bias}, dsconv.py:122-149)."""
+    g = torch.Generator().manual_seed(seed)
+    nc = num_channels
+    chans = [(in_channels, nc), (nc, nc), (nc, nc), (nc, nc), (2 * nc, nc), (2 * nc, nc),
+             (2 * nc, in_channels)]
+    sd = {}
+    for i, (ci, co) in enumerate(chans, 1):
+        if regime == "init":
+            dw = torch.randn(ci, 1, 3, 3, generator=g) * 0.02
+            pw = torch.randn(co, ci, 1, 1, generator=g) * 0.02
+        else:
+            dw = torch.randn(ci, 1, 3, 3, generator=g) * (1.4 / 3.0)
+            pw = torch.randn(co, ci, 1, 1, generator=g) * (1.4 / ci ** 0.5)
+        dwb = (torch.rand(ci, generator=g) * 2 - 1) / 3.0
+        pwb = (torch.rand(co, generator=g) * 2 - 1) / ci ** 0.5
+        sd[f"e_conv{i}.dw_conv.weight"] = dw
+        sd[f"e_conv{i}.dw_conv.bias"] = dwb
+        sd[f"e_conv{i}.pw_conv.weight"] = pw
+        sd[f"e_conv{i}.pw_conv.bias"] = pwb
+    return sd
+
+
+def make_sci_state_dict(seed: int, regime: str = "init") -> dict:
+    """Seeded SCI EnhanceNetwork(layers=1, channels=3) weights, keys as in
+    sci/model.py:16-34 (without the `enhance.` prefix of Finetunemodel)."""
+    g = torch.Generator().manual_seed(seed)
+    s = 0.02 if regime == "init" else 0.35
+    sd = {}
+    for name in ("in_conv.0", "conv.0", "out_conv.0"):
+        sd[f"{name}.weight"] = torch.randn(3, 3, 3, 3, generator=g) * s
+        sd[f"{name}.bias"] = (torch.rand(3, generator=g) * 2 - 1) * (0.0 if regime == "init" else 0.2)
+    if regime == "init":
+        sd["conv.1.weight"] = 1.0 + torch.randn(3, generator=g) * 0.02
+        sd["conv.1.bias"] = torch.zeros(3)
+        sd["conv.1.running_mean"] = torch.zeros(3)
+        sd["conv.1.running_var"] = torch.ones(3)
+    else:
+        sd["conv.1.weight"] = 1.0 + torch.randn(3, generator=g) * 0.3
+        sd["conv.1.bias"] = torch.randn(3, generator=g) * 0.2
+        sd["conv.1.running_mean"] = torch.randn(3, generator=g) * 0.1
+        sd["conv.1.running_var"] = 0.5 + torch.rand(3, generator=g)
+    sd["conv.1.num_batches_tracked"] = torch.tensor(0, dtype=torch.long)
+    return sd
+
+
+def synthetic_lowlight(B: int, H: int, W: int, seed: int, device="cpu") -> torch.Tensor:
+    """Seeded synthetic low-light frame batch: dark gamma'd
+    noise blended with a smooth gradient field; a few pixels forced to exactly
+    0 and 1.  NCHW fp32 in [0,1]."""
+    g = torch.Generator().manual_seed(seed)
+    u = torch.rand(B, 3, H, W, generator=g)
+    noise = 0.02 + 0.33 * u.pow(2.2)
+    field = torch.rand(B, 3, 9, 16, generator=g)
+    smooth = 0.45 * F.interpolate(field, size=(H, W), mode="bilinear", align_corners=True)
+    x = (0.5 * noise + 0.5 * smooth).clamp_(0, 1)
+    x[:, :, 0, 0] = 0.0
+    x[:, :, -1, -1] = 1.0
+    if H > 2 and W > 2:
+        x[:, 1, H // 2, W // 2] = 1.0
+        x[:, 2, H // 2, W // 2 - 1] = 0.0
+    return x.to(device)
+
+
+# --------------------------------------------------------------------------- #
+# forwards
+# --------------------------------------------------------------------------- #
+def curve_shared(x: torch.Tensor, a: torch.Tensor, num_iters: int = 8) -> torch.Tensor:
+    """zero_dcepp.py:201-203 — y = y + a*(y**2 - y), same map every iteration."""
+    y = x
+    for _ in range(num_iters):
+        y = y + a * (torch.pow(y, 2) - y)
+    return y
+
+
+def curve_per_iter(x: torch.Tensor, a: torch.Tensor, num_iters: int = 8) -> torch.Tensor:
+    """zero_dce.py:183-188 — one C-channel map per iteration (split along dim 1)."""
+    c = x.shape[1]
+    a_s = torch.split(a, c, dim=1)
+    y = x
+    for i in range(num_iters):
+        y = y + a_s[i] * (torch.pow(y, 2) - y)
+    return y
+
+
+@torch.no_grad()
+def zero_dce_forward(x: torch.Tensor, sd: dict, num_iters: int = 8) -> dict:
+    """ZeroDCE_RE.forward (zero_dce.py:173-191).  Returns the reference's dict
+    (adjust_0.., adjust, enhanced — in that insertion order)."""
+    def conv(t, i):
+        return F.conv2d(t, sd[f"e_conv{i}.weight"], sd[f"e_conv{i}.bias"], stride=1, padding=1)
+    x1 = F.relu(conv(x, 1))
+    x2 = F.relu(conv(x1, 2))
+    x3 = F.relu(conv(x2, 3))
+    x4 = F.relu(conv(x3, 4))
+    x5 = F.relu(conv(torch.cat([x3, x4], 1), 5))
+    x6 = F.relu(conv(torch.cat([x2, x5], 1), 6))
+    x_r = torch.tanh(conv(torch.cat([x1, x6], 1), 7))
+    x_rs = torch.split(x_r, x.shape[1], dim=1)
+    y = x
+    out = {}
+    for i in range(num_iters):
+        y = y + x_rs[i] * (torch.pow(y, 2) - y)
+        out[f"adjust_{i}"] = x_rs[i]
+    out["adjust"] = x_r
+    out["enhanced"] = y
+    return out
+
+
+@torch.no_grad()
+def zero_dcepp_lowres_net(x_down: torch.Tensor, sd: dict) -> torch.Tensor:
+    """The 7 depthwise-separable layers + tanh (zero_dcepp.py:190-196)."""
+    def ds(t, i):
+        c = t.shape[1]
+        t = F.conv2d(t, sd[f"e_conv{i}.dw_conv.weight"], sd[f"e_conv{i}.dw_conv.bias"], stride=1, padding=1, groups=c)
+        return F.conv2d(t, sd[f"e_conv{i}.pw_conv.weight"], sd[f"e_conv{i}.pw_conv.bias"])
+    x1 = F.relu(ds(x_down, 1))
+    x2 = F.relu(ds(x1, 2))
+    x3 = F.relu(ds(x2, 3))
+    x4 = F.relu(ds(x3, 4))
+    x5 = F.relu(ds(torch.cat([x3, x4], 1), 5))
+    x6 = F.relu(ds(torch.cat([x2, x5], 1), 6))
+    return torch.tanh(ds(torch.cat([x1, x6], 1), 7))
+
+
+@torch.no_grad()
+def zero_dcepp_forward(x: torch.Tensor, sd: dict, scale_factor: float = 1.0, num_iters: int = 8) -> dict:
+    """ZeroDCEpp_RE.forward (zero_dcepp.py:182-208) with upstream's working
+    upsample for scale_factor != 1 (zero_dce++/model.py:39,68,80)."""
+    x_down = x
+    if scale_factor != 1:
+        x_down = F.interpolate(x, scale_factor=1 / scale_factor, mode="bilinear")
+    x_r = zero_dcepp_lowres_net(x_down, sd)
+    if scale_factor != 1:
+        x_r = torch.nn.UpsamplingBilinear2d(scale_factor=scale_factor)(x_r)
+    y = curve_shared(x, x_r, num_iters)
+    return {"adjust": x_r, "enhanced": y}
+
+
+@torch.no_grad()
+def sci_forward(x: torch.Tensor, sd: dict, eps: float = 1e-5) -> tuple:
+    """Finetunemodel.forward (sci/model.py:155-159) over EnhanceNetwork.forward
+    (:36-45), BatchNorm2d in eval mode.  Returns (illu, r)."""
+    fea = F.relu(F.conv2d(x, sd["in_conv.0.weight"], sd["in_conv.0.bias"], padding=1))
+    t = F.conv2d(fea, sd["conv.0.weight"], sd["conv.0.bias"], padding=1)
+    t = F.batch_norm(t, sd["conv.1.running_mean"], sd["conv.1.running_var"], sd["conv.1.weight"], sd["conv.1.bias"],
+                     training=False, eps=eps)
+    fea = fea + F.relu(t)
+    fea = torch.sigmoid(F.conv2d(fea, sd["out_conv.0.weight"], sd["out_conv.0.bias"], padding=1))
+    illu = torch.clamp(fea + x, 0.0001, 1)
+    r = torch.clamp(x / illu, 0, 1)
+    return illu, r
+
+
+# --------------------------------------------------------------------------- #
+# independent explicit-index restatements of ATen's bilinear resize (numpy)
+# --------------------------------------------------------------------------- #
+def bilinear_down_ref(x: np.ndarray, sf: int) -> np.ndarray:
+    """F.interpolate(x, scale_factor=1/sf, mode='bilinear') for integer sf:
+    align_corners=False, scale used directly: src = sf*(dst+0.5)-0.5, clamped
+    at 0 (ATen area_pixel_compute_source_index).  x: [B,C,H,W] float32."""
+    B, C, H, W = x.shape
+    h, w = int(np.floor(H * (1.0 / sf))), int(np.floor(W * (1.0 / sf)))
+    scale = np.float32(1.0 / (1.0 / sf))  # ATen: 1/scale_factor when given
+    out = np.empty((B, C, h, w), np.float32)
+
+    def idx(d, size):
+        src = np.float32(scale) * (np.float32(d) + np.float32(0.5)) - np.float32(0.5)
+        src = max(np.float32(0), src)
+        i0 = int(src)
+        i1 = i0 + (1 if i0 < size - 1 else 0)
+        l1 = np.float32(src - np.float32(i0))
+        return i0, i1, np.float32(1) - l1, l1
+
+    for yy in range(h):
+        y0, y1, wy0, wy1 = idx(yy, H)
+        for xx in range(w):
+            x0, x1, wx0, wx1 = idx(xx, W)
+            out[:, :, yy, xx] = wy0 * (wx0 * x[:, :, y0, x0] + wx1 * x[:, :, y0, x1]) + \
+                wy1 * (wx0 * x[:, :, y1, x0] + wx1 * x[:, :, y1, x1])
+    return out
+
+
+def bilinear_up_ref(a: np.ndarray, H: int, W: int) -> np.ndarray:
+    """nn.UpsamplingBilinear2d(scale_factor=sf) == interpolate(size=(H,W),
+    align_corners=True): src = dst*(in-1)/(out-1) in fp32."""
+    B, C, h, w = a.shape
+    out = np.empty((B, C, H, W), np.float32)
+    sh = np.float32(h - 1) / np.float32(H - 1) if H > 1 else np.float32(0)
+    sw = np.float32(w - 1) / np.float32(W - 1) if W > 1 else np.float32(0)
+
+    def idx(d, scale, size):
+        src = np.float32(scale * np.float32(d))
+        i0 = int(src)
+        i1 = i0 + (1 if i0 < size - 1 else 0)
+        l1 = np.float32(src - np.float32(i0))
+        return i0, i1, np.float32(1) - l1, l1
+
+    xs = [idx(X, sw, w) for X in range(W)]
+    for Y in range(H):
+        y0, y1, wy0, wy1 = idx(Y, sh, h)
+        for X in range(W):
+            x0, x1, wx0, wx1 = xs[X]
+            out[:, :, Y, X] = wy0 * (wx0 * a[:, :, y0, x0] + wx1 * a[:, :, y0, x1]) + \
+                wy1 * (wx0 * a[:, :, y1, x0] + wx1 * a[:, :, y1, x1])
+    return out
+
+
+def psnr(a: torch.Tensor, b: torch.Tensor) -> float:
+    mse = torch.mean((a.double() - b.double()) ** 2).item()
+    if mse == 0:
+        return float("inf")
+    return 10.0 * np.log10(1.0 / mse)

@@ -1,0 +1,293 @@
+#!/usr/bin/env python
+"""Pin the oracle against the reference's OWN code and write tests/golden/*.npz.
+
+TEST INFRASTRUCTURE.  Runs only in the build container (needs /root/reference).
+
+What is executed from the reference, unmodified, read from where it lies:
+  * src/mon/vision/enhance/llie/zero_dce/zero_dce.py     (class ZeroDCE_RE)
+  * src/mon/vision/enhance/llie/zero_dce/zero_dcepp.py   (class ZeroDCEpp_RE)
+  * src/mon/nn/modules/conv/dsconv.py                    (DSConv2d -> state_dict keys)
+  * src/mon_extra/vision/enhance/llie/zero_dce/model.py      (upstream Zero-DCE)
+  * src/mon_extra/vision/enhance/llie/zero_dce++/model.py    (upstream Zero-DCE++, sf != 1)
+  * src/mon_extra/vision/enhance/llie/sci/model.py           (upstream SCI EnhanceNetwork)
+`import mon` itself is impossible here (plum/humps/lightning/fvcore/... are not
+installed, no network), so the three `mon` files are exec'd under a STUB `mon`
+package that provides only the base-class plumbing they subclass
+(Model ctor: src/mon/nn/model.py:237-277; assert_datapoint:
+src/mon/vision/enhance/base.py:32-47).  The arithmetic (`forward`) and the
+parameter names are the reference's own code.
+
+Assertions (all on CPU, fp32): oracle == reference bit-for-bit.
+Outputs: tests/golden/{dce,dcepp_sf1,dcepp_sf2,dcepp_sf12,sci}_{init,stress}.npz
+holding input, weights and the REFERENCE outputs.
+"""
+from __future__ import annotations
+
+import importlib.util
+import os
+import sys
+import types
+from enum import Enum
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+from oracle import oracle as O  # noqa: E402
+
+REF = Path(os.environ.get("B200DCE_REFERENCE", "/root/reference"))
+GOLD = ROOT / "tests" / "golden"
+
+
+def _load_file(name: str, path: Path):
+    spec = importlib.util.spec_from_file_location(name, str(path))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def install_stub_mon():
+    """A minimal `mon` so the reference model files import.  Only plumbing."""
+    mon = types.ModuleType("mon")
+    core = types.ModuleType("mon.core")
+    nn = types.ModuleType("mon.nn")
+    glob = types.ModuleType("mon.globals")
+    vision = types.ModuleType("mon.vision")
+    enhance = types.ModuleType("mon.vision.enhance")
+    base = types.ModuleType("mon.vision.enhance.base")
+    nn_modules = types.ModuleType("mon.nn.modules")
+    activation = types.ModuleType("mon.nn.modules.activation")
+
+    class _Console:
+        def log(self, *a, **k):
+            pass
+    core.console = _Console()
+    core.Path = Path
+
+    for k in dir(torch.nn):
+        if not k.startswith("_"):
+            setattr(nn, k, getattr(torch.nn, k))
+
+    class Loss(torch.nn.Module):  # stands in for mon.nn.Loss (nn/loss/base.py:82)
+        def __init__(self, *a, **k):
+            super().__init__()
+    nn.Loss = Loss
+
+    class _SpaLoss(torch.nn.Module):
+        """Only the 4 fixed parameters SpatialConsistencyLoss registers
+        (src/mon/nn/loss/image.py:925-945,1082-1085)."""
+        def __init__(self, *a, **k):
+            super().__init__()
+            def p(rows):
+                return torch.nn.Parameter(torch.tensor(rows, dtype=torch.float32)[None, None], requires_grad=False)
+            self.weight_left = p([[0, 0, 0], [-1, 1, 0], [0, 0, 0]])
+            self.weight_right = p([[0, 0, 0], [0, 1, -1], [0, 0, 0]])
+            self.weight_up = p([[0, -1, 0], [0, 1, 0], [0, 0, 0]])
+            self.weight_down = p([[0, 0, 0], [0, 1, 0], [0, -1, 0]])
+
+    class _NoLoss(torch.nn.Module):
+        def __init__(self, *a, **k):
+            super().__init__()
+    nn.SpatialConsistencyLoss = _SpaLoss
+    nn.ExposureControlLoss = _NoLoss
+    nn.ColorConstancyLoss = _NoLoss
+    nn.TotalVariationLoss = _NoLoss
+
+    class Task(Enum):
+        LLIE = "llie"
+
+    class Scheme(Enum):
+        UNSUPERVISED = "unsupervised"
+        ZERO_REFERENCE = "zero_reference"
+        SUPERVISED = "supervised"
+
+    class _Models(dict):
+        def register(self, name=None, arch=None, replace=False):
+            def deco(cls):
+                self.setdefault(arch, {})[name] = cls
+                return cls
+            return deco
+    glob.MODELS, glob.Task, glob.Scheme = _Models(), Task, Scheme
+
+    class ImageEnhancementModel(torch.nn.Module):
+        """Model ctor contract of src/mon/nn/model.py:237-277 (subset)."""
+        schemes: list = []
+        zoo: dict = {}
+
+        def __init__(self, name=None, in_channels=3, out_channels=None, num_classes=None, weights=None, **kw):
+            super().__init__()
+            self.name = name
+            self.in_channels = in_channels
+            self.out_channels = out_channels or num_classes or self.in_channels
+            self.weights = weights
+            self.predicting = True
+
+        def assert_datapoint(self, datapoint):
+            if "image" not in datapoint:
+                raise ValueError("The key ``'image'`` must be defined in the `datapoint`.")
+
+        def assert_outputs(self, outputs):
+            if "enhanced" not in outputs:
+                raise ValueError("The key ``'enhanced'`` must be defined in the `outputs`.")
+
+        def load_weights(self):
+            raise NotImplementedError
+    base.ImageEnhancementModel = ImageEnhancementModel
+
+    mon.core, mon.nn, mon.globals, mon.vision = core, nn, glob, vision
+    vision.enhance, enhance.base, nn.modules, nn_modules.activation = enhance, base, nn_modules, activation
+    for n, m in [("mon", mon), ("mon.core", core), ("mon.nn", nn), ("mon.globals", glob), ("mon.vision", vision),
+                 ("mon.vision.enhance", enhance), ("mon.vision.enhance.base", base), ("mon.nn.modules", nn_modules),
+                 ("mon.nn.modules.activation", activation)]:
+        sys.modules[n] = m
+    ds = _load_file("mon.nn.modules.conv.dsconv", REF / "src/mon/nn/modules/conv/dsconv.py")
+    nn.DSConv2d = ds.DSConv2d
+    zd = _load_file("ref_zero_dce", REF / "src/mon/vision/enhance/llie/zero_dce/zero_dce.py")
+    zp = _load_file("ref_zero_dcepp", REF / "src/mon/vision/enhance/llie/zero_dce/zero_dcepp.py")
+    return zd.ZeroDCE_RE, zp.ZeroDCEpp_RE, glob.MODELS
+
+
+def load_upstream():
+    up = REF / "src/mon_extra/vision/enhance/llie"
+    dce = _load_file("up_zero_dce_model", up / "zero_dce/model.py")
+    dcepp = _load_file("up_zero_dcepp_model", up / "zero_dce++/model.py")
+    sys.path.insert(0, str(up / "sci"))  # sci/model.py does `from loss import LossFunction`
+    sci = _load_file("up_sci_model", up / "sci/model.py")
+    return dce, dcepp, sci
+
+
+def to_upstream_keys(sd: dict) -> dict:
+    return {k.replace("dw_conv", "depth_conv").replace("pw_conv", "point_conv"): v for k, v in sd.items()}
+
+
+def eq(a, b, what):
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    assert torch.equal(a, b), f"{what}: max abs diff {(a - b).abs().max().item():.3e}"
+
+
+def save(name, x, sd, **outs):
+    GOLD.mkdir(parents=True, exist_ok=True)
+    arrs = {"x": x.numpy()}
+    for k, v in sd.items():
+        arrs["w:" + k] = v.numpy()
+    for k, v in outs.items():
+        arrs["out:" + k] = v.numpy()
+    np.savez_compressed(GOLD / f"{name}.npz", **arrs)
+
+
+def main():
+    torch.manual_seed(0)
+    torch.set_num_threads(4)
+    ZeroDCE_RE, ZeroDCEpp_RE, MODELS = install_stub_mon()
+    up_dce, up_dcepp, up_sci = load_upstream()
+    assert MODELS["zero_dce"]["zero_dce_re"] is ZeroDCE_RE
+    assert MODELS["zero_dce"]["zero_dce++_re"] is ZeroDCEpp_RE
+    report = []
+
+    # ---- state_dict layouts straight from the reference classes (F6) ----
+    m = ZeroDCE_RE()
+    keys = list(m.state_dict().keys())
+    exp = [f"e_conv{i}.{p}" for i in range(1, 8) for p in ("weight", "bias")] + \
+          [f"loss.loss_spa.weight_{d}" for d in ("left", "right", "up", "down")]
+    assert keys == exp, keys
+    assert m.out_channels == 24
+    mp = ZeroDCEpp_RE()
+    keys = list(mp.state_dict().keys())
+    exp = [f"e_conv{i}.{c}.{p}" for i in range(1, 8) for c in ("dw_conv", "pw_conv") for p in ("weight", "bias")] + \
+          [f"loss.loss_spa.weight_{d}" for d in ("left", "right", "up", "down")]
+    assert keys == exp, keys
+    assert mp.out_channels == 3
+    # init_weights: every conv weight ~ N(0, 0.02) (zero_dcepp.py:157-167)
+    for k, v in mp.state_dict().items():
+        if k.endswith("conv.weight") and v.numel() > 200:
+            assert 0.012 < v.std().item() < 0.028, (k, v.std().item())
+    # sf != 1 raises in the mon class as written
+    try:
+        ZeroDCEpp_RE(scale_factor=12).eval()({"image": torch.rand(1, 3, 48, 48)})
+        raise SystemExit("expected the reference ZeroDCEpp_RE(scale_factor=12) to raise")
+    except RuntimeError:
+        report.append("mon ZeroDCEpp_RE(scale_factor=12).forward raises RuntimeError (F3 confirmed)")
+
+    for regime in ("init", "stress"):
+        # ---------------- Zero-DCE ----------------
+        x = O.synthetic_lowlight(2, 40, 52, seed=101)
+        sd = O.make_dce_state_dict(7, regime)
+        m = ZeroDCE_RE().eval()
+        m.load_state_dict(sd, strict=False)
+        with torch.no_grad():
+            ref = m({"image": x})
+        assert list(ref.keys()) == [f"adjust_{i}" for i in range(8)] + ["adjust", "enhanced"]
+        got = O.zero_dce_forward(x, sd)
+        assert list(got.keys()) == list(ref.keys())
+        for k in ref:
+            eq(got[k], ref[k], f"dce/{regime}/{k}")
+        um = up_dce.enhance_net_nopool().eval()
+        um.load_state_dict(sd)
+        with torch.no_grad():
+            e1, e, r = um(x)
+        eq(got["enhanced"], e, f"dce-upstream/{regime}/enhanced")
+        eq(got["adjust"], r, f"dce-upstream/{regime}/adjust")
+        save(f"dce_{regime}", x, sd, adjust=ref["adjust"], enhanced=ref["enhanced"])
+        report.append(f"dce/{regime}: oracle == mon class == upstream; |adjust|max={ref['adjust'].abs().max():.3f}")
+
+        # ---------------- Zero-DCE++ ----------------
+        for sf, (H, W) in ((1, (36, 44)), (2, (36, 44)), (12, (96, 132))):
+            x = O.synthetic_lowlight(2, H, W, seed=200 + sf)
+            sd = O.make_dcepp_state_dict(11, regime)
+            got = O.zero_dcepp_forward(x, sd, scale_factor=sf)
+            um = up_dcepp.enhance_net_nopool(sf).eval()
+            um.load_state_dict(to_upstream_keys(sd))
+            with torch.no_grad():
+                e, r = um(x)
+            eq(got["enhanced"], e, f"dcepp-upstream/sf{sf}/{regime}/enhanced")
+            eq(got["adjust"], r, f"dcepp-upstream/sf{sf}/{regime}/adjust")
+            if sf == 1:
+                m = ZeroDCEpp_RE().eval()
+                m.load_state_dict(sd, strict=False)
+                with torch.no_grad():
+                    ref = m({"image": x})
+                assert list(ref.keys()) == ["adjust", "enhanced"]
+                eq(got["enhanced"], ref["enhanced"], f"dcepp-mon/sf1/{regime}/enhanced")
+                eq(got["adjust"], ref["adjust"], f"dcepp-mon/sf1/{regime}/adjust")
+            else:
+                # explicit-index restatements of ATen's resize agree with ATen
+                xd = torch.nn.functional.interpolate(x, scale_factor=1 / sf, mode="bilinear")
+                d = np.abs(O.bilinear_down_ref(x.numpy(), sf) - xd.numpy()).max()
+                assert d <= 1e-6, d
+                a_lr = O.zero_dcepp_lowres_net(xd, sd)
+                d = np.abs(O.bilinear_up_ref(a_lr.numpy(), H, W) - r.numpy()).max()
+                assert d <= 2e-6, d
+            save(f"dcepp_sf{sf}_{regime}", x, sd, adjust=r, enhanced=e)
+            report.append(f"dcepp/sf{sf}/{regime}: oracle == upstream"
+                          f"{' == mon class' if sf == 1 else ''}; |adjust|max={r.abs().max():.3f}")
+
+        # ---------------- SCI ----------------
+        x = O.synthetic_lowlight(2, 40, 52, seed=301)
+        sd = O.make_sci_state_dict(13, regime)
+        net = up_sci.EnhanceNetwork(layers=1, channels=3).eval()
+        full = dict(sd)
+        for k in list(sd):
+            if k.startswith("conv."):
+                full["blocks.0." + k[len("conv."):]] = sd[k]  # aliased module (sci/model.py:27-29)
+        net.load_state_dict(full)
+        with torch.no_grad():
+            illu_ref = net(x)
+            r_ref = torch.clamp(x / illu_ref, 0, 1)  # Finetunemodel.forward, sci/model.py:155-159
+        illu, r = O.sci_forward(x, sd)
+        eq(illu, illu_ref, f"sci/{regime}/illu")
+        eq(r, r_ref, f"sci/{regime}/r")
+        save(f"sci_{regime}", x, sd, illu=illu_ref, r=r_ref)
+        report.append(f"sci/{regime}: oracle == upstream EnhanceNetwork + divide")
+
+    (GOLD / "PIN_REPORT.txt").write_text(
+        f"generated by oracle/pin_against_reference.py with torch {torch.__version__} (CPU, fp32)\n" +
+        "\n".join(report) + "\n")
+    print("\n".join(report))
+    print("golden fixtures written to", GOLD)
+
+
+if __name__ == "__main__":
+    main()
