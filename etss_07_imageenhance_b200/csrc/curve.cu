@@ -1,0 +1,199 @@
+// Light-enhancement curve kernels and u8<->fp32 frame conversion.
+// HBM-bound streaming kernels: 128-bit accesses, grid sized in multiples of the SM count.
+#include "common.cuh"
+
+namespace b200 {
+
+// PER_ITER=false: a is [B,C,H,W]     (zero_dcepp.py:201-203)
+// PER_ITER=true : a is [B,C*iters,H,W], iteration i uses plane i*C+c (zero_dce.py:183-188)
+template <bool PER_ITER>
+__global__ void __launch_bounds__(256) curve_vec4_kernel(const float* __restrict__ x, const float* __restrict__ a,
+                                                         float* __restrict__ y, long long planes, int C,
+                                                         long long hw4, int iters) {
+    // one item = 4 consecutive pixels of one (b,c) plane
+    const long long total = planes * hw4;
+    for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < total;
+         it += (long long)gridDim.x * blockDim.x) {
+        const long long plane = it / hw4;
+        const long long p4 = it - plane * hw4;
+        const float* xp = x + (plane * hw4 + p4) * 4;
+        float4 v = ld_stream4(xp);
+        if (!PER_ITER) {
+            float4 m = ld_stream4(a + (plane * hw4 + p4) * 4);
+            for (int i = 0; i < iters; ++i) {
+                v.x = curve_step(v.x, m.x);
+                v.y = curve_step(v.y, m.y);
+                v.z = curve_step(v.z, m.z);
+                v.w = curve_step(v.w, m.w);
+            }
+        } else {
+            const long long b = plane / C;
+            const int c = (int)(plane - b * C);
+            const float* ap = a + ((b * C * iters + c) * hw4 + p4) * 4;
+            const long long stride = (long long)C * hw4 * 4;
+            float4 m[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (i < iters) m[i] = ld_stream4(ap + i * stride);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (i < iters) {
+                    v.x = curve_step(v.x, m[i].x);
+                    v.y = curve_step(v.y, m[i].y);
+                    v.z = curve_step(v.z, m[i].z);
+                    v.w = curve_step(v.w, m[i].w);
+                }
+            for (int i = 8; i < iters; ++i) {
+                float4 mm = ld_stream4(ap + i * stride);
+                v.x = curve_step(v.x, mm.x);
+                v.y = curve_step(v.y, mm.y);
+                v.z = curve_step(v.z, mm.z);
+                v.w = curve_step(v.w, mm.w);
+            }
+        }
+        st_stream4(y + (plane * hw4 + p4) * 4, v);
+    }
+}
+
+// scalar tail version for H*W not divisible by 4
+template <bool PER_ITER>
+__global__ void __launch_bounds__(256) curve_scalar_kernel(const float* __restrict__ x, const float* __restrict__ a,
+                                                           float* __restrict__ y, long long planes, int C,
+                                                           long long hw, int iters) {
+    const long long total = planes * hw;
+    for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < total;
+         it += (long long)gridDim.x * blockDim.x) {
+        const long long plane = it / hw;
+        const long long p = it - plane * hw;
+        float v = x[it];
+        if (!PER_ITER) {
+            const float m = a[it];
+            for (int i = 0; i < iters; ++i) v = curve_step(v, m);
+        } else {
+            const long long b = plane / C;
+            const int c = (int)(plane - b * C);
+            for (int i = 0; i < iters; ++i) v = curve_step(v, a[((b * iters + i) * C + c) * hw + p]);
+        }
+        y[it] = v;
+    }
+}
+
+template <bool PER_ITER>
+static int launch_curve(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream) {
+    if (!x || !a || !y) return B200_ERR_NULL;
+    if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || iters < 0) return B200_ERR_BAD_SHAPE;
+    if (!aligned16(x) || !aligned16(a) || !aligned16(y)) return B200_ERR_MISALIGNED;
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long planes = (long long)B * C;
+    const long long hw = (long long)H * W;
+    if (hw % 4 == 0) {
+        const long long total = planes * (hw / 4);
+        long long blocks = (total + 255) / 256;
+        const long long cap = (long long)B200_NUM_SMS * 16;
+        if (blocks > cap) blocks = cap;
+        curve_vec4_kernel<PER_ITER><<<(unsigned)blocks, 256, 0, s>>>(x, a, y, planes, C, hw / 4, iters);
+    } else {
+        const long long total = planes * hw;
+        long long blocks = (total + 255) / 256;
+        const long long cap = (long long)B200_NUM_SMS * 16;
+        if (blocks > cap) blocks = cap;
+        curve_scalar_kernel<PER_ITER><<<(unsigned)blocks, 256, 0, s>>>(x, a, y, planes, C, hw, iters);
+    }
+    return launch_status();
+}
+
+// ---- u8 HWC <-> fp32 NCHW (C = 3) ------------------------------------------------
+// One thread handles 4 consecutive pixels = 12 interleaved bytes (3 x 32-bit words).
+__global__ void __launch_bounds__(256) u8hwc_to_f32nchw_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst,
+                                                               long long frames, long long hw) {
+    const long long hw4 = hw >> 2;
+    const long long total = frames * hw4;
+    for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < total;
+         it += (long long)gridDim.x * blockDim.x) {
+        const long long f = it / hw4;
+        const long long p4 = it - f * hw4;
+        const uint32_t* s = reinterpret_cast<const uint32_t*>(src + (f * hw + p4 * 4) * 3);
+        const uint32_t w0 = __ldg(s), w1 = __ldg(s + 1), w2 = __ldg(s + 2);
+        // bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+        const float k = 255.f;
+        float4 r, g, b;
+        r.x = __fdiv_rn((float)(w0 & 0xff), k);
+        g.x = __fdiv_rn((float)((w0 >> 8) & 0xff), k);
+        b.x = __fdiv_rn((float)((w0 >> 16) & 0xff), k);
+        r.y = __fdiv_rn((float)(w0 >> 24), k);
+        g.y = __fdiv_rn((float)(w1 & 0xff), k);
+        b.y = __fdiv_rn((float)((w1 >> 8) & 0xff), k);
+        r.z = __fdiv_rn((float)((w1 >> 16) & 0xff), k);
+        g.z = __fdiv_rn((float)(w1 >> 24), k);
+        b.z = __fdiv_rn((float)(w2 & 0xff), k);
+        r.w = __fdiv_rn((float)((w2 >> 8) & 0xff), k);
+        g.w = __fdiv_rn((float)((w2 >> 16) & 0xff), k);
+        b.w = __fdiv_rn((float)(w2 >> 24), k);
+        float* d = dst + f * 3 * hw + p4 * 4;
+        st_stream4(d, r);
+        st_stream4(d + hw, g);
+        st_stream4(d + 2 * hw, b);
+    }
+}
+
+__device__ __forceinline__ uint32_t to_u8(float v) {
+    // to_image_nparray(denormalize=True): v*255 then astype(uint8) (truncation toward zero)
+    float t = __fmul_rn(fminf(fmaxf(v, 0.f), 1.f), 255.f);
+    return (uint32_t)(int)t;
+}
+
+__global__ void __launch_bounds__(256) f32nchw_to_u8hwc_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst,
+                                                               long long frames, long long hw) {
+    const long long hw4 = hw >> 2;
+    const long long total = frames * hw4;
+    for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < total;
+         it += (long long)gridDim.x * blockDim.x) {
+        const long long f = it / hw4;
+        const long long p4 = it - f * hw4;
+        const float* s = src + f * 3 * hw + p4 * 4;
+        const float4 r = ld_stream4(s), g = ld_stream4(s + hw), b = ld_stream4(s + 2 * hw);
+        const uint32_t w0 = to_u8(r.x) | (to_u8(g.x) << 8) | (to_u8(b.x) << 16) | (to_u8(r.y) << 24);
+        const uint32_t w1 = to_u8(g.y) | (to_u8(b.y) << 8) | (to_u8(r.z) << 16) | (to_u8(g.z) << 24);
+        const uint32_t w2 = to_u8(b.z) | (to_u8(r.w) << 8) | (to_u8(g.w) << 16) | (to_u8(b.w) << 24);
+        uint32_t* d = reinterpret_cast<uint32_t*>(dst + (f * hw + p4 * 4) * 3);
+        d[0] = w0;
+        d[1] = w1;
+        d[2] = w2;
+    }
+}
+
+}  // namespace b200
+
+extern "C" int b200_curve_shared(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters,
+                                 void* stream) {
+    return b200::launch_curve<false>(x, a, y, B, C, H, W, iters, stream);
+}
+
+extern "C" int b200_curve_per_iter(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters,
+                                   void* stream) {
+    return b200::launch_curve<true>(x, a, y, B, C, H, W, iters, stream);
+}
+
+extern "C" int b200_u8hwc_to_f32nchw(const uint8_t* src, float* dst, int B, int H, int W, void* stream) {
+    if (!src || !dst) return B200_ERR_NULL;
+    if (B <= 0 || H <= 0 || W <= 0) return B200_ERR_BAD_SHAPE;
+    const long long hw = (long long)H * W;
+    if (hw % 4 != 0) return B200_ERR_UNSUPPORTED;
+    if (!b200::aligned16(dst) || (reinterpret_cast<uintptr_t>(src) & 3u)) return B200_ERR_MISALIGNED;
+    long long blocks = ((long long)B * (hw / 4) + 255) / 256;
+    if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
+    b200::u8hwc_to_f32nchw_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, B, hw);
+    return b200::launch_status();
+}
+
+extern "C" int b200_f32nchw_to_u8hwc(const float* src, uint8_t* dst, int B, int H, int W, void* stream) {
+    if (!src || !dst) return B200_ERR_NULL;
+    if (B <= 0 || H <= 0 || W <= 0) return B200_ERR_BAD_SHAPE;
+    const long long hw = (long long)H * W;
+    if (hw % 4 != 0) return B200_ERR_UNSUPPORTED;
+    if (!b200::aligned16(src) || (reinterpret_cast<uintptr_t>(dst) & 3u)) return B200_ERR_MISALIGNED;
+    long long blocks = ((long long)B * (hw / 4) + 255) / 256;
+    if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
+    b200::f32nchw_to_u8hwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, B, hw);
+    return b200::launch_status();
+}

@@ -1,0 +1,158 @@
+/*
+ * b200dce.h — C ABI of the B200-native (sm_100a) Zero-DCE / Zero-DCE++ / SCI
+ * inference hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types.  Each
+ * entry point cites the reference code it replaces (paths relative to the
+ * reference repository root, SKKUAutoLab/ETSS-07-ImageEnhance).
+ *
+ * Conventions
+ *   - All image tensors are NCHW, contiguous, fp32, values nominally in [0,1],
+ *     device pointers in the current CUDA context.  16-byte alignment is
+ *     required for every tensor base pointer (B200_ERR_MISALIGNED otherwise).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default
+ *     stream).  Every call only ENQUEUES work on that stream: the library never
+ *     allocates, frees or synchronises, and holds no mutable global state, so it
+ *     is re-entrant and thread safe.  The caller owns every buffer, including
+ *     the workspace, and must keep them alive until the stream has drained.
+ *   - Return value: 0 (B200_OK) or a negative B200_ERR_* code;
+ *     b200_strerror() gives the text.  Launch failures are reported from
+ *     cudaGetLastError() (B200_ERR_LAUNCH).
+ *   - There is NO CPU fallback: on a machine without an sm_100 device every
+ *     compute entry point returns B200_ERR_LAUNCH / B200_ERR_NO_DEVICE.
+ */
+#ifndef B200DCE_H_
+#define B200DCE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_ERR_NULL (-1)        /* a required pointer is NULL */
+#define B200_ERR_BAD_SHAPE (-2)   /* non-positive dims, H or W not divisible by scale_factor, ... */
+#define B200_ERR_MISALIGNED (-3)  /* a tensor base pointer is not 16-byte aligned */
+#define B200_ERR_UNSUPPORTED (-4) /* hyper-parameter outside what the kernels implement */
+#define B200_ERR_WORKSPACE (-5)   /* workspace too small (see *_workspace_bytes) */
+#define B200_ERR_LAUNCH (-6)      /* CUDA launch error */
+#define B200_ERR_NO_DEVICE (-7)   /* no sm_100 CUDA device is current */
+
+/* precision selector for the Zero-DCE conv stack */
+#define B200_PREC_FP32 0   /* fp32 CUDA-core direct convolution (FFMA2), fp32 accumulate            */
+#define B200_PREC_BF16 1   /* bf16 operands on tcgen05 tensor cores, fp32 accumulate in TMEM         */
+#define B200_PREC_BF16X3 2 /* 3-term split-bf16 (hi*hi + lo*hi + hi*lo) on tcgen05: ~fp32 accuracy   */
+
+int b200_version(void);
+const char* b200_strerror(int code);
+/* 0 if the current device is sm_100 (B200), else B200_ERR_NO_DEVICE. */
+int b200_check_device(void);
+
+/* ------------------------------------------------------------------------- *
+ * Light-enhancement curve  y <- y + a*(y*y - y), `iters` times.
+ * ------------------------------------------------------------------------- */
+
+/* Shared map: the same C-channel map `a` [B,C,H,W] is used for every iteration.
+ * Replaces src/mon/vision/enhance/llie/zero_dce/zero_dcepp.py:201-203
+ * (upstream src/mon_extra/vision/enhance/llie/zero_dce++/model.py:51-62).
+ * Bit-exact against ATen on CPU (mul, sub, mul, add with no contraction). */
+int b200_curve_shared(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream);
+
+/* Per-iteration maps: `a` is [B, C*iters, H, W]; iteration i uses channels
+ * [i*C, (i+1)*C).  Replaces zero_dce.py:183-188 (torch.split + loop). */
+int b200_curve_per_iter(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Zero-DCE++  (ZeroDCEpp_RE.forward, zero_dcepp.py:182-208; for scale_factor
+ * != 1 the intended semantics of upstream zero_dce++/model.py:39,64-82).
+ * Architecture: in_channels=3, num_channels=32 (the reference default).
+ * ------------------------------------------------------------------------- */
+
+/* Number of floats in the packed weight buffer. */
+size_t b200_dcepp_packed_floats(void);
+
+/* Re-pack the 28 state_dict tensors (device pointers, fp32, the layouts of
+ * e_conv{i}.dw_conv.weight [Cin,1,3,3], .dw_conv.bias [Cin], .pw_conv.weight
+ * [Cout,Cin,1,1], .pw_conv.bias [Cout]; src/mon/nn/modules/conv/dsconv.py:122-149)
+ * into `packed` (device, b200_dcepp_packed_floats() floats).  The four arrays
+ * are HOST arrays of 7 device pointers, layer order e_conv1..7. */
+int b200_dcepp_pack_weights(const float* const* dw_w, const float* const* dw_b, const float* const* pw_w,
+                            const float* const* pw_b, float* packed, void* stream);
+
+size_t b200_dcepp_workspace_bytes(int B, int H, int W, int scale_factor);
+
+/* x [B,3,H,W] -> enhanced [B,3,H,W] and (optional, may be NULL) adjust
+ * [B,3,H,W] (the full-resolution curve map the reference returns).
+ * scale_factor: integer >= 1; H and W must be divisible by it (the reference
+ * raises a broadcast error otherwise).  Stages:
+ *   a3  bilinear downsample, align_corners=False (zero_dcepp.py:186-188) — fused into layer 1's load
+ *   a4  7x [depthwise 3x3 + pointwise 1x1] + ReLU/tanh (zero_dcepp.py:190-196)
+ *   a5  bilinear upsample, align_corners=True (upstream model.py:39,80)   \  one fused full-resolution pass:
+ *   a6  8-iteration curve (zero_dcepp.py:201-203)                         /  reads x once, writes each output once */
+int b200_dcepp_forward(const float* x, const float* packed, float* enhanced, float* adjust_or_null, int B, int H, int W,
+                       int scale_factor, int iters, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Only the low-resolution curve-estimation net (stages a3+a4): writes a_lr
+ * [B,3,H/sf,W/sf].  Exposed for tests and for callers that cache the map. */
+int b200_dcepp_lowres(const float* x, const float* packed, float* a_lr, int B, int H, int W, int scale_factor,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* Only stages a5+a6: a_lr [B,3,h,w] -> enhanced / adjust at [B,3,H,W]. */
+int b200_dcepp_apply(const float* x, const float* a_lr, float* enhanced, float* adjust_or_null, int B, int H, int W,
+                     int h, int w, int iters, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Zero-DCE  (ZeroDCE_RE.forward, zero_dce.py:173-191): 7x conv3x3 (3->32,
+ * 32->32 x3, 64->32 x2, 64->3*iters) with ReLU / tanh and the per-iteration
+ * curve.  in_channels=3, num_channels=32, 1 <= iters <= 8.
+ * ------------------------------------------------------------------------- */
+size_t b200_dce_packed_bytes(int precision, int iters);
+
+/* w[i]: e_conv{i+1}.weight (OIHW fp32, device), b[i]: e_conv{i+1}.bias.
+ * HOST arrays of 7 device pointers. */
+int b200_dce_pack_weights(const float* const* w, const float* const* b, void* packed, int precision, int iters,
+                          void* stream);
+
+size_t b200_dce_workspace_bytes(int B, int H, int W, int precision);
+
+/* x [B,3,H,W] -> adjust [B,3*iters,H,W] (tanh output, zero_dce.py:182) and
+ * enhanced [B,3,H,W] (zero_dce.py:186-188).  Both are required outputs of the
+ * reference; `adjust` may be NULL to skip materialising it. */
+int b200_dce_forward(const float* x, const void* packed, float* adjust_or_null, float* enhanced, int B, int H, int W,
+                     int iters, int precision, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * SCI  (Finetunemodel.forward, src/mon_extra/vision/enhance/llie/sci/model.py:155-159
+ * over EnhanceNetwork.forward :36-45, layers=1, channels=3, BatchNorm in eval mode).
+ * ------------------------------------------------------------------------- */
+#define B200_SCI_PACKED_FLOATS 252
+
+/* HOST-side pack (no CUDA): all pointers are HOST memory.  conv weights are
+ * [3,3,3,3] OIHW, biases [3]; bn_* are the BatchNorm2d affine/running stats
+ * (folded into the second conv).  `packed_host` receives 252 floats that
+ * b200_sci_forward passes to the kernel by value (constant bank). */
+int b200_sci_pack_weights_host(const float* in_w, const float* in_b, const float* mid_w, const float* mid_b,
+                               const float* bn_gamma, const float* bn_beta, const float* bn_mean, const float* bn_var,
+                               float bn_eps, const float* out_w, const float* out_b, float* packed_host);
+
+/* x [B,3,H,W] -> illu [B,3,H,W] (may be NULL) and r [B,3,H,W].
+ * `packed_host` is HOST memory (B200_SCI_PACKED_FLOATS floats). */
+int b200_sci_forward(const float* x, const float* packed_host, float* illu_or_null, float* r, int B, int H, int W,
+                     void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * "next" rows: u8 HWC <-> fp32 NCHW frame conversion.
+ * Replaces src/mon/core/image/utils.py:801-848 (to_image_tensor, /255) and
+ * :766-800 (to_image_nparray denormalize: *255 then astype(uint8), i.e.
+ * truncation; values are clamped to [0,255] first, which is identical for the
+ * enhancers' [0,1] outputs).
+ * ------------------------------------------------------------------------- */
+int b200_u8hwc_to_f32nchw(const uint8_t* src, float* dst, int B, int H, int W, void* stream);
+int b200_f32nchw_to_u8hwc(const float* src, uint8_t* dst, int B, int H, int W, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DCE_H_ */
