@@ -1,0 +1,114 @@
+"""ctypes binding of the C-ABI library `lib/libb200dce.so` (include/b200dce.h).
+
+The library is the product: there is NO fallback.  If it is missing or cannot be
+loaded, importing the ops raises with the build command.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_size_t, c_void_p
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "lib" / "libb200dce.so"
+
+# error codes (include/b200dce.h)
+OK = 0
+ERR_NULL, ERR_BAD_SHAPE, ERR_MISALIGNED, ERR_UNSUPPORTED = -1, -2, -3, -4
+ERR_WORKSPACE, ERR_LAUNCH, ERR_NO_DEVICE = -5, -6, -7
+PREC_FP32, PREC_BF16, PREC_BF16X3 = 0, 1, 2
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3}
+SCI_PACKED_FLOATS = 252
+
+_PP = POINTER(c_void_p)  # const float* const*  (host array of device pointers)
+
+_SIGNATURES = {
+    "b200_version": (c_int, []),
+    "b200_strerror": (c_char_p, [c_int]),
+    "b200_check_device": (c_int, []),
+    "b200_curve_shared": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_curve_per_iter": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_dcepp_packed_floats": (c_size_t, []),
+    "b200_dcepp_pack_weights": (c_int, [_PP, _PP, _PP, _PP, c_void_p, c_void_p]),
+    "b200_dcepp_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200_dcepp_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                   c_void_p, c_size_t, c_void_p]),
+    "b200_dcepp_lowres": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_size_t,
+                                  c_void_p]),
+    "b200_dcepp_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                 c_void_p]),
+    "b200_dce_packed_bytes": (c_size_t, [c_int, c_int]),
+    "b200_dce_pack_weights": (c_int, [_PP, _PP, c_void_p, c_int, c_int, c_void_p]),
+    "b200_dce_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200_dce_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                 c_void_p, c_size_t, c_void_p]),
+    "b200_sci_pack_weights_host": (c_int, [c_void_p] * 8 + [c_float, c_void_p, c_void_p, c_void_p]),
+    "b200_sci_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "b200_u8hwc_to_f32nchw": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "b200_f32nchw_to_u8hwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+}
+EXPORTS = tuple(_SIGNATURES)
+
+_lib = None
+
+
+class B200Error(RuntimeError):
+    """A negative return code from the C ABI."""
+
+    def __init__(self, code: int, where: str):
+        self.code = code
+        text = lib().b200_strerror(code).decode() if _lib is not None else "?"
+        super().__init__(f"{where}: {text} (code {code})")
+
+
+def _preload_cudart():
+    try:
+        import nvidia.cuda_runtime  # type: ignore
+        d = Path(list(nvidia.cuda_runtime.__path__)[0]) / "lib"
+        for f in sorted(d.glob("libcudart.so*")):
+            ctypes.CDLL(str(f), mode=ctypes.RTLD_GLOBAL)
+            return
+    except Exception:
+        pass
+
+
+def lib() -> ctypes.CDLL:
+    """Load (once) and return the C-ABI library.  Raises if it is absent: build it
+    with `python -m etss_07_imageenhance_b200.build` (or `__graft_entry__.build()`)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = Path(os.environ.get("B200DCE_LIB", LIB_PATH))
+    if not path.exists():
+        raise RuntimeError(
+            f"b200dce: native library {path} is missing and there is no fallback path. "
+            "Build it with `python -m etss_07_imageenhance_b200.build`.")
+    try:
+        import torch  # noqa: F401  (loads the CUDA runtime the library shares with torch)
+    except Exception:
+        pass
+    try:
+        handle = ctypes.CDLL(str(path))
+    except OSError:
+        _preload_cudart()
+        handle = ctypes.CDLL(str(path))
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(handle, name)  # AttributeError if the .so does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = handle
+    return _lib
+
+
+def check(code: int, where: str) -> None:
+    if code != OK:
+        raise B200Error(code, where)
+
+
+def ptr_array(ptrs) -> ctypes.Array:
+    """Host array of device pointers (the `const float* const*` arguments)."""
+    arr = (c_void_p * len(ptrs))()
+    for i, p in enumerate(ptrs):
+        arr[i] = p
+    return arr

@@ -1,0 +1,241 @@
+"""GPU (-m gpu): the CUDA path, called through the plugin classes / torch.ops / C ABI, against the oracle
+(oracle/oracle.py, pinned to the reference by oracle/pin_against_reference.py) and the committed golden
+vectors.  Tolerance per BASELINE.json: fp32 mode max-abs <= 1e-3 on `adjust` and `enhanced` (the fp32
+kernels are expected ~1e-6..1e-5: TIGHT below catches indexing bugs the 1e-3 contract would hide);
+the curve kernels are bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+import etss_07_imageenhance_b200 as P
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-3      # contract (BASELINE.json north_star, fp32 mode)
+TIGHT = 1e-4    # what the fp32 kernels actually have to meet here
+
+
+def maxerr(a, b):
+    return (a.detach().cpu().double() - b.detach().cpu().double()).abs().max().item()
+
+
+def load_into(model, sd):
+    missing, unexpected = model.load_state_dict(sd, strict=False)
+    assert not unexpected and all(k.startswith("loss.") for k in missing)
+    return model
+
+
+# ------------------------------------------------------------------ curve kernels: bit-exact
+@pytest.mark.parametrize("shape", [(2, 3, 40, 52), (1, 3, 7, 9), (3, 3, 33, 31), (1, 1, 1, 1)])
+@pytest.mark.parametrize("iters", [1, 8])
+def test_curve_shared_bit_exact(cuda_dev, shape, iters):
+    g = torch.Generator().manual_seed(1)
+    x = torch.rand(shape, generator=g)
+    a = torch.rand(shape, generator=g) * 2 - 1
+    y = torch.ops.b200dce.curve_shared(x.to(cuda_dev), a.to(cuda_dev), iters)
+    assert torch.equal(y.cpu(), O.curve_shared(x, a, iters))
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 40, 52), (1, 3, 7, 9)])
+@pytest.mark.parametrize("iters", [1, 3, 8])
+def test_curve_per_iter_bit_exact(cuda_dev, shape, iters):
+    g = torch.Generator().manual_seed(2)
+    B, C, H, W = shape
+    x = torch.rand(shape, generator=g)
+    a = torch.rand(B, C * iters, H, W, generator=g) * 2 - 1
+    y = torch.ops.b200dce.curve_per_iter(x.to(cuda_dev), a.to(cuda_dev), iters)
+    assert torch.equal(y.cpu(), O.curve_per_iter(x, a, iters))
+
+
+def test_curve_fixed_points_full_size(cuda_dev):
+    # size-independent property at BASELINE size (one 4K frame): y in {0,1} or a == 0  =>  unchanged
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = (torch.rand(1, 3, 2160, 3840, device=cuda_dev, generator=g) > 0.5).float()
+    a = torch.rand(1, 3, 2160, 3840, device=cuda_dev, generator=g) * 2 - 1
+    assert torch.equal(torch.ops.b200dce.curve_shared(x, a, 8), x)
+    x = torch.rand(1, 3, 2160, 3840, device=cuda_dev, generator=g)
+    assert torch.equal(torch.ops.b200dce.curve_shared(x, torch.zeros_like(x), 8), x)
+
+
+def test_empty_batch(cuda_dev):
+    x = torch.empty(0, 3, 24, 24, device=cuda_dev)
+    assert torch.ops.b200dce.curve_shared(x, x, 8).shape == x.shape
+    m = P.ZeroDCEpp_RE(scale_factor=12).to(cuda_dev)
+    out = m({"image": x})
+    assert out["enhanced"].shape == x.shape
+
+
+# ------------------------------------------------------------------ Zero-DCE++ against the reference golden vectors
+@pytest.mark.parametrize("regime", ["init", "stress"])
+@pytest.mark.parametrize("name,sf", [("dcepp_sf1", 1), ("dcepp_sf2", 2), ("dcepp_sf12", 12)])
+def test_dcepp_golden(cuda_dev, golden, name, sf, regime):
+    x, sd, outs = golden(f"{name}_{regime}")
+    m = load_into(P.MODELS.build(config={"name": "zero_dce++_re", "scale_factor": sf}), sd).to(cuda_dev)
+    xin = x.to(cuda_dev)
+    keep = xin.clone()
+    out = m({"image": xin})
+    assert list(out.keys()) == ["adjust", "enhanced"]
+    assert torch.equal(xin, keep) and out["enhanced"].data_ptr() != xin.data_ptr()
+    assert out["enhanced"].dtype == torch.float32 and out["enhanced"].device == xin.device
+    ea, ee = maxerr(out["adjust"], outs["adjust"]), maxerr(out["enhanced"], outs["enhanced"])
+    assert ea <= TOL and ee <= TOL
+    assert ea <= TIGHT and ee <= TIGHT, (ea, ee)
+    # fast mode: same enhanced, no adjust
+    m.return_adjust = False
+    out2 = m({"image": xin})
+    assert list(out2.keys()) == ["enhanced"] and torch.equal(out2["enhanced"], out["enhanced"])
+
+
+@pytest.mark.parametrize("sf,H,W,B", [(1, 37, 45, 2), (1, 8, 32, 1), (3, 27, 33, 2), (4, 64, 100, 1),
+                                      (12, 36, 60, 3), (12, 12, 12, 1), (2, 2, 2, 1), (1, 1, 1, 1)])
+def test_dcepp_ragged_shapes_vs_oracle(cuda_dev, sf, H, W, B):
+    x = O.synthetic_lowlight(B, H, W, seed=40 + sf)
+    sd = O.make_dcepp_state_dict(21, "stress")
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=sf), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    ref = O.zero_dcepp_forward(x, sd, scale_factor=sf)
+    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT
+    assert maxerr(out["enhanced"], ref["enhanced"]) <= TIGHT
+
+
+def test_dcepp_stage_ops_vs_oracle(cuda_dev):
+    x = O.synthetic_lowlight(2, 96, 144, seed=7)
+    sd = O.make_dcepp_state_dict(5, "stress")
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=12), sd).to(cuda_dev)
+    a_lr = torch.ops.b200dce.dcepp_lowres(x.to(cuda_dev), m.packed_weights(), 12)
+    xd = torch.nn.functional.interpolate(x, scale_factor=1 / 12, mode="bilinear")
+    ref_lr = O.zero_dcepp_lowres_net(xd, sd)
+    assert maxerr(a_lr, ref_lr) <= TIGHT
+    # upsample + curve from the ORACLE's low-res map: isolates the full-resolution kernel
+    adj, enh = torch.ops.b200dce.dcepp_apply(x.to(cuda_dev), ref_lr.to(cuda_dev), 8, True)
+    up = torch.from_numpy(O.bilinear_up_ref(ref_lr.numpy(), 96, 144))
+    assert maxerr(adj, up) <= 2e-6
+    assert maxerr(enh, O.curve_shared(x, up, 8)) <= 1e-5
+
+
+def test_dcepp_indivisible_size_raises(cuda_dev):
+    m = P.ZeroDCEpp_RE(scale_factor=12).to(cuda_dev)
+    with pytest.raises(RuntimeError, match="divisible"):
+        m({"image": torch.rand(1, 3, 50, 48, device=cuda_dev)})
+
+
+def test_dcepp_full_size_1080p_vs_oracle_and_properties(cuda_dev):
+    # BASELINE C5 shape; the CPU oracle does a 1080p sf=12 frame in ~50 ms, so compare directly
+    x = O.synthetic_lowlight(2, 1080, 1920, seed=55)
+    sd = O.make_dcepp_state_dict(31, "stress")
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=12), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    ref = O.zero_dcepp_forward(x, sd, scale_factor=12)
+    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT
+    assert maxerr(out["enhanced"], ref["enhanced"]) <= TIGHT
+    # zero weights + zero bias => adjust == 0 and enhanced == x exactly, at full 4K size
+    z = load_into(P.ZeroDCEpp_RE(scale_factor=12), {k: torch.zeros_like(v) for k, v in sd.items()}).to(cuda_dev)
+    x4k = O.synthetic_lowlight(1, 2160, 3840, seed=56).to(cuda_dev)
+    o = z({"image": x4k})
+    assert torch.equal(o["enhanced"], x4k) and not o["adjust"].any()
+    # frames are independent: batch of 2 == two batches of 1 (the sharding premise)
+    o1 = m({"image": x[1:2].to(cuda_dev)})
+    assert torch.equal(o1["enhanced"], out["enhanced"][1:2])
+
+
+def test_dcepp_weight_cache_invalidation(cuda_dev):
+    x = O.synthetic_lowlight(1, 48, 72, seed=3).to(cuda_dev)
+    m = P.ZeroDCEpp_RE(scale_factor=12).to(cuda_dev)
+    a = m({"image": x})["enhanced"]
+    sd = O.make_dcepp_state_dict(9, "stress")
+    load_into(m, sd)
+    b = m({"image": x})["enhanced"]
+    assert not torch.equal(a, b)
+    assert maxerr(b, O.zero_dcepp_forward(x.cpu(), sd, 12)["enhanced"]) <= TIGHT
+
+
+# ------------------------------------------------------------------ Zero-DCE (fp32 mode)
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_dce_fp32_golden(cuda_dev, golden, regime):
+    x, sd, outs = golden(f"dce_{regime}")
+    m = load_into(P.MODELS.build(name="zero_dce_re"), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    assert list(out.keys()) == [f"adjust_{i}" for i in range(8)] + ["adjust", "enhanced"]
+    for i in range(8):   # views of adjust, as in the reference
+        assert out[f"adjust_{i}"].data_ptr() == out["adjust"][:, 3 * i:3 * i + 3].data_ptr()
+    ea, ee = maxerr(out["adjust"], outs["adjust"]), maxerr(out["enhanced"], outs["enhanced"])
+    assert ea <= TOL and ee <= TOL
+    assert ea <= TIGHT and ee <= TIGHT, (ea, ee)
+
+
+@pytest.mark.parametrize("H,W,B,iters", [(37, 45, 3, 8), (8, 32, 1, 8), (1, 1, 1, 8), (19, 70, 2, 3), (64, 64, 5, 1)])
+def test_dce_fp32_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
+    x = O.synthetic_lowlight(B, H, W, seed=60 + iters)
+    sd = O.make_dce_state_dict(17, "stress", num_iters=iters)
+    m = load_into(P.ZeroDCE_RE(num_iters=iters), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    ref = O.zero_dce_forward(x, sd, num_iters=iters)
+    assert out["adjust"].shape == (B, 3 * iters, H, W)
+    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT
+    assert maxerr(out["enhanced"], ref["enhanced"]) <= TIGHT
+
+
+def test_dce_fp32_zero_weights_identity_1080p(cuda_dev):
+    sd = {k: torch.zeros_like(v) for k, v in O.make_dce_state_dict(1).items()}
+    m = load_into(P.ZeroDCE_RE(), sd).to(cuda_dev)
+    x = O.synthetic_lowlight(1, 1080, 1920, seed=8).to(cuda_dev)
+    out = m({"image": x})
+    assert torch.equal(out["enhanced"], x) and not out["adjust"].any()
+
+
+# ------------------------------------------------------------------ SCI
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_sci_golden(cuda_dev, golden, regime):
+    x, sd, outs = golden(f"sci_{regime}")
+    m = P.MODELS.build(name="sci_re")
+    m.enhance.load_state_dict({**sd, **{"blocks.0." + k[5:]: v for k, v in sd.items() if k.startswith("conv.")}})
+    m = m.to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    assert list(out.keys()) == ["illumination", "enhanced"]
+    assert maxerr(out["illumination"], outs["illu"]) <= TIGHT
+    # r = clamp(x / illu): the division amplifies illu's rounding where illu is small -> contract tolerance
+    assert maxerr(out["enhanced"], outs["r"]) <= TOL
+
+
+@pytest.mark.parametrize("H,W,B", [(17, 33, 2), (1, 1, 1), (16, 32, 1), (45, 100, 3)])
+def test_sci_ragged_shapes_vs_oracle(cuda_dev, H, W, B):
+    x = O.synthetic_lowlight(B, H, W, seed=70)
+    sd = O.make_sci_state_dict(23, "stress")
+    illu, r = torch.ops.b200dce.sci_forward(x.to(cuda_dev), P.ops.sci_pack(sd), True)
+    ri, rr = O.sci_forward(x, sd)
+    assert maxerr(illu, ri) <= TIGHT and maxerr(r, rr) <= TOL
+
+
+# ------------------------------------------------------------------ frame format + scheduler
+def test_u8_conversions_exact(cuda_dev):
+    g = torch.Generator().manual_seed(5)
+    frames = torch.randint(0, 256, (2, 36, 52, 3), dtype=torch.uint8, generator=g)
+    f = torch.ops.b200dce.u8hwc_to_f32nchw(frames.to(cuda_dev)).cpu()
+    ref = frames.permute(0, 3, 1, 2).float() / 255.0          # to_image_tensor(normalize=True)
+    assert torch.equal(f, ref)
+    back = torch.ops.b200dce.f32nchw_to_u8hwc(f.to(cuda_dev)).cpu()
+    ref_back = (ref * 255).to(torch.uint8).permute(0, 2, 3, 1)  # to_image_nparray(denormalize=True): truncation
+    assert torch.equal(back, ref_back)
+
+
+@pytest.mark.parametrize("wire", ["f32", "u8"])
+def test_frame_pipeline_matches_direct_forward(cuda_dev, wire):
+    H, W, N = 48, 72, 7
+    sd = O.make_dcepp_state_dict(5, "stress")
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=12), sd).to(cuda_dev)
+    pipe = P.FramePipeline(m, frames_per_chunk=2, H=H, W=W, wire=wire, slots=3)
+    if wire == "f32":
+        host_in = O.synthetic_lowlight(N, H, W, seed=2).pin_memory()
+        host_out = torch.empty_like(host_in).pin_memory()
+        pipe.run(host_in, host_out)
+        ref = m({"image": host_in.to(cuda_dev)})["enhanced"].cpu()
+        assert torch.equal(host_out, ref)
+    else:
+        g = torch.Generator().manual_seed(6)
+        host_in = torch.randint(0, 120, (N, H, W, 3), dtype=torch.uint8, generator=g).pin_memory()
+        host_out = torch.empty_like(host_in).pin_memory()
+        pipe.run(host_in, host_out)
+        x = torch.ops.b200dce.u8hwc_to_f32nchw(host_in.to(cuda_dev))
+        ref = torch.ops.b200dce.f32nchw_to_u8hwc(m({"image": x})["enhanced"]).cpu()
+        assert torch.equal(host_out, ref)
+    assert pipe.launches > 0

@@ -1,0 +1,95 @@
+"""CPU: the oracle restatement against the golden vectors produced by the REFERENCE's own code
+(oracle/pin_against_reference.py), plus the domain properties the GPU tests rely on."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+CASES_DCEPP = [("dcepp_sf1", 1), ("dcepp_sf2", 2), ("dcepp_sf12", 12)]
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_oracle_dce_matches_reference_golden(golden, regime):
+    x, sd, outs = golden(f"dce_{regime}")
+    got = O.zero_dce_forward(x, sd)
+    assert list(got.keys()) == [f"adjust_{i}" for i in range(8)] + ["adjust", "enhanced"]
+    assert torch.equal(got["adjust"], outs["adjust"])
+    assert torch.equal(got["enhanced"], outs["enhanced"])
+    for i in range(8):  # adjust_i are views of adjust (zero_dce.py:183)
+        assert got[f"adjust_{i}"].data_ptr() == got["adjust"][:, 3 * i:3 * i + 3].data_ptr()
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+@pytest.mark.parametrize("name,sf", CASES_DCEPP)
+def test_oracle_dcepp_matches_reference_golden(golden, name, sf, regime):
+    x, sd, outs = golden(f"{name}_{regime}")
+    got = O.zero_dcepp_forward(x, sd, scale_factor=sf)
+    assert torch.equal(got["adjust"], outs["adjust"])
+    assert torch.equal(got["enhanced"], outs["enhanced"])
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_oracle_sci_matches_reference_golden(golden, regime):
+    x, sd, outs = golden(f"sci_{regime}")
+    illu, r = O.sci_forward(x, sd)
+    assert torch.equal(illu, outs["illu"])
+    assert torch.equal(r, outs["r"])
+
+
+def test_stress_regime_exercises_the_curve(golden):
+    _, _, outs = golden("dce_stress")
+    assert outs["adjust"].abs().max() > 0.5
+    _, _, outs = golden("dcepp_sf12_stress")
+    assert outs["adjust"].abs().max() > 0.5
+
+
+def test_curve_sign_follows_the_code_not_the_paper():
+    # zero_dce.py:187: y + a*(y^2 - y) == y - a*y*(1-y); positive a DARKENS
+    x = torch.full((1, 3, 2, 2), 0.5)
+    a = torch.full((1, 3, 2, 2), 0.5)
+    y = O.curve_shared(x, a, 1)
+    assert torch.allclose(y, torch.full_like(y, 0.5 + 0.5 * (0.25 - 0.5)))
+
+
+def test_curve_fixed_points_and_identity():
+    g = torch.Generator().manual_seed(3)
+    a = torch.rand(2, 3, 5, 7, generator=g) * 2 - 1
+    for v in (0.0, 1.0):
+        x = torch.full((2, 3, 5, 7), v)
+        assert torch.equal(O.curve_shared(x, a, 8), x)
+    x = torch.rand(2, 3, 5, 7, generator=g)
+    assert torch.equal(O.curve_shared(x, torch.zeros_like(x), 8), x)
+    a24 = torch.zeros(2, 24, 5, 7)
+    assert torch.equal(O.curve_per_iter(x, a24, 8), x)
+
+
+def test_zero_weights_give_identity():
+    sd = {k: torch.zeros_like(v) for k, v in O.make_dcepp_state_dict(1).items()}
+    x = O.synthetic_lowlight(1, 24, 36, seed=5)
+    out = O.zero_dcepp_forward(x, sd, scale_factor=12)
+    assert torch.equal(out["adjust"], torch.zeros_like(x))
+    assert torch.equal(out["enhanced"], x)
+
+
+@pytest.mark.parametrize("sf,H,W", [(2, 12, 20), (3, 18, 27), (12, 48, 72)])
+def test_explicit_bilinear_restatements_match_aten(sf, H, W):
+    x = O.synthetic_lowlight(1, H, W, seed=9)
+    xd = torch.nn.functional.interpolate(x, scale_factor=1 / sf, mode="bilinear")
+    assert np.abs(O.bilinear_down_ref(x.numpy(), sf) - xd.numpy()).max() <= 1e-6
+    up = torch.nn.UpsamplingBilinear2d(scale_factor=sf)(xd)
+    assert np.abs(O.bilinear_up_ref(xd.numpy(), H, W) - up.numpy()).max() <= 2e-6
+
+
+def test_sf12_downsample_is_the_2x2_mean_at_offsets_5_6():
+    # SURVEY F4
+    x = O.synthetic_lowlight(1, 48, 72, seed=4)
+    xd = torch.nn.functional.interpolate(x, scale_factor=1 / 12, mode="bilinear")
+    m = 0.25 * (x[..., 5::12, 5::12] + x[..., 5::12, 6::12] + x[..., 6::12, 5::12] + x[..., 6::12, 6::12])
+    assert (xd - m).abs().max() < 1e-6
+
+
+def test_synthetic_input_is_deterministic_and_in_range():
+    a = O.synthetic_lowlight(2, 24, 36, seed=1)
+    b = O.synthetic_lowlight(2, 24, 36, seed=1)
+    assert torch.equal(a, b) and a.min() == 0.0 and a.max() == 1.0
