@@ -82,11 +82,14 @@ template <bool PER_ITER>
 static int launch_curve(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream) {
     if (!x || !a || !y) return B200_ERR_NULL;
     if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || iters < 0) return B200_ERR_BAD_SHAPE;
-    if (!aligned16(x) || !aligned16(a) || !aligned16(y)) return B200_ERR_MISALIGNED;
+    // float alignment is required; 16-byte alignment only selects the vector kernel (frame sub-batches of a
+    // ragged shape start at 4-byte-aligned offsets)
+    if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(y)) & 3u)
+        return B200_ERR_MISALIGNED;
     cudaStream_t s = (cudaStream_t)stream;
     const long long planes = (long long)B * C;
     const long long hw = (long long)H * W;
-    if (hw % 4 == 0) {
+    if (hw % 4 == 0 && aligned16(x) && aligned16(a) && aligned16(y)) {
         const long long total = planes * (hw / 4);
         long long blocks = (total + 255) / 256;
         const long long cap = (long long)B200_NUM_SMS * 16;

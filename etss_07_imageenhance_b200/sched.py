@@ -81,6 +81,7 @@ class FramePipeline:
         if self.device.type != "cuda":
             raise RuntimeError("FramePipeline needs the model on a CUDA device (no CPU fallback)")
         self.return_adjust = return_adjust
+        self.prec = self.sf = 0
         L = lib()
         F = self.F
         if isinstance(model, M.ZeroDCEpp_RE):
