@@ -286,14 +286,13 @@ dcepp_apply_vec4_kernel(const float* __restrict__ x, const float* __restrict__ a
                 a.y = tx[1].w0 * vr[tx[1].i0] + tx[1].w1 * vr[tx[1].i1];
                 a.z = tx[2].w0 * vr[tx[2].i0] + tx[2].w1 * vr[tx[2].i1];
                 a.w = tx[3].w0 * vr[tx[3].i0] + tx[3].w1 * vr[tx[3].i1];
-                float4 y = v[c];
+                float2 y0 = make_float2(v[c].x, v[c].y), y1 = make_float2(v[c].z, v[c].w);
+                const float2 na0 = make_float2(-a.x, -a.y), na1 = make_float2(-a.z, -a.w);
                 for (int i = 0; i < iters; ++i) {
-                    y.x = curve_step(y.x, a.x);
-                    y.y = curve_step(y.y, a.y);
-                    y.z = curve_step(y.z, a.z);
-                    y.w = curve_step(y.w, a.w);
+                    y0 = curve_step2(y0, na0);
+                    y1 = curve_step2(y1, na1);
                 }
-                st_stream4(enh + base + c * plane, y);
+                st_stream4(enh + base + c * plane, make_float4(y0.x, y0.y, y1.x, y1.y));
                 if (WRITE_ADJ) st_stream4(adj + base + c * plane, a);
             }
         }
