@@ -11,6 +11,9 @@ namespace b200 {
 
 __host__ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+int curve_per_iter_unaligned_ok(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters,
+                                cudaStream_t s);  // curve.cu
+
 __host__ inline int launch_status() {
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? B200_OK : B200_ERR_LAUNCH;

@@ -79,11 +79,13 @@ __global__ void __launch_bounds__(256) curve_scalar_kernel(const float* __restri
 }
 
 template <bool PER_ITER>
-static int launch_curve(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream) {
+static int launch_curve(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream,
+                        bool strict = true) {
     if (!x || !a || !y) return B200_ERR_NULL;
     if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || iters < 0) return B200_ERR_BAD_SHAPE;
-    // float alignment is required; 16-byte alignment only selects the vector kernel (frame sub-batches of a
-    // ragged shape start at 4-byte-aligned offsets)
+    // the public ABI requires 16-byte aligned bases; internal callers (frame sub-batches of a ragged shape start
+    // at 4-byte-aligned offsets) pass strict=false and fall back to the scalar kernel
+    if (strict && (!aligned16(x) || !aligned16(a) || !aligned16(y))) return B200_ERR_MISALIGNED;
     if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(y)) & 3u)
         return B200_ERR_MISALIGNED;
     cudaStream_t s = (cudaStream_t)stream;
@@ -163,6 +165,12 @@ __global__ void __launch_bounds__(256) f32nchw_to_u8hwc_kernel(const float* __re
         d[1] = w1;
         d[2] = w2;
     }
+}
+
+// internal entry for sub-batch pointers that are only float-aligned (dce.cu)
+int curve_per_iter_unaligned_ok(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters,
+                                cudaStream_t s) {
+    return launch_curve<true>(x, a, y, B, C, H, W, iters, (void*)s, false);
 }
 
 }  // namespace b200

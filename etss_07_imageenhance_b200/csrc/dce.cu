@@ -188,7 +188,7 @@ static int dce_forward_f32(const float* x, const float* packed, float* adjust, f
         if ((rc = launch_conv_f32(x3, 32, x4, 32, x5, packed + dce_f32_layer_offset(4), 32, false, nb, H, W, s))) return rc;
         if ((rc = launch_conv_f32(x2, 32, x5, 32, x6, packed + dce_f32_layer_offset(5), 32, false, nb, H, W, s))) return rc;
         if ((rc = launch_conv_f32(x1, 32, x6, 32, ab, packed + dce_f32_layer_offset(6), cout7, true, nb, H, W, s))) return rc;
-        if ((rc = b200_curve_per_iter(xb, ab, enhanced + (size_t)b0 * 3 * plane, nb, 3, H, W, iters, (void*)s))) return rc;
+        if ((rc = curve_per_iter_unaligned_ok(xb, ab, enhanced + (size_t)b0 * 3 * plane, nb, 3, H, W, iters, s))) return rc;
     }
     return B200_OK;
 }

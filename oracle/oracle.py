@@ -178,6 +178,26 @@ def zero_dce_forward(x: torch.Tensor, sd: dict, num_iters: int = 8) -> dict:
 
 
 @torch.no_grad()
+def zero_dce_forward_bf16_operands(x: torch.Tensor, sd: dict, num_iters: int = 8) -> dict:
+    """`zero_dce_forward` with the OPERAND rounding of the tensor-core mode: every conv input and every
+    weight is rounded to bf16 (round-to-nearest-even), products/accumulation/bias/activation stay fp32.
+    Not a reference path — a test helper that separates layout/indexing bugs (large errors against this)
+    from the expected bf16 quantisation noise (the PSNR contract is checked against `zero_dce_forward`)."""
+    r = lambda t: t.to(torch.bfloat16).to(torch.float32)  # noqa: E731
+
+    def conv(t, i):
+        return F.conv2d(r(t), r(sd[f"e_conv{i}.weight"]), sd[f"e_conv{i}.bias"], stride=1, padding=1)
+    x1 = F.relu(conv(x, 1))
+    x2 = F.relu(conv(x1, 2))
+    x3 = F.relu(conv(x2, 3))
+    x4 = F.relu(conv(x3, 4))
+    x5 = F.relu(conv(torch.cat([x3, x4], 1), 5))
+    x6 = F.relu(conv(torch.cat([x2, x5], 1), 6))
+    x_r = torch.tanh(conv(torch.cat([x1, x6], 1), 7))
+    return {"adjust": x_r, "enhanced": curve_per_iter(x, x_r, num_iters)}
+
+
+@torch.no_grad()
 def zero_dcepp_lowres_net(x_down: torch.Tensor, sd: dict) -> torch.Tensor:
     """The 7 depthwise-separable layers + tanh (zero_dcepp.py:190-196)."""
     def ds(t, i):

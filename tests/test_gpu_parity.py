@@ -183,6 +183,60 @@ def test_dce_fp32_zero_weights_identity_1080p(cuda_dev):
     assert torch.equal(out["enhanced"], x) and not out["adjust"].any()
 
 
+# ------------------------------------------------------------------ Zero-DCE (bf16 tensor-core mode, tcgen05)
+# Contract (BASELINE.json north_star): PSNR >= 50 dB on `enhanced` against the reference's fp32 output.
+# Indexing/layout check: against the oracle with bf16-rounded operands the error must be accumulation-order +
+# tanh.approx noise only.
+BF16_EMU_TOL = 1.5e-2
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_dce_bf16_golden(cuda_dev, golden, regime):
+    x, sd, outs = golden(f"dce_{regime}")
+    m = load_into(P.MODELS.build(config={"name": "zero_dce_re", "precision": "bf16"}), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    assert list(out.keys()) == [f"adjust_{i}" for i in range(8)] + ["adjust", "enhanced"]
+    emu = O.zero_dce_forward_bf16_operands(x, sd)
+    ea, ee = maxerr(out["adjust"], emu["adjust"]), maxerr(out["enhanced"], emu["enhanced"])
+    p = O.psnr(out["enhanced"].cpu(), outs["enhanced"])
+    print(f"bf16 {regime}: max|adjust - emu|={ea:.3e} max|enh - emu|={ee:.3e} PSNR vs fp32 reference={p:.1f} dB")
+    assert ea <= BF16_EMU_TOL and ee <= BF16_EMU_TOL, (ea, ee)
+    assert p >= 50.0, p
+
+
+@pytest.mark.parametrize("H,W,B,iters", [(37, 45, 3, 8), (8, 32, 1, 8), (1, 1, 1, 8), (19, 70, 2, 3), (64, 64, 5, 1),
+                                         (90, 260, 2, 8), (130, 300, 1, 8), (41, 128, 1, 8), (40, 129, 1, 8)])
+def test_dce_bf16_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
+    x = O.synthetic_lowlight(B, H, W, seed=70 + iters)
+    sd = O.make_dce_state_dict(23, "stress", num_iters=iters)
+    m = load_into(P.ZeroDCE_RE(num_iters=iters, precision="bf16"), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    emu = O.zero_dce_forward_bf16_operands(x, sd, num_iters=iters)
+    ref = O.zero_dce_forward(x, sd, num_iters=iters)
+    assert out["adjust"].shape == (B, 3 * iters, H, W)
+    assert maxerr(out["adjust"], emu["adjust"]) <= BF16_EMU_TOL
+    assert maxerr(out["enhanced"], emu["enhanced"]) <= BF16_EMU_TOL
+    assert O.psnr(out["enhanced"].cpu(), ref["enhanced"]) >= 45.0
+
+
+def test_dce_bf16_zero_weights_identity_1080p(cuda_dev):
+    sd = {k: torch.zeros_like(v) for k, v in O.make_dce_state_dict(1).items()}
+    m = load_into(P.ZeroDCE_RE(precision="bf16"), sd).to(cuda_dev)
+    x = O.synthetic_lowlight(1, 1080, 1920, seed=8).to(cuda_dev)
+    out = m({"image": x})
+    assert torch.equal(out["enhanced"], x) and not out["adjust"].any()
+
+
+def test_dce_bf16_matches_fp32_mode_1080p(cuda_dev):
+    # full BASELINE frame size: the two precision modes of the SAME weights agree to bf16 noise
+    sd = O.make_dce_state_dict(5, "init")
+    x = O.synthetic_lowlight(2, 1080, 1920, seed=9).to(cuda_dev)
+    a = load_into(P.ZeroDCE_RE(precision="fp32"), sd).to(cuda_dev)({"image": x})
+    b = load_into(P.ZeroDCE_RE(precision="bf16"), sd).to(cuda_dev)({"image": x})
+    assert O.psnr(b["enhanced"].cpu(), a["enhanced"].cpu()) >= 50.0
+    assert maxerr(b["adjust"], a["adjust"]) <= 2e-2
+
+
 # ------------------------------------------------------------------ SCI
 @pytest.mark.parametrize("regime", ["init", "stress"])
 def test_sci_golden(cuda_dev, golden, regime):
