@@ -28,13 +28,17 @@ using namespace tc;
 constexpr int TC_M = 128;        // pixels per strip = MMA M = TMEM lanes
 constexpr int TC_N = 32;         // output channels (24 padded to 32 in layer 7)
 constexpr int TC_NSLOT = 4;      // TMEM ring slots (input rows)
-constexpr int TC_NSTAGE = 4;     // smem staging buffers (input rows)
-constexpr int TC_PF = 2;         // cp.async prefetch distance (rows)
+constexpr int TC_NSTAGE = 8;     // smem staging buffers (input rows)
+constexpr int TC_PF = 6;         // cp.async prefetch distance (rows); NSTAGE >= PF + 2
+constexpr int TC_NSTAGE1 = 12;   // layer 1: staged fp32 input rows, each feeds 3 output rows; NSTAGE1 >= PF1 + 4
+constexpr int TC_PF1 = 8;
+constexpr int TC_ROW1 = 3 * 132; // layer 1: floats per staged row ([3 channels][132])
+constexpr int TC_NACC = 4;       // accumulator buffers
 constexpr int TC_PXP = 80;       // staging pixel pitch in bytes (64 B of channels + 16 B pad)
 constexpr int TC_SPX = TC_M + 2; // staged pixels per row (halo of 1 on each side)
 constexpr int TC_TILE = 1024;    // bytes of one B tile (N=32 x K=16 bf16)
 constexpr int TC_THREADS = 288;
-constexpr int TC_ACC_COLS = 64;  // 2 accumulator buffers x 32 columns
+constexpr int TC_ACC_COLS = 128; // 4 accumulator buffers x 32 columns
 
 __host__ __device__ constexpr int tc_ntap(int l) { return l == 0 ? 1 : 9; }
 __host__ __device__ constexpr int tc_kc(int l) { return l == 0 ? 2 : (l <= 3 ? 2 : 4); }
@@ -104,7 +108,7 @@ struct TcArgs {
 template <int NSRC, bool FIRST>
 constexpr int tc_smem_bytes() {
     return (FIRST ? 2 : 9 * 2 * NSRC) * TC_TILE + 128 + 128 + 16 +
-           (FIRST ? 0 : TC_NSTAGE * NSRC * TC_SPX * TC_PXP);
+           (FIRST ? TC_NSTAGE1 * TC_ROW1 * 4 : TC_NSTAGE * NSRC * TC_SPX * TC_PXP);
 }
 
 template <int NSRC, bool FIRST, bool LAST>
@@ -124,8 +128,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(smem + WBYTES + 128);
     uint64_t* full = s_bar;                   // [NSLOT]  loader -> MMA      (128 arrivals)
     uint64_t* empty = s_bar + TC_NSLOT;       // [NSLOT]  MMA commit -> loader (1 arrival)
-    uint64_t* acc_full = s_bar + 2 * TC_NSLOT;      // [2] MMA commit -> epilogue (1)
-    uint64_t* acc_empty = s_bar + 2 * TC_NSLOT + 2;  // [2] epilogue -> MMA (128)
+    uint64_t* acc_full = s_bar + 2 * TC_NSLOT;              // [NACC] MMA commit -> epilogue (1)
+    uint64_t* acc_empty = s_bar + 2 * TC_NSLOT + TC_NACC;   // [NACC] epilogue -> MMA (128)
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + WBYTES + 256);
     uint8_t* s_stage = smem + WBYTES + 256 + 16;
 
@@ -146,7 +150,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
                 mbar_init(&full[i], 128);
                 mbar_init(&empty[i], 1);
             }
-            for (int i = 0; i < 2; ++i) {
+            for (int i = 0; i < TC_NACC; ++i) {
                 mbar_init(&acc_full[i], 1);
                 mbar_init(&acc_empty[i], 128);
             }
@@ -173,18 +177,41 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
             const int nout = min(R, H - y0);
             const int nrows = nout + ROWS - 1;
             if constexpr (FIRST) {
+                // layer 1: fp32 NCHW input rows staged once ([3][132] floats per row), each feeds 3 output rows;
+                // the im2col row (27 taps x channels, padded to K = 32) is gathered from shared memory.
                 const float* xin = reinterpret_cast<const float*>(args.src0) + (size_t)b * 3 * H * W;
-                const int xx = x0 + t;
-                for (int r = 0; r < nrows; ++r) {
-                    const int y = y0 + r;
+                float* stg = reinterpret_cast<float*>(s_stage);
+                const int nin = nout + 2;
+                auto issue_row1 = [&](int y, uint32_t stage) {
+                    const bool yok = y >= 0 && y < H;
+                    const uint32_t sdst = smem_u32(stg) + stage * (TC_ROW1 * 4);
+                    for (int i = t; i < 3 * TC_SPX; i += 128) {
+                        const int c = i / TC_SPX, px = i - c * TC_SPX;
+                        const int xs = x0 - 1 + px;
+                        const bool ok = yok && xs >= 0 && xs < W;
+                        const float* gp = xin + (ok ? ((size_t)c * H + y) * W + xs : (size_t)0);
+                        cp_async4(sdst + (c * 132 + px) * 4, gp, ok);
+                    }
+                };
+#pragma unroll
+                for (int k = 0; k < TC_PF1; ++k) {
+                    if (k < nin) issue_row1(y0 - 1 + k, (g + k) % TC_NSTAGE1);
+                    cp_async_commit();
+                }
+                for (int ri = 0; ri < nin; ++ri) {
+                    if (ri + TC_PF1 < nin) issue_row1(y0 - 1 + ri + TC_PF1, (g + ri + TC_PF1) % TC_NSTAGE1);
+                    cp_async_commit();
+                    cp_async_wait<TC_PF1>();
+                    named_bar_sync(1, 128);
+                    if (ri < 2) continue;
                     float v[28];
 #pragma unroll
-                    for (int tp = 0; tp < 9; ++tp) {
-                        const int yy = y + tp / 3 - 1, xs = xx + tp % 3 - 1;
-                        const bool ok = yy >= 0 && yy < H && xs >= 0 && xs < W;
+                    for (int ky = 0; ky < 3; ++ky) {
+                        const float* sp = stg + ((g + ri - 2 + ky) % TC_NSTAGE1) * TC_ROW1 + t;
 #pragma unroll
-                        for (int c = 0; c < 3; ++c)
-                            v[tp * 3 + c] = ok ? __ldg(xin + ((size_t)c * H + yy) * W + xs) : 0.f;
+                        for (int kx = 0; kx < 3; ++kx)
+#pragma unroll
+                            for (int c = 0; c < 3; ++c) v[(ky * 3 + kx) * 3 + c] = sp[c * 132 + kx];
                     }
                     v[27] = 0.f;
                     uint32_t pk[16];
@@ -203,6 +230,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
                     mbar_arrive(&full[slot]);
                     ++fill;
                 }
+                g += nin;
             } else {
                 const uint8_t* srcs[2] = {reinterpret_cast<const uint8_t*>(args.src0),
                                           reinterpret_cast<const uint8_t*>(args.src1)};
@@ -273,8 +301,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
                         const uint32_t f = f0 + j + ROWS - 1;
                         mbar_wait(&full[f % TC_NSLOT], (f / TC_NSLOT) & 1);
                     }
-                    const uint32_t buf = o & 1;
-                    if (o >= 2) mbar_wait(&acc_empty[buf], ((o >> 1) - 1) & 1);
+                    const uint32_t buf = o % TC_NACC;
+                    if (o >= TC_NACC) mbar_wait(&acc_empty[buf], ((o / TC_NACC) - 1) & 1);
                     tc_fence_after();
                     const uint32_t d = tbase + buf * TC_N;
 #pragma unroll
@@ -316,8 +344,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
             const int y0 = seg * R, xx = strip * TC_M + m;
             const int nout = min(R, H - y0);
             for (int j = 0; j < nout; ++j) {
-                const uint32_t buf = o & 1;
-                mbar_wait(&acc_full[buf], (o >> 1) & 1);
+                const uint32_t buf = o % TC_NACC;
+                mbar_wait(&acc_full[buf], (o / TC_NACC) & 1);
                 tc_fence_after();
                 uint32_t v[32];
                 tmem_ld32(tlane + buf * TC_N, v);
