@@ -1,21 +1,29 @@
 // Zero-DCE conv stack (ZeroDCE_RE.forward, zero_dce.py:173-191) on the sm_100a tensor cores.
 //
-// One launch per layer.  Per layer the 3x3 convolution is an implicit GEMM
-//     D[M = 128 pixels of one image row, N = 32] += A_tap[M, K = Cin] * W_tap[K, N]      (9 taps)
-// issued as tcgen05.mma.cta_group::1.kind::f16 (bf16 x bf16 -> fp32 in TMEM), M=128 N=32 K=16, in **TS mode**:
-// the activation operand A lives in TMEM (lane = pixel, one 32-bit column = two bf16 channels), only the 1 KB
-// weight tile B comes from shared memory.  With N = 32 an SS-mode MMA would need 256 B/clk of shared-memory reads
-// for A — twice what the SM has — so the A rows are staged once per input row instead:
-//     global NHWC bf16 --cp.async--> smem (80 B pixel pitch, bank-conflict-free) --LDS.128--> registers
-//       --tcgen05.st--> three lane-shifted copies (dx = -1, 0, +1) in a 4-slot TMEM ring of input rows.
-// dy shifts are ring slots, so rows stream top to bottom with no recompute inside a strip.
+// One launch per layer.  Per layer the 3x3 convolution is an implicit GEMM in "input-row-stationary" form:
+// an input row r (128 pixels of one strip, all Cin channels) contributes to the three output rows r+1, r, r-1
+// through the filter rows dy = 0, 1, 2, so for every (dx, 16-channel chunk) ONE
+//     tcgen05.mma.cta_group::1.kind::f16   M = 128 pixels, N = 96 = 3 output rows x 32 couts, K = 16
+// accumulates into three ADJACENT 32-column fp32 accumulator blocks of a TMEM ring (bf16 x bf16 -> fp32).
+// The MMA runs in **TS mode**: the activation operand A lives in TMEM (lane = pixel, one 32-bit column = two
+// bf16 channels); only the 3 KB weight tile B is read from shared memory.  With N this small an SS-mode MMA would
+// need more shared-memory bandwidth for A than an SM has.  A 3x3 tap's dx shift cannot be a TMEM lane shift, so the
+// loader warps write three lane-shifted copies (dx = -1, 0, +1) of each input row:
+//     global NHWC bf16 --TMA (4-D tile, 64B swizzle, zero fill outside the image)--> smem ring
+//       --LDS.128 (conflict-free through the swizzle)--> registers --tcgen05.st--> TMEM A slot (3 copies).
+// Rows stream top to bottom inside a strip: no halo recompute in y, one input row lives in TMEM for one MMA batch.
+// An accumulator block is complete after the input row below it has been consumed; the epilogue drains it,
+// re-zeroes it (every MMA accumulates) and hands it back.
 //
-// Warp roles (288 threads, 1 persistent CTA per SM, all 512 TMEM columns):
-//   warps 0-3  loader: stage + fill TMEM ring slot, arrive on full[slot]
-//   warp  4    lane 0 issues the 9 * Cin/16 MMAs per output row, tcgen05.commit -> acc_full[buf], empty[slot]
-//   warps 5-8  epilogue: tcgen05.ld accumulator row -> bias + ReLU -> bf16 NHWC store; layer 7: tanh -> `adjust`
-//              (NCHW fp32) and the 8-iteration curve on x -> `enhanced`   (zero_dce.py:182-188)
-// Layer 1 (Cin = 3) uses the same pipeline with an im2col loader: K = 27 (pad 32), one "tap", 2 MMAs per row.
+// Warp roles (576 threads, 1 persistent CTA per SM, 512 TMEM columns):
+//   warps 0-7    loaders, two per TMEM lane quarter, alternating input rows
+//   warp  8      lane 0 issues the MMAs, tcgen05.commit -> empty[slot], acc_full[block]
+//   warp  9      lane 0 is the TMA producer (expect_tx + cp.async.bulk.tensor per input row and source)
+//   warps 10-17  epilogue, two per lane quarter, alternating output rows: tcgen05.ld -> bias + ReLU -> bf16 NHWC
+//                store; layer 7: tanh -> `adjust` (NCHW fp32) + the 8-iteration curve on x -> `enhanced`
+// Layer 1 (Cin = 3) uses the same pipeline with an im2col loader (K = 27 padded to 32, N = 32, 2 MMAs per row);
+// its fp32 NCHW input rows are staged with cp.async.
+#include <cuda.h>
 #include <cuda_bf16.h>
 
 #include "common.cuh"
@@ -25,25 +33,28 @@
 namespace b200 {
 using namespace tc;
 
-constexpr int TC_M = 128;        // pixels per strip = MMA M = TMEM lanes
-constexpr int TC_N = 32;         // output channels (24 padded to 32 in layer 7)
-constexpr int TC_NSLOT = 4;      // TMEM ring slots (input rows)
-constexpr int TC_NSTAGE = 8;     // smem staging buffers (input rows)
-constexpr int TC_PF = 6;         // cp.async prefetch distance (rows); NSTAGE >= PF + 2
-constexpr int TC_NSTAGE1 = 12;   // layer 1: staged fp32 input rows, each feeds 3 output rows; NSTAGE1 >= PF1 + 4
+constexpr int TC_M = 128;            // pixels per strip = MMA M = TMEM lanes
+constexpr int TC_NSLOT = 3;          // TMEM A slots (input rows)
+constexpr int TC_NB = 6;             // accumulator blocks (32 columns each) in the TMEM ring; even
+constexpr int TC_ACC_COLS = TC_NB * 32;
+constexpr int TC_NST = 8;            // TMA smem stages (input rows); even
+constexpr int TC_SPX = TC_M + 2;     // staged pixels per row (halo of 1 on each side)
+constexpr int TC_SRC_BYTES = TC_SPX * 64;          // TMA box bytes per source per row (8320)
+constexpr int TC_SRC_STRIDE = 8704;                // smem bytes per source per stage (17 x 512: keeps the swizzle phase)
+constexpr int TC_NSTAGE1 = 12;       // layer 1: staged fp32 input rows; NSTAGE1 >= PF1 + 4
 constexpr int TC_PF1 = 8;
-constexpr int TC_ROW1 = 3 * 132; // layer 1: floats per staged row ([3 channels][132])
-constexpr int TC_NACC = 4;       // accumulator buffers
-constexpr int TC_PXP = 80;       // staging pixel pitch in bytes (64 B of channels + 16 B pad)
-constexpr int TC_SPX = TC_M + 2; // staged pixels per row (halo of 1 on each side)
-constexpr int TC_TILE = 1024;    // bytes of one B tile (N=32 x K=16 bf16)
-constexpr int TC_THREADS = 288;
-constexpr int TC_ACC_COLS = 128; // 4 accumulator buffers x 32 columns
+constexpr int TC_ROW1 = 3 * 132;     // layer 1: floats per staged row ([3 channels][132])
+constexpr int TC_THREADS = 576;
+static_assert((2 * TC_NST + 2 * TC_NSLOT + 2 * TC_NB) * 8 <= 384, "mbarrier area");
 
-__host__ __device__ constexpr int tc_ntap(int l) { return l == 0 ? 1 : 9; }
+// packed weights per layer: B tiles then 32 fp32 biases.
+//   layer 0   : 2 tiles [N=32][K=16] (1 KB each), k = (ky*3+kx)*3 + c
+//   layers 1-6: per (dx, kc) one tile [N=96 = dy*32 + cout][K=16] (3 KB)
+// element (n, kk) of a tile at byte (n/8)*256 + (kk/8)*128 + (n%8)*16 + (kk%8)*2   (K-major core matrices,
+// LBO = 128, SBO = 256)
 __host__ __device__ constexpr int tc_kc(int l) { return l == 0 ? 2 : (l <= 3 ? 2 : 4); }
-__host__ __device__ constexpr int tc_wbytes(int l) { return tc_ntap(l) * tc_kc(l) * TC_TILE; }
-__host__ __device__ constexpr int tc_layer_bytes(int l) { return tc_wbytes(l) + 128; }  // + 32 fp32 biases
+__host__ __device__ constexpr int tc_wbytes(int l) { return l == 0 ? 2 * 1024 : 3 * tc_kc(l) * 3072; }
+__host__ __device__ constexpr int tc_layer_bytes(int l) { return tc_wbytes(l) + 128; }
 __host__ __device__ constexpr int tc_layer_offset(int l) {
     int o = 0;
     for (int i = 0; i < l; ++i) o += tc_layer_bytes(i);
@@ -51,10 +62,6 @@ __host__ __device__ constexpr int tc_layer_offset(int l) {
 }
 constexpr int TC_PACKED_BYTES = tc_layer_offset(7);
 
-// ------------------------------------------------------------------------------------------------
-// weight packing: OIHW fp32 -> per (tap, k-chunk) UMMA K-major core-matrix tiles, bf16
-//   element (n, kk) of a tile at byte (n/8)*256 + (kk/8)*128 + (n%8)*16 + (kk%8)*2      (LBO = 128, SBO = 256)
-// ------------------------------------------------------------------------------------------------
 struct TcPackArgs {
     const float* w[7];
     const float* b[7];
@@ -62,32 +69,34 @@ struct TcPackArgs {
 
 __global__ void dce_tc_pack_kernel(TcPackArgs a, uint8_t* __restrict__ packed, int cout_last) {
     const int l = blockIdx.x;
-    const int ntap = tc_ntap(l), kc_n = tc_kc(l);
+    const int kc_n = tc_kc(l);
     const int cin = l == 0 ? 3 : (l <= 3 ? 32 : 64);
     const int cout = l == 6 ? cout_last : 32;
     uint8_t* base = packed + tc_layer_offset(l);
     __nv_bfloat16* tiles = reinterpret_cast<__nv_bfloat16*>(base);
-    const int n_el = ntap * kc_n * 512;
-    for (int i = threadIdx.x; i < n_el; i += blockDim.x) {
-        const int tile = i >> 9, e = i & 511;
-        const int tap = tile / kc_n, kc = tile - tap * kc_n;
-        // e enumerates (n, kk) row-major: n = e / 16, kk = e % 16
-        const int n = e >> 4, kk = e & 15;
-        float v = 0.f;
-        if (n < cout) {
-            if (l == 0) {
-                const int k = kc * 16 + kk;  // k = (ky*3+kx)*3 + c
-                if (k < 27) {
-                    const int tp = k / 3, c = k - tp * 3;
-                    v = a.w[0][(n * 3 + c) * 9 + tp];
-                }
-            } else {
-                const int ci = kc * 16 + kk;
-                v = a.w[l][(n * cin + ci) * 9 + tap];
+    if (l == 0) {
+        for (int i = threadIdx.x; i < 2 * 512; i += blockDim.x) {
+            const int kc = i >> 9, e = i & 511;
+            const int n = e >> 4, kk = e & 15;
+            const int k = kc * 16 + kk;
+            float v = 0.f;
+            if (k < 27) {
+                const int tp = k / 3, c = k - tp * 3;
+                v = a.w[0][(n * 3 + c) * 9 + tp];
             }
+            tiles[kc * 512 + (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7)] = __float2bfloat16_rn(v);
         }
-        const int off = (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7);  // in bf16 elements
-        tiles[tile * 512 + off] = __float2bfloat16_rn(v);
+    } else {
+        const int n_el = 3 * kc_n * 1536;
+        for (int i = threadIdx.x; i < n_el; i += blockDim.x) {
+            const int tile = i / 1536, e = i - tile * 1536;
+            const int dx = tile / kc_n, kc = tile - dx * kc_n;
+            const int n = e >> 4, kk = e & 15;  // n = dy*32 + cout
+            const int dy = n >> 5, oc = n & 31;
+            const int ci = kc * 16 + kk;
+            const float v = oc < cout ? a.w[l][(oc * cin + ci) * 9 + dy * 3 + dx] : 0.f;
+            tiles[tile * 1536 + (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7)] = __float2bfloat16_rn(v);
+        }
     }
     float* bias = reinterpret_cast<float*>(base + tc_wbytes(l));
     for (int i = threadIdx.x; i < 32; i += blockDim.x) bias[i] = i < cout ? a.b[l][i] : 0.f;
@@ -95,62 +104,76 @@ __global__ void dce_tc_pack_kernel(TcPackArgs a, uint8_t* __restrict__ packed, i
 
 // ------------------------------------------------------------------------------------------------
 struct TcArgs {
-    const void* src0;       // NHWC bf16 [B,H,W,32]   (FIRST: x, NCHW fp32)
-    const void* src1;       // second concat source or nullptr
-    __nv_bfloat16* dst;     // NHWC bf16 [B,H,W,32]   (!LAST)
-    const float* x;         // LAST: network input (NCHW fp32) for the curve
-    float* adjust;          // LAST: [B,3*iters,H,W] or nullptr
-    float* enhanced;        // LAST: [B,3,H,W]
-    const uint8_t* wpack;   // this layer's packed block
+    const float* x;        // network input, NCHW fp32 (layer 1 source; layer 7 curve input)
+    __nv_bfloat16* dst;    // NHWC bf16 [B,H,W,32]   (!LAST)
+    float* adjust;         // LAST: [B,3*iters,H,W] or nullptr
+    float* enhanced;       // LAST: [B,3,H,W]
+    const uint8_t* wpack;  // this layer's packed block
     int B, H, W, R, nseg, nstrip, iters;
 };
 
 template <int NSRC, bool FIRST>
+__host__ __device__ constexpr int tc_wbytes_t() {
+    return FIRST ? 2 * 1024 : 3 * 2 * NSRC * 3072;
+}
+template <int NSRC, bool FIRST>
 constexpr int tc_smem_bytes() {
-    return (FIRST ? 2 : 9 * 2 * NSRC) * TC_TILE + 128 + 128 + 16 +
-           (FIRST ? TC_NSTAGE1 * TC_ROW1 * 4 : TC_NSTAGE * NSRC * TC_SPX * TC_PXP);
+    // weights | bias 128 | barriers 384 | tmem addr 16 | pad to 1024 | stages
+    return tc_wbytes_t<NSRC, FIRST>() + 128 + 384 + 16 + 1024 +
+           (FIRST ? TC_NSTAGE1 * TC_ROW1 * 4 : TC_NST * NSRC * TC_SRC_STRIDE);
 }
 
+__device__ __forceinline__ int tc_pos(uint32_t o) { return TC_NB - 1 - (int)(o % TC_NB); }
+
 template <int NSRC, bool FIRST, bool LAST>
-__global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArgs args) {
-    constexpr int KC = FIRST ? 2 : 2 * NSRC;        // K chunks of 16 per tap
-    constexpr int NTAP = FIRST ? 1 : 9;
-    constexpr int WBYTES = NTAP * KC * TC_TILE;
-    constexpr int COPY_COLS = FIRST ? 16 : 16 * NSRC;  // TMEM columns of one dx copy
-    constexpr int SLOT_COLS = FIRST ? 16 : 3 * COPY_COLS;
-    constexpr int ROWS = FIRST ? 1 : 3;             // input rows per output row
-    constexpr int SRC_STAGE = TC_SPX * TC_PXP;      // bytes per source per staged row
+__global__ void __launch_bounds__(TC_THREADS, 1)
+dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1) {
+    constexpr int KC = FIRST ? 2 : 2 * NSRC;            // K chunks of 16 per (dy, dx)
+    constexpr int NDY = FIRST ? 1 : 3;                  // output rows one input row feeds
+    constexpr int NDX = FIRST ? 1 : 3;
+    constexpr int WBYTES = tc_wbytes_t<NSRC, FIRST>();
+    constexpr int TILE = FIRST ? 1024 : 3072;
+    constexpr int COPY_COLS = FIRST ? 16 : 16 * NSRC;   // TMEM columns of one dx copy
+    constexpr int SLOT_COLS = NDX * COPY_COLS;
     static_assert(TC_ACC_COLS + TC_NSLOT * SLOT_COLS <= 512, "TMEM budget");
 
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* s_w = smem;
-    float* s_bias = reinterpret_cast<float*>(smem + WBYTES);
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(smem + WBYTES + 128);
-    uint64_t* full = s_bar;                   // [NSLOT]  loader -> MMA      (128 arrivals)
-    uint64_t* empty = s_bar + TC_NSLOT;       // [NSLOT]  MMA commit -> loader (1 arrival)
-    uint64_t* acc_full = s_bar + 2 * TC_NSLOT;              // [NACC] MMA commit -> epilogue (1)
-    uint64_t* acc_empty = s_bar + 2 * TC_NSLOT + TC_NACC;   // [NACC] epilogue -> MMA (128)
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + WBYTES + 256);
-    uint8_t* s_stage = smem + WBYTES + 256 + 16;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* s_w = smem_raw;
+    float* s_bias = reinterpret_cast<float*>(smem_raw + WBYTES);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(smem_raw + WBYTES + 128);
+    uint64_t* stage_full = s_bar;                                   // [NST]   TMA complete_tx (1 arrival + bytes)
+    uint64_t* stage_empty = s_bar + TC_NST;                         // [NST]   loaders of one parity (128)
+    uint64_t* full = s_bar + 2 * TC_NST;                            // [NSLOT] loaders of one parity (128)
+    uint64_t* empty = s_bar + 2 * TC_NST + TC_NSLOT;                // [NSLOT] MMA commit (1)
+    uint64_t* acc_full = s_bar + 2 * TC_NST + 2 * TC_NSLOT;         // [NB]    MMA commit (1)
+    uint64_t* acc_empty = s_bar + 2 * TC_NST + 2 * TC_NSLOT + TC_NB;  // [NB]  epilogue warps of one parity (128)
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + WBYTES + 128 + 384);
+    // stage area: 1024-byte aligned in the shared window (swizzle phase = address bits 7-8)
+    const uint32_t stage_u32 = (smem_u32(smem_raw + WBYTES + 128 + 384 + 16) + 1023u) & ~1023u;
+    uint8_t* s_stage = smem_raw + (stage_u32 - smem_u32(smem_raw));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int B = args.B, H = args.H, W = args.W, R = args.R;
-    const int n_items = B * args.nseg * args.nstrip;
+    const int H = args.H, W = args.W, R = args.R;
+    const int n_items = args.B * args.nseg * args.nstrip;
 
     // ---- one-time setup ----
     {
         const uint4* g = reinterpret_cast<const uint4*>(args.wpack);
-        uint4* s = reinterpret_cast<uint4*>(smem);
+        uint4* s = reinterpret_cast<uint4*>(smem_raw);
         for (int i = tid; i < (WBYTES + 128) / 16; i += TC_THREADS) s[i] = __ldg(g + i);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // weights are read by the tensor core (async proxy)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // B tiles are read through the async proxy
     }
-    if (warp == 4) {
+    if (warp == 8) {
         if (lane == 0) {
+            for (int i = 0; i < TC_NST; ++i) {
+                mbar_init(&stage_full[i], 1);
+                mbar_init(&stage_empty[i], 128);
+            }
             for (int i = 0; i < TC_NSLOT; ++i) {
                 mbar_init(&full[i], 128);
                 mbar_init(&empty[i], 1);
             }
-            for (int i = 0; i < TC_NACC; ++i) {
+            for (int i = 0; i < TC_NB; ++i) {
                 mbar_init(&acc_full[i], 1);
                 mbar_init(&acc_empty[i], 128);
             }
@@ -159,33 +182,47 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
         __syncwarp();
         tmem_alloc(s_tmem, 512);
     }
+    if (!FIRST && warp == 9 && lane == 0) {
+        tma_prefetch_desc(&tm0);
+        if (NSRC == 2) tma_prefetch_desc(&tm1);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tbase = *s_tmem;
+    if (warp >= 10 && warp < 14) {  // every MMA accumulates: start from zeroed accumulator blocks
+        const uint32_t tl = tbase + ((uint32_t)((warp & 3) * 32) << 16);
+        for (int i = 0; i < TC_NB; ++i) tmem_zero32(tl + i * 32);
+        tc_wait_st();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
 
-    if (warp < 4) {
-        // =========================== LOADER ===========================
-        const int t = tid;  // 0..127 = pixel in strip = TMEM lane
-        const uint32_t tlane = tbase + ((uint32_t)(warp * 32) << 16);
-        uint32_t fill = 0, g = 0;
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int strip = item % args.nstrip;
-            const int seg = (item / args.nstrip) % args.nseg;
-            const int b = item / (args.nstrip * args.nseg);
-            const int y0 = seg * R, x0 = strip * TC_M;
-            const int nout = min(R, H - y0);
-            const int nrows = nout + ROWS - 1;
-            if constexpr (FIRST) {
-                // layer 1: fp32 NCHW input rows staged once ([3][132] floats per row), each feeds 3 output rows;
-                // the im2col row (27 taps x channels, padded to K = 32) is gathered from shared memory.
-                const float* xin = reinterpret_cast<const float*>(args.src0) + (size_t)b * 3 * H * W;
-                float* stg = reinterpret_cast<float*>(s_stage);
+    if (warp < 8) {
+        // =========================== LOADERS ===========================
+        const int q = warp & 3, par = warp >> 2;
+        const int t = q * 32 + lane;  // pixel in strip = TMEM lane
+        const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16) + TC_ACC_COLS;
+        uint32_t g_base = 0;
+        if constexpr (FIRST) {
+            // fp32 NCHW input rows staged once ([3][132] floats per row) by all 256 loader threads; each staged row
+            // feeds 3 output rows; the im2col row (27 = taps x channels, padded to K = 32) is gathered from smem.
+            float* stg = reinterpret_cast<float*>(s_stage);
+            const int t256 = tid;  // 0..255
+            uint32_t gs_base = 0;
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+                const int strip = item % args.nstrip;
+                const int seg = (item / args.nstrip) % args.nseg;
+                const int b = item / (args.nstrip * args.nseg);
+                const int y0 = seg * R, x0 = strip * TC_M;
+                const int nout = min(R, H - y0);
                 const int nin = nout + 2;
+                const float* xin = args.x + (size_t)b * 3 * H * W;
                 auto issue_row1 = [&](int y, uint32_t stage) {
                     const bool yok = y >= 0 && y < H;
                     const uint32_t sdst = smem_u32(stg) + stage * (TC_ROW1 * 4);
-                    for (int i = t; i < 3 * TC_SPX; i += 128) {
+                    for (int i = t256; i < 3 * TC_SPX; i += 256) {
                         const int c = i / TC_SPX, px = i - c * TC_SPX;
                         const int xs = x0 - 1 + px;
                         const bool ok = yok && xs >= 0 && xs < W;
@@ -195,19 +232,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
                 };
 #pragma unroll
                 for (int k = 0; k < TC_PF1; ++k) {
-                    if (k < nin) issue_row1(y0 - 1 + k, (g + k) % TC_NSTAGE1);
+                    if (k < nin) issue_row1(y0 - 1 + k, (gs_base + k) % TC_NSTAGE1);
                     cp_async_commit();
                 }
                 for (int ri = 0; ri < nin; ++ri) {
-                    if (ri + TC_PF1 < nin) issue_row1(y0 - 1 + ri + TC_PF1, (g + ri + TC_PF1) % TC_NSTAGE1);
+                    if (ri + TC_PF1 < nin) issue_row1(y0 - 1 + ri + TC_PF1, (gs_base + ri + TC_PF1) % TC_NSTAGE1);
                     cp_async_commit();
                     cp_async_wait<TC_PF1>();
-                    named_bar_sync(1, 128);
+                    named_bar_sync(1, 256);
                     if (ri < 2) continue;
+                    const uint32_t g = g_base + (ri - 2);
+                    if ((int)(g & 1) != par) continue;
                     float v[28];
 #pragma unroll
                     for (int ky = 0; ky < 3; ++ky) {
-                        const float* sp = stg + ((g + ri - 2 + ky) % TC_NSTAGE1) * TC_ROW1 + t;
+                        const float* sp = stg + ((gs_base + ri - 2 + ky) % TC_NSTAGE1) * TC_ROW1 + t;
 #pragma unroll
                         for (int kx = 0; kx < 3; ++kx)
 #pragma unroll
@@ -221,121 +260,137 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
                         pk[j] = *reinterpret_cast<uint32_t*>(&h);
                     }
                     pk[14] = pk[15] = 0u;
-                    const uint32_t slot = fill % TC_NSLOT, use = fill / TC_NSLOT;
+                    const uint32_t slot = g % TC_NSLOT, use = g / TC_NSLOT;
                     if (use > 0) mbar_wait(&empty[slot], (use - 1) & 1);
                     tc_fence_after();
-                    tmem_st16(tlane + TC_ACC_COLS + slot * SLOT_COLS, pk);
+                    tmem_st16(tlane + slot * SLOT_COLS, pk);
                     tc_wait_st();
                     tc_fence_before();
                     mbar_arrive(&full[slot]);
-                    ++fill;
                 }
-                g += nin;
-            } else {
-                const uint8_t* srcs[2] = {reinterpret_cast<const uint8_t*>(args.src0),
-                                          reinterpret_cast<const uint8_t*>(args.src1)};
-                auto issue_row = [&](int y, uint32_t stage) {
-                    const bool yok = y >= 0 && y < H;
-                    const uint32_t sdst = smem_u32(s_stage) + stage * (NSRC * SRC_STAGE);
-                    for (int i = t; i < NSRC * TC_SPX * 4; i += 128) {
-                        const int s = i / (TC_SPX * 4);
-                        const int rem = i - s * (TC_SPX * 4);
-                        const int px = rem >> 2, ch = rem & 3;
-                        const int xs = x0 - 1 + px;
-                        const bool ok = yok && xs >= 0 && xs < W;
-                        const uint8_t* gp =
-                            srcs[s] + (ok ? (((size_t)b * H + y) * W + xs) * 64 + ch * 16 : (size_t)0);
-                        cp_async16(sdst + s * SRC_STAGE + px * TC_PXP + ch * 16, gp, ok);
-                    }
-                };
+                gs_base += nin;
+                g_base += nout;
+            }
+        } else {
+            // per-thread swizzled smem offsets of the three pixels (dx copies) this lane feeds:
+            // TMA SWIZZLE_64B stores 16-byte chunk c of pixel p at  p*64 + ((c ^ ((p >> 1) & 3)) << 4)
+            uint32_t poff[3], psw[3];
 #pragma unroll
-                for (int k = 0; k < TC_PF; ++k) {
-                    if (k < nrows) issue_row(y0 - 1 + k, (g + k) % TC_NSTAGE);
-                    cp_async_commit();
-                }
-                for (int r = 0; r < nrows; ++r) {
-                    if (r + TC_PF < nrows) issue_row(y0 - 1 + r + TC_PF, (g + r + TC_PF) % TC_NSTAGE);
-                    cp_async_commit();
-                    cp_async_wait<TC_PF>();
-                    named_bar_sync(1, 128);
-                    const uint32_t slot = fill % TC_NSLOT, use = fill / TC_NSLOT;
+            for (int dx = 0; dx < 3; ++dx) {
+                const int p = t + dx;
+                poff[dx] = p * 64;
+                psw[dx] = (p >> 1) & 3;
+            }
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+                const int seg = (item / args.nstrip) % args.nseg;
+                const int nin = min(R, H - seg * R) + 2;
+                for (int ri = 0; ri < nin; ++ri) {
+                    const uint32_t g = g_base + ri;
+                    if ((int)(g & 1) != par) continue;
+                    const uint32_t s = g % TC_NST, us = g / TC_NST;
+                    mbar_wait(&stage_full[s], us & 1);
+                    const uint32_t slot = g % TC_NSLOT, use = g / TC_NSLOT;
                     if (use > 0) mbar_wait(&empty[slot], (use - 1) & 1);
                     tc_fence_after();
-                    const uint8_t* st = s_stage + ((g + r) % TC_NSTAGE) * (NSRC * SRC_STAGE);
+                    const uint8_t* st = s_stage + s * (NSRC * TC_SRC_STRIDE);
 #pragma unroll
-                    for (int s = 0; s < NSRC; ++s) {
+                    for (int src = 0; src < NSRC; ++src) {
 #pragma unroll
                         for (int dx = 0; dx < 3; ++dx) {
-                            const uint4* p = reinterpret_cast<const uint4*>(st + s * SRC_STAGE + (t + dx) * TC_PXP);
-                            const uint4 q0 = p[0], q1 = p[1], q2 = p[2], q3 = p[3];
+                            const uint8_t* pp = st + src * TC_SRC_STRIDE + poff[dx];
+                            const uint4 q0 = *reinterpret_cast<const uint4*>(pp + ((0 ^ psw[dx]) << 4));
+                            const uint4 q1 = *reinterpret_cast<const uint4*>(pp + ((1 ^ psw[dx]) << 4));
+                            const uint4 q2 = *reinterpret_cast<const uint4*>(pp + ((2 ^ psw[dx]) << 4));
+                            const uint4 q3 = *reinterpret_cast<const uint4*>(pp + ((3 ^ psw[dx]) << 4));
                             const uint32_t pk[16] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w,
                                                      q2.x, q2.y, q2.z, q2.w, q3.x, q3.y, q3.z, q3.w};
-                            tmem_st16(tlane + TC_ACC_COLS + slot * SLOT_COLS + dx * COPY_COLS + s * 16, pk);
+                            tmem_st16(tlane + slot * SLOT_COLS + dx * COPY_COLS + src * 16, pk);
                         }
                     }
                     tc_wait_st();
                     tc_fence_before();
                     mbar_arrive(&full[slot]);
-                    ++fill;
+                    mbar_arrive(&stage_empty[s]);
                 }
-                g += nrows;
+                g_base += nin;
             }
         }
-    } else if (warp == 4) {
+    } else if (warp == 9) {
+        // =========================== TMA PRODUCER (one thread) ===========================
+        if (!FIRST && lane == 0) {
+            uint32_t g_base = 0;
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+                const int strip = item % args.nstrip;
+                const int seg = (item / args.nstrip) % args.nseg;
+                const int b = item / (args.nstrip * args.nseg);
+                const int y0 = seg * R, x0 = strip * TC_M;
+                const int nin = min(R, H - y0) + 2;
+                for (int ri = 0; ri < nin; ++ri) {
+                    const uint32_t g = g_base + ri;
+                    const uint32_t s = g % TC_NST, us = g / TC_NST;
+                    if (us > 0) mbar_wait(&stage_empty[s], (us - 1) & 1);
+                    mbar_arrive_expect_tx(&stage_full[s], NSRC * TC_SRC_BYTES);
+                    const uint32_t dst = stage_u32 + s * (NSRC * TC_SRC_STRIDE);
+                    tma_load_4d(dst, &tm0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                    if (NSRC == 2) tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                }
+                g_base += nin;
+            }
+        }
+    } else if (warp == 8) {
         // =========================== MMA ISSUER (one thread) ===========================
         if (lane == 0) {
-            constexpr uint32_t IDESC = idesc_bf16_f32(TC_M, TC_N);
+            constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
             const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_w), 128, 256);
-            uint32_t f0 = 0, o = 0;
+            uint32_t g_base = 0, o_base = 0;
             for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
                 const int seg = (item / args.nstrip) % args.nseg;
                 const int nout = min(R, H - seg * R);
-                for (int j = 0; j < nout; ++j) {
-                    if (j == 0) {
-                        for (int dy = 0; dy < ROWS - 1; ++dy) {
-                            const uint32_t f = f0 + dy;
-                            mbar_wait(&full[f % TC_NSLOT], (f / TC_NSLOT) & 1);
-                        }
+                const int nin = nout + NDY - 1;
+                for (int ri = 0; ri < nin; ++ri) {
+                    const uint32_t g = g_base + ri;
+                    const uint32_t slot = g % TC_NSLOT, use = g / TC_NSLOT;
+                    mbar_wait(&full[slot], use & 1);
+                    if (ri < nout) {  // this input row opens the accumulator block of output row ri
+                        const uint32_t o = o_base + ri, u = o / TC_NB;
+                        if (u > 0) mbar_wait(&acc_empty[tc_pos(o)], (u - 1) & 1);
                     }
-                    {
-                        const uint32_t f = f0 + j + ROWS - 1;
-                        mbar_wait(&full[f % TC_NSLOT], (f / TC_NSLOT) & 1);
-                    }
-                    const uint32_t buf = o % TC_NACC;
-                    if (o >= TC_NACC) mbar_wait(&acc_empty[buf], ((o / TC_NACC) - 1) & 1);
                     tc_fence_after();
-                    const uint32_t d = tbase + buf * TC_N;
+                    const uint32_t abase = tbase + TC_ACC_COLS + slot * SLOT_COLS;
+                    // output row j = ri - dy must lie in [0, nout)
+                    int dy = max(0, ri - (nout - 1));
+                    const int dy_hi = min(NDY - 1, ri);
+                    while (dy <= dy_hi) {
+                        const int p0 = tc_pos(o_base + ri - dy);  // blocks of dy, dy+1, .. are p0, p0+1, .. until the ring wraps
+                        const int cnt = min(dy_hi - dy + 1, TC_NB - p0);
+                        const uint32_t idesc = IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17);
+                        const uint32_t d = tbase + p0 * 32;
+                        const uint64_t bd = bdesc0 + (uint64_t)((dy * 1024) >> 4);
 #pragma unroll
-                    for (int dy = 0; dy < ROWS; ++dy) {
-                        const uint32_t slot = (f0 + j + dy) % TC_NSLOT;
-                        const uint32_t abase = tbase + TC_ACC_COLS + slot * SLOT_COLS;
+                        for (int dx = 0; dx < NDX; ++dx)
 #pragma unroll
-                        for (int dx = 0; dx < (FIRST ? 1 : 3); ++dx) {
-#pragma unroll
-                            for (int kc = 0; kc < KC; ++kc) {
-                                const int tile = (dy * 3 + dx) * KC + kc;
-                                mma_ts(d, abase + dx * COPY_COLS + kc * 8, bdesc0 + (uint64_t)(tile * (TC_TILE >> 4)),
-                                       IDESC, (dy | dx | kc) != 0);
-                            }
-                        }
+                            for (int kc = 0; kc < KC; ++kc)
+                                mma_ts(d, abase + dx * COPY_COLS + kc * 8,
+                                       bd + (uint64_t)(((dx * KC + kc) * TILE) >> 4), idesc, 1u);
+                        dy += cnt;
                     }
-                    tc_commit(&acc_full[buf]);
-                    tc_commit(&empty[(f0 + j) % TC_NSLOT]);
-                    ++o;
+                    tc_commit(&empty[slot]);
+                    const int jc = ri - (NDY - 1);
+                    if (jc >= 0) tc_commit(&acc_full[tc_pos(o_base + jc)]);
                 }
-                for (int dy = 1; dy < ROWS; ++dy) tc_commit(&empty[(f0 + nout - 1 + dy) % TC_NSLOT]);
-                f0 += nout + ROWS - 1;
+                g_base += nin;
+                o_base += nout;
             }
         }
     } else {
         // =========================== EPILOGUE ===========================
-        const int q = warp & 3;
+        const int q = warp & 3, par = (warp - 10) >> 2;
         const int m = q * 32 + lane;
         const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
         float bias[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) bias[i] = s_bias[i];
-        uint32_t o = 0;
+        uint32_t o_base = 0;
         const size_t plane = (size_t)H * W;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int strip = item % args.nstrip;
@@ -344,15 +399,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
             const int y0 = seg * R, xx = strip * TC_M + m;
             const int nout = min(R, H - y0);
             for (int j = 0; j < nout; ++j) {
-                const uint32_t buf = o % TC_NACC;
-                mbar_wait(&acc_full[buf], (o / TC_NACC) & 1);
+                const uint32_t o = o_base + j;
+                if ((int)(o & 1) != par) continue;
+                const int p = tc_pos(o);
+                mbar_wait(&acc_full[p], (o / TC_NB) & 1);
                 tc_fence_after();
                 uint32_t v[32];
-                tmem_ld32(tlane + buf * TC_N, v);
+                tmem_ld32(tlane + p * 32, v);
                 tc_wait_ld();
+                tmem_zero32(tlane + p * 32);
+                tc_wait_st();
                 tc_fence_before();
-                mbar_arrive(&acc_empty[buf]);
-                ++o;
+                mbar_arrive(&acc_empty[p]);
                 const int y = y0 + j;
                 if (xx >= W) continue;
                 if constexpr (!LAST) {
@@ -372,34 +430,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
                 } else {
                     const int iters = args.iters;
                     const size_t pix = (size_t)y * W + xx;
-                    float a[24];
-#pragma unroll
-                    for (int c = 0; c < 24; ++c) a[c] = tanh_approx(__uint_as_float(v[c]) + bias[c]);
-                    if (args.adjust != nullptr) {
-                        float* ap = args.adjust + (size_t)b * 3 * iters * plane + pix;
-#pragma unroll
-                        for (int c = 0; c < 24; ++c)
-                            if (c < 3 * iters) ap[(size_t)c * plane] = a[c];
-                    }
+                    float* ap = args.adjust ? args.adjust + (size_t)b * 3 * iters * plane + pix : nullptr;
                     const float* xp = args.x + (size_t)b * 3 * plane + pix;
                     float* ep = args.enhanced + (size_t)b * 3 * plane + pix;
+                    float yv[3];
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        float yv = __ldg(xp + (size_t)c * plane);
+                    for (int c = 0; c < 3; ++c) yv[c] = __ldg(xp + (size_t)c * plane);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            if (i < iters) yv = curve_step(yv, a[i * 3 + c]);
-                        ep[(size_t)c * plane] = yv;
+                    for (int i = 0; i < 8; ++i) {
+                        if (i < iters) {
+#pragma unroll
+                            for (int c = 0; c < 3; ++c) {
+                                const float a = tanh_approx(__uint_as_float(v[i * 3 + c]) + bias[i * 3 + c]);
+                                if (ap) ap[(size_t)(i * 3 + c) * plane] = a;
+                                yv[c] = curve_step(yv[c], a);
+                            }
+                        }
                     }
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) ep[(size_t)c * plane] = yv[c];
                 }
             }
+            o_base += nout;
         }
     }
 
     // ---- teardown ----
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) {
+    if (warp == 8) {
         tc_fence_after();
         tmem_dealloc(tbase, 512);
     }
@@ -410,17 +469,60 @@ __global__ void __launch_bounds__(TC_THREADS, 1) dce_tc_layer_kernel(const TcArg
 // ------------------------------------------------------------------------------------------------
 static size_t tc_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+typedef CUresult (*tc_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency)
+static tc_encode_fn tc_encoder() {
+    static tc_encode_fn fn = []() -> tc_encode_fn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            (void)cudaGetLastError();
+            return nullptr;
+        }
+        return reinterpret_cast<tc_encode_fn>(p);
+    }();
+    return fn;
+}
+
+// NHWC bf16 [B,H,W,32] as a 4-D tensor (c, x, y, b); box = 32 channels x 130 pixels of one row; 64-byte swizzle;
+// coordinates outside the image (x = -1, x >= W, y = -1, y >= H) are zero-filled = the conv's zero padding.
+static int tc_make_map(CUtensorMap* m, const void* base, int B, int H, int W) {
+    tc_encode_fn enc = tc_encoder();
+    if (!enc) return B200_ERR_LAUNCH;
+    const cuuint64_t dims[4] = {32, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    const cuuint64_t strides[3] = {64, (cuuint64_t)W * 64, (cuuint64_t)H * W * 64};
+    const cuuint32_t box[4] = {32, (cuuint32_t)TC_SPX, 1, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? B200_OK : B200_ERR_LAUNCH;
+}
+
 template <int NSRC, bool FIRST, bool LAST>
-static int tc_launch(const TcArgs& a, cudaStream_t s) {
+static int tc_launch(const TcArgs& a, const void* s0, const void* s1, cudaStream_t s) {
     auto kern = dce_tc_layer_kernel<NSRC, FIRST, LAST>;
     constexpr int smem = tc_smem_bytes<NSRC, FIRST>();
+    static_assert(smem <= 227 * 1024, "shared memory budget");
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
         (void)cudaGetLastError();
         return B200_ERR_LAUNCH;
     }
+    CUtensorMap m0, m1;
+    memset(&m0, 0, sizeof(m0));
+    memset(&m1, 0, sizeof(m1));
+    if (!FIRST) {
+        int rc;
+        if ((rc = tc_make_map(&m0, s0, a.B, a.H, a.W))) return rc;
+        if (NSRC == 2 && (rc = tc_make_map(&m1, s1, a.B, a.H, a.W))) return rc;
+    }
     const long long items = (long long)a.B * a.nseg * a.nstrip;
     const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
-    kern<<<grid, TC_THREADS, smem, s>>>(a);
+    kern<<<grid, TC_THREADS, smem, s>>>(a, m0, m1);
     return launch_status();
 }
 
@@ -462,6 +564,7 @@ int dce_tc_forward(const float* x, const void* packed, float* adjust, float* enh
     const uint8_t* pk = (const uint8_t*)packed;
 
     TcArgs a{};
+    a.x = x;
     a.B = B;
     a.H = H;
     a.W = W;
@@ -470,29 +573,26 @@ int dce_tc_forward(const float* x, const void* packed, float* adjust, float* enh
     a.nseg = (H + a.R - 1) / a.R;
     a.nstrip = (W + TC_M - 1) / TC_M;
     int rc;
-    auto layer = [&](int l, const void* s0, const void* s1, __nv_bfloat16* dst) { 
-        a.src0 = s0;
-        a.src1 = s1;
+    auto layer = [&](int l, __nv_bfloat16* dst) {
         a.dst = dst;
         a.wpack = pk + tc_layer_offset(l);
     };
-    layer(0, x, nullptr, x1);
-    if ((rc = tc_launch<1, true, false>(a, s))) return rc;
-    layer(1, x1, nullptr, x2);
-    if ((rc = tc_launch<1, false, false>(a, s))) return rc;
-    layer(2, x2, nullptr, x3);
-    if ((rc = tc_launch<1, false, false>(a, s))) return rc;
-    layer(3, x3, nullptr, x4);
-    if ((rc = tc_launch<1, false, false>(a, s))) return rc;
-    layer(4, x3, x4, x5);
-    if ((rc = tc_launch<2, false, false>(a, s))) return rc;
-    layer(5, x2, x5, x6);
-    if ((rc = tc_launch<2, false, false>(a, s))) return rc;
-    layer(6, x1, x6, nullptr);
-    a.x = x;
+    layer(0, x1);
+    if ((rc = tc_launch<1, true, false>(a, nullptr, nullptr, s))) return rc;
+    layer(1, x2);
+    if ((rc = tc_launch<1, false, false>(a, x1, nullptr, s))) return rc;
+    layer(2, x3);
+    if ((rc = tc_launch<1, false, false>(a, x2, nullptr, s))) return rc;
+    layer(3, x4);
+    if ((rc = tc_launch<1, false, false>(a, x3, nullptr, s))) return rc;
+    layer(4, x5);
+    if ((rc = tc_launch<2, false, false>(a, x3, x4, s))) return rc;
+    layer(5, x6);
+    if ((rc = tc_launch<2, false, false>(a, x2, x5, s))) return rc;
+    layer(6, nullptr);
     a.adjust = adjust;
     a.enhanced = enhanced;
-    if ((rc = tc_launch<2, false, true>(a, s))) return rc;
+    if ((rc = tc_launch<2, false, true>(a, x1, x6, s))) return rc;
     return B200_OK;
 }
 
