@@ -316,9 +316,12 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
             }
         }
     } else if (warp == 9) {
-        // =========================== TMA PRODUCER (one thread) ===========================
-        if (!FIRST && lane == 0) {
-            uint32_t g_base = 0;
+        // =========================== TMA PRODUCER ===========================
+        // warp-uniform control flow, one elected lane issues expect_tx + the bulk tensor copies
+        if constexpr (!FIRST) {
+            const bool leader = elect_one();
+            uint32_t s = 0, spar = 0;  // stage ring position / phase parity of the NEXT fill
+            bool first_round = true;
             for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
                 const int strip = item % args.nstrip;
                 const int seg = (item / args.nstrip) % args.nseg;
@@ -326,42 +329,61 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                 const int y0 = seg * R, x0 = strip * TC_M;
                 const int nin = min(R, H - y0) + 2;
                 for (int ri = 0; ri < nin; ++ri) {
-                    const uint32_t g = g_base + ri;
-                    const uint32_t s = g % TC_NST, us = g / TC_NST;
-                    if (us > 0) mbar_wait(&stage_empty[s], (us - 1) & 1);
-                    mbar_arrive_expect_tx(&stage_full[s], NSRC * TC_SRC_BYTES);
-                    const uint32_t dst = stage_u32 + s * (NSRC * TC_SRC_STRIDE);
-                    tma_load_4d(dst, &tm0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
-                    if (NSRC == 2) tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                    if (!first_round) mbar_wait(&stage_empty[s], spar ^ 1);
+                    if (leader) {
+                        mbar_arrive_expect_tx(&stage_full[s], NSRC * TC_SRC_BYTES);
+                        const uint32_t dst = stage_u32 + s * (NSRC * TC_SRC_STRIDE);
+                        tma_load_4d(dst, &tm0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                        if (NSRC == 2)
+                            tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                    }
+                    __syncwarp();
+                    if (++s == TC_NST) {
+                        s = 0;
+                        spar ^= 1;
+                        first_round = false;
+                    }
                 }
-                g_base += nin;
             }
         }
     } else if (warp == 8) {
-        // =========================== MMA ISSUER (one thread) ===========================
-        if (lane == 0) {
-            constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
-            const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_w), 128, 256);
-            uint32_t g_base = 0, o_base = 0;
-            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-                const int seg = (item / args.nstrip) % args.nseg;
-                const int nout = min(R, H - seg * R);
-                const int nin = nout + NDY - 1;
-                for (int ri = 0; ri < nin; ++ri) {
-                    const uint32_t g = g_base + ri;
-                    const uint32_t slot = g % TC_NSLOT, use = g / TC_NSLOT;
-                    mbar_wait(&full[slot], use & 1);
-                    if (ri < nout) {  // this input row opens the accumulator block of output row ri
-                        const uint32_t o = o_base + ri, u = o / TC_NB;
-                        if (u > 0) mbar_wait(&acc_empty[tc_pos(o)], (u - 1) & 1);
+        // =========================== MMA ISSUER ===========================
+        // The whole warp runs the (warp-uniform) control flow so that addresses and descriptors stay in uniform
+        // registers; one elected lane issues every tcgen05.mma / tcgen05.commit.
+        constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
+        constexpr uint32_t IDESC_FULL = IDESC0 | ((uint32_t)(NDY * 32 >> 3) << 17);
+        const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_w), 128, 256);
+        const bool leader = elect_one();
+        uint32_t slot = 0, spar = 0;  // A-slot ring position and phase parity
+        uint32_t o_base = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int seg = (item / args.nstrip) % args.nseg;
+            const int nout = min(R, H - seg * R);
+            const int nin = nout + NDY - 1;
+            uint32_t on = o_base % TC_NB, upar = (o_base / TC_NB) & 1;  // block ring position / use parity of row o_base+ri
+            for (int ri = 0; ri < nin; ++ri) {
+                mbar_wait(&full[slot], spar);
+                const int pn = TC_NB - 1 - (int)on;  // block opened by this input row (output row ri, dy = 0)
+                if (ri < nout && o_base + ri >= TC_NB) mbar_wait(&acc_empty[pn], upar ^ 1);
+                tc_fence_after();
+                const uint32_t abase = tbase + TC_ACC_COLS + slot * SLOT_COLS;
+                if (ri >= NDY - 1 && ri < nout && pn + NDY <= TC_NB) {
+                    // interior row, no ring wrap: one N = 32*NDY MMA per (dx, kc)
+                    if (leader) {
+                        const uint32_t d = tbase + pn * 32;
+#pragma unroll
+                        for (int dx = 0; dx < NDX; ++dx)
+#pragma unroll
+                            for (int kc = 0; kc < KC; ++kc)
+                                mma_ts(d, abase + dx * COPY_COLS + kc * 8,
+                                       bdesc0 + (uint64_t)(((dx * KC + kc) * TILE) >> 4), IDESC_FULL, 1u);
                     }
-                    tc_fence_after();
-                    const uint32_t abase = tbase + TC_ACC_COLS + slot * SLOT_COLS;
-                    // output row j = ri - dy must lie in [0, nout)
+                } else if (leader) {
+                    // segment borders (output row j = ri - dy must lie in [0, nout)) and ring wrap: split into groups
                     int dy = max(0, ri - (nout - 1));
                     const int dy_hi = min(NDY - 1, ri);
                     while (dy <= dy_hi) {
-                        const int p0 = tc_pos(o_base + ri - dy);  // blocks of dy, dy+1, .. are p0, p0+1, .. until the ring wraps
+                        const int p0 = (pn + dy) % TC_NB;
                         const int cnt = min(dy_hi - dy + 1, TC_NB - p0);
                         const uint32_t idesc = IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17);
                         const uint32_t d = tbase + p0 * 32;
@@ -374,13 +396,22 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                                        bd + (uint64_t)(((dx * KC + kc) * TILE) >> 4), idesc, 1u);
                         dy += cnt;
                     }
-                    tc_commit(&empty[slot]);
-                    const int jc = ri - (NDY - 1);
-                    if (jc >= 0) tc_commit(&acc_full[tc_pos(o_base + jc)]);
                 }
-                g_base += nin;
-                o_base += nout;
+                if (leader) {
+                    tc_commit(&empty[slot]);
+                    if (ri >= NDY - 1) tc_commit(&acc_full[(pn + NDY - 1) % TC_NB]);
+                }
+                __syncwarp();
+                if (++slot == TC_NSLOT) {
+                    slot = 0;
+                    spar ^= 1;
+                }
+                if (++on == TC_NB) {
+                    on = 0;
+                    upar ^= 1;
+                }
             }
+            o_base += nout;
         }
     } else {
         // =========================== EPILOGUE ===========================
