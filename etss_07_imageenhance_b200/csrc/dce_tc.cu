@@ -17,12 +17,13 @@
 //
 // Warp roles (576 threads, 1 persistent CTA per SM, 512 TMEM columns):
 //   warps 0-7    loaders, two per TMEM lane quarter, alternating input rows
-//   warp  8      lane 0 issues the MMAs, tcgen05.commit -> empty[slot], acc_full[block]
-//   warp  9      lane 0 is the TMA producer (expect_tx + cp.async.bulk.tensor per input row and source)
+//   warp  8      MMA issuer: warp-uniform control flow, one elected lane issues tcgen05.mma / tcgen05.commit
+//                (-> empty[slot], acc_full[block])
+//   warp  9      TMA producer: one elected lane, expect_tx + cp.async.bulk.tensor per input row and source
 //   warps 10-17  epilogue, two per lane quarter, alternating output rows: tcgen05.ld -> bias + ReLU -> bf16 NHWC
 //                store; layer 7: tanh -> `adjust` (NCHW fp32) + the 8-iteration curve on x -> `enhanced`
-// Layer 1 (Cin = 3) uses the same pipeline with an im2col loader (K = 27 padded to 32, N = 32, 2 MMAs per row);
-// its fp32 NCHW input rows are staged with cp.async.
+// Layer 1 (Cin = 3) runs the same pipeline with K padded to 16 (one chunk): its loaders read the fp32 NCHW input
+// directly (coalesced along x, one row ahead) and rewrite only the two non-zero TMEM columns of each dx copy.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -41,19 +42,15 @@ constexpr int TC_NST = 8;            // TMA smem stages (input rows); even
 constexpr int TC_SPX = TC_M + 2;     // staged pixels per row (halo of 1 on each side)
 constexpr int TC_SRC_BYTES = TC_SPX * 64;          // TMA box bytes per source per row (8320)
 constexpr int TC_SRC_STRIDE = 8704;                // smem bytes per source per stage (17 x 512: keeps the swizzle phase)
-constexpr int TC_NSTAGE1 = 12;       // layer 1: staged fp32 input rows; NSTAGE1 >= PF1 + 4
-constexpr int TC_PF1 = 8;
-constexpr int TC_ROW1 = 3 * 132;     // layer 1: floats per staged row ([3 channels][132])
 constexpr int TC_THREADS = 576;
 static_assert((2 * TC_NST + 2 * TC_NSLOT + 2 * TC_NB) * 8 <= 384, "mbarrier area");
 
 // packed weights per layer: B tiles then 32 fp32 biases.
-//   layer 0   : 2 tiles [N=32][K=16] (1 KB each), k = (ky*3+kx)*3 + c
-//   layers 1-6: per (dx, kc) one tile [N=96 = dy*32 + cout][K=16] (3 KB)
+//   per (dx, kc) one tile [N=96 = dy*32 + cout][K=16] (3 KB); layer 0 has one K chunk (3 channels, zero padded)
 // element (n, kk) of a tile at byte (n/8)*256 + (kk/8)*128 + (n%8)*16 + (kk%8)*2   (K-major core matrices,
 // LBO = 128, SBO = 256)
-__host__ __device__ constexpr int tc_kc(int l) { return l == 0 ? 2 : (l <= 3 ? 2 : 4); }
-__host__ __device__ constexpr int tc_wbytes(int l) { return l == 0 ? 2 * 1024 : 3 * tc_kc(l) * 3072; }
+__host__ __device__ constexpr int tc_kc(int l) { return l == 0 ? 1 : (l <= 3 ? 2 : 4); }
+__host__ __device__ constexpr int tc_wbytes(int l) { return 3 * tc_kc(l) * 3072; }
 __host__ __device__ constexpr int tc_layer_bytes(int l) { return tc_wbytes(l) + 128; }
 __host__ __device__ constexpr int tc_layer_offset(int l) {
     int o = 0;
@@ -74,29 +71,15 @@ __global__ void dce_tc_pack_kernel(TcPackArgs a, uint8_t* __restrict__ packed, i
     const int cout = l == 6 ? cout_last : 32;
     uint8_t* base = packed + tc_layer_offset(l);
     __nv_bfloat16* tiles = reinterpret_cast<__nv_bfloat16*>(base);
-    if (l == 0) {
-        for (int i = threadIdx.x; i < 2 * 512; i += blockDim.x) {
-            const int kc = i >> 9, e = i & 511;
-            const int n = e >> 4, kk = e & 15;
-            const int k = kc * 16 + kk;
-            float v = 0.f;
-            if (k < 27) {
-                const int tp = k / 3, c = k - tp * 3;
-                v = a.w[0][(n * 3 + c) * 9 + tp];
-            }
-            tiles[kc * 512 + (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7)] = __float2bfloat16_rn(v);
-        }
-    } else {
-        const int n_el = 3 * kc_n * 1536;
-        for (int i = threadIdx.x; i < n_el; i += blockDim.x) {
-            const int tile = i / 1536, e = i - tile * 1536;
-            const int dx = tile / kc_n, kc = tile - dx * kc_n;
-            const int n = e >> 4, kk = e & 15;  // n = dy*32 + cout
-            const int dy = n >> 5, oc = n & 31;
-            const int ci = kc * 16 + kk;
-            const float v = oc < cout ? a.w[l][(oc * cin + ci) * 9 + dy * 3 + dx] : 0.f;
-            tiles[tile * 1536 + (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7)] = __float2bfloat16_rn(v);
-        }
+    const int n_el = 3 * kc_n * 1536;
+    for (int i = threadIdx.x; i < n_el; i += blockDim.x) {
+        const int tile = i / 1536, e = i - tile * 1536;
+        const int dx = tile / kc_n, kc = tile - dx * kc_n;
+        const int n = e >> 4, kk = e & 15;  // n = dy*32 + cout
+        const int dy = n >> 5, oc = n & 31;
+        const int ci = kc * 16 + kk;
+        const float v = (oc < cout && ci < cin) ? a.w[l][(oc * cin + ci) * 9 + dy * 3 + dx] : 0.f;
+        tiles[tile * 1536 + (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7)] = __float2bfloat16_rn(v);
     }
     float* bias = reinterpret_cast<float*>(base + tc_wbytes(l));
     for (int i = threadIdx.x; i < 32; i += blockDim.x) bias[i] = i < cout ? a.b[l][i] : 0.f;
@@ -114,13 +97,13 @@ struct TcArgs {
 
 template <int NSRC, bool FIRST>
 __host__ __device__ constexpr int tc_wbytes_t() {
-    return FIRST ? 2 * 1024 : 3 * 2 * NSRC * 3072;
+    return FIRST ? 3 * 3072 : 3 * 2 * NSRC * 3072;
 }
 template <int NSRC, bool FIRST>
 constexpr int tc_smem_bytes() {
     // weights | bias 128 | barriers 384 | tmem addr 16 | pad to 1024 | stages
     return tc_wbytes_t<NSRC, FIRST>() + 128 + 384 + 16 + 1024 +
-           (FIRST ? TC_NSTAGE1 * TC_ROW1 * 4 : TC_NST * NSRC * TC_SRC_STRIDE);
+           (FIRST ? 0 : TC_NST * NSRC * TC_SRC_STRIDE);
 }
 
 __device__ __forceinline__ int tc_pos(uint32_t o) { return TC_NB - 1 - (int)(o % TC_NB); }
@@ -128,12 +111,12 @@ __device__ __forceinline__ int tc_pos(uint32_t o) { return TC_NB - 1 - (int)(o %
 template <int NSRC, bool FIRST, bool LAST>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1) {
-    constexpr int KC = FIRST ? 2 : 2 * NSRC;            // K chunks of 16 per (dy, dx)
-    constexpr int NDY = FIRST ? 1 : 3;                  // output rows one input row feeds
-    constexpr int NDX = FIRST ? 1 : 3;
+    constexpr int KC = FIRST ? 1 : 2 * NSRC;            // K chunks of 16 per (dy, dx)
+    constexpr int NDY = 3;                              // output rows one input row feeds
+    constexpr int NDX = 3;
     constexpr int WBYTES = tc_wbytes_t<NSRC, FIRST>();
-    constexpr int TILE = FIRST ? 1024 : 3072;
-    constexpr int COPY_COLS = FIRST ? 16 : 16 * NSRC;   // TMEM columns of one dx copy
+    constexpr int TILE = 3072;
+    constexpr int COPY_COLS = FIRST ? 8 : 16 * NSRC;    // TMEM columns of one dx copy
     constexpr int SLOT_COLS = NDX * COPY_COLS;
     static_assert(TC_ACC_COLS + TC_NSLOT * SLOT_COLS <= 512, "TMEM budget");
 
@@ -206,70 +189,57 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16) + TC_ACC_COLS;
         uint32_t g_base = 0;
         if constexpr (FIRST) {
-            // fp32 NCHW input rows staged once ([3][132] floats per row) by all 256 loader threads; each staged row
-            // feeds 3 output rows; the im2col row (27 = taps x channels, padded to K = 32) is gathered from smem.
-            float* stg = reinterpret_cast<float*>(s_stage);
-            const int t256 = tid;  // 0..255
-            uint32_t gs_base = 0;
+            // Layer 1: Cin = 3, K padded to 16 (8 TMEM columns per dx copy, only the first two are non-zero and are
+            // the only ones rewritten).  Each lane reads its 3 x 3 (dx, channel) fp32 values straight from the NCHW
+            // input (coalesced along x), one row ahead of the one it is converting.
+            for (int sl = par; sl < TC_NSLOT; sl += 2) {  // zero the padding columns of every slot once
+                const uint32_t z[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+                tmem_st16(tlane + sl * SLOT_COLS, z);
+                tmem_st16(tlane + sl * SLOT_COLS + 8, z);
+            }
+            tc_wait_st();
+            named_bar_sync(1, 256);
             for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
                 const int strip = item % args.nstrip;
                 const int seg = (item / args.nstrip) % args.nseg;
                 const int b = item / (args.nstrip * args.nseg);
-                const int y0 = seg * R, x0 = strip * TC_M;
-                const int nout = min(R, H - y0);
-                const int nin = nout + 2;
+                const int y0 = seg * R, xx = strip * TC_M + t;
+                const int nin = min(R, H - y0) + 2;
                 const float* xin = args.x + (size_t)b * 3 * H * W;
-                auto issue_row1 = [&](int y, uint32_t stage) {
+                auto load_row = [&](int y, float (&v)[9]) {
                     const bool yok = y >= 0 && y < H;
-                    const uint32_t sdst = smem_u32(stg) + stage * (TC_ROW1 * 4);
-                    for (int i = t256; i < 3 * TC_SPX; i += 256) {
-                        const int c = i / TC_SPX, px = i - c * TC_SPX;
-                        const int xs = x0 - 1 + px;
+#pragma unroll
+                    for (int dx = 0; dx < 3; ++dx) {
+                        const int xs = xx + dx - 1;
                         const bool ok = yok && xs >= 0 && xs < W;
-                        const float* gp = xin + (ok ? ((size_t)c * H + y) * W + xs : (size_t)0);
-                        cp_async4(sdst + (c * 132 + px) * 4, gp, ok);
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) v[dx * 3 + c] = ok ? __ldg(xin + ((size_t)c * H + y) * W + xs) : 0.f;
                     }
                 };
+                int ri = (int)((g_base ^ (uint32_t)par) & 1);  // first input row of this item with (g & 1) == par
+                float nxt[9];
+                if (ri < nin) load_row(y0 - 1 + ri, nxt);
+                for (; ri < nin; ri += 2) {
+                    float cur[9];
 #pragma unroll
-                for (int k = 0; k < TC_PF1; ++k) {
-                    if (k < nin) issue_row1(y0 - 1 + k, (gs_base + k) % TC_NSTAGE1);
-                    cp_async_commit();
-                }
-                for (int ri = 0; ri < nin; ++ri) {
-                    if (ri + TC_PF1 < nin) issue_row1(y0 - 1 + ri + TC_PF1, (gs_base + ri + TC_PF1) % TC_NSTAGE1);
-                    cp_async_commit();
-                    cp_async_wait<TC_PF1>();
-                    named_bar_sync(1, 256);
-                    if (ri < 2) continue;
-                    const uint32_t g = g_base + (ri - 2);
-                    if ((int)(g & 1) != par) continue;
-                    float v[28];
-#pragma unroll
-                    for (int ky = 0; ky < 3; ++ky) {
-                        const float* sp = stg + ((gs_base + ri - 2 + ky) % TC_NSTAGE1) * TC_ROW1 + t;
-#pragma unroll
-                        for (int kx = 0; kx < 3; ++kx)
-#pragma unroll
-                            for (int c = 0; c < 3; ++c) v[(ky * 3 + kx) * 3 + c] = sp[c * 132 + kx];
-                    }
-                    v[27] = 0.f;
-                    uint32_t pk[16];
-#pragma unroll
-                    for (int j = 0; j < 14; ++j) {
-                        __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                        pk[j] = *reinterpret_cast<uint32_t*>(&h);
-                    }
-                    pk[14] = pk[15] = 0u;
+                    for (int i = 0; i < 9; ++i) cur[i] = nxt[i];
+                    if (ri + 2 < nin) load_row(y0 - 1 + ri + 2, nxt);
+                    const uint32_t g = g_base + ri;
                     const uint32_t slot = g % TC_NSLOT, use = g / TC_NSLOT;
                     if (use > 0) mbar_wait(&empty[slot], (use - 1) & 1);
                     tc_fence_after();
-                    tmem_st16(tlane + slot * SLOT_COLS, pk);
+#pragma unroll
+                    for (int dx = 0; dx < 3; ++dx) {
+                        __nv_bfloat162 h0 = __floats2bfloat162_rn(cur[dx * 3], cur[dx * 3 + 1]);
+                        __nv_bfloat162 h1 = __floats2bfloat162_rn(cur[dx * 3 + 2], 0.f);
+                        tmem_st2(tlane + slot * SLOT_COLS + dx * COPY_COLS, *reinterpret_cast<uint32_t*>(&h0),
+                                 *reinterpret_cast<uint32_t*>(&h1));
+                    }
                     tc_wait_st();
                     tc_fence_before();
                     mbar_arrive(&full[slot]);
                 }
-                gs_base += nin;
-                g_base += nout;
+                g_base += nin;
             }
         } else {
             // per-thread swizzled smem offsets of the three pixels (dx copies) this lane feeds:
