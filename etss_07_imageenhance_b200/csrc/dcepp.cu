@@ -10,6 +10,7 @@
 //       (align_corners=True) from shared memory, applies the 8-iteration curve, writes `enhanced` and
 //       `adjust` once each.  Persistent CTAs, grid = multiple of the SM count.
 #include "common.cuh"
+#include "dcepp_mma.cuh"
 
 namespace b200 {
 
@@ -55,6 +56,10 @@ __global__ void dcepp_pack_kernel(PackArgs args, float* __restrict__ packed) {
     }
     out += n_pw;
     for (int i = threadIdx.x; i < n_pb; i += blockDim.x) out[i] = i < L.cout ? args.pw_b[l][i] : 0.f;
+    // layers 2..7 also get the tensor-core layout (depthwise taps + split-bf16 pointwise fragments)
+    if (l >= 1)
+        mm_pack_layer(l, args.dw_w[l], args.dw_b[l], args.pw_w[l], args.pw_b[l],
+                      reinterpret_cast<uint32_t*>(packed + PP_TOTAL_FLOATS) + mm_offset(l));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -326,7 +331,7 @@ static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 using namespace b200;
 
-extern "C" size_t b200_dcepp_packed_floats(void) { return (size_t)PP_TOTAL_FLOATS; }
+extern "C" size_t b200_dcepp_packed_floats(void) { return (size_t)PP_TOTAL_FLOATS + MM_TOTAL_WORDS; }
 
 extern "C" int b200_dcepp_pack_weights(const float* const* dw_w, const float* const* dw_b, const float* const* pw_w,
                                        const float* const* pw_b, float* packed, void* stream) {
@@ -373,12 +378,13 @@ extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_l
     const float sfs = (float)sf;
     int rc;
     if ((rc = launch_k1<3, 1, 8, true, false>(x, nullptr, x1, packed + pp_layer_offset(0), B, h, w, H, W, sfs, s))) return rc;
-    if ((rc = launch_k1<32, 1, 8, false, false>(x1, nullptr, x2, packed + pp_layer_offset(1), B, h, w, h, w, 1.f, s))) return rc;
-    if ((rc = launch_k1<32, 1, 8, false, false>(x2, nullptr, x3, packed + pp_layer_offset(2), B, h, w, h, w, 1.f, s))) return rc;
-    if ((rc = launch_k1<32, 1, 8, false, false>(x3, nullptr, x4, packed + pp_layer_offset(3), B, h, w, h, w, 1.f, s))) return rc;
-    if ((rc = launch_k1<32, 2, 8, false, false>(x3, x4, x5, packed + pp_layer_offset(4), B, h, w, h, w, 1.f, s))) return rc;
-    if ((rc = launch_k1<32, 2, 8, false, false>(x2, x5, x6, packed + pp_layer_offset(5), B, h, w, h, w, 1.f, s))) return rc;
-    if ((rc = launch_k1<32, 2, 1, false, true>(x1, x6, a_lr, packed + pp_layer_offset(6), B, h, w, h, w, 1.f, s))) return rc;
+    const uint32_t* mm = reinterpret_cast<const uint32_t*>(packed + PP_TOTAL_FLOATS);
+    if ((rc = launch_mm<1, 4, false>(x1, nullptr, x2, mm + mm_offset(1), B, h, w, s))) return rc;
+    if ((rc = launch_mm<1, 4, false>(x2, nullptr, x3, mm + mm_offset(2), B, h, w, s))) return rc;
+    if ((rc = launch_mm<1, 4, false>(x3, nullptr, x4, mm + mm_offset(3), B, h, w, s))) return rc;
+    if ((rc = launch_mm<2, 4, false>(x3, x4, x5, mm + mm_offset(4), B, h, w, s))) return rc;
+    if ((rc = launch_mm<2, 4, false>(x2, x5, x6, mm + mm_offset(5), B, h, w, s))) return rc;
+    if ((rc = launch_mm<2, 1, true>(x1, x6, a_lr, mm + mm_offset(6), B, h, w, s))) return rc;
     return B200_OK;
 }
 

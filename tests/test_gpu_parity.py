@@ -13,6 +13,7 @@ from oracle import oracle as O
 pytestmark = pytest.mark.gpu
 TOL = 1e-3      # contract (BASELINE.json north_star, fp32 mode)
 TIGHT = 1e-4    # what the fp32 kernels actually have to meet here
+TIGHT_PP = 2.5e-4  # Zero-DCE++ end to end: the pointwise convs run as 3-term split-bf16 tensor-core MMAs (~2^-16 per product)
 
 
 def maxerr(a, b):
@@ -79,7 +80,7 @@ def test_dcepp_golden(cuda_dev, golden, name, sf, regime):
     assert out["enhanced"].dtype == torch.float32 and out["enhanced"].device == xin.device
     ea, ee = maxerr(out["adjust"], outs["adjust"]), maxerr(out["enhanced"], outs["enhanced"])
     assert ea <= TOL and ee <= TOL
-    assert ea <= TIGHT and ee <= TIGHT, (ea, ee)
+    assert ea <= TIGHT_PP and ee <= TIGHT_PP, (ea, ee)
     # fast mode: same enhanced, no adjust
     m.return_adjust = False
     out2 = m({"image": xin})
@@ -94,8 +95,8 @@ def test_dcepp_ragged_shapes_vs_oracle(cuda_dev, sf, H, W, B):
     m = load_into(P.ZeroDCEpp_RE(scale_factor=sf), sd).to(cuda_dev)
     out = m({"image": x.to(cuda_dev)})
     ref = O.zero_dcepp_forward(x, sd, scale_factor=sf)
-    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT
-    assert maxerr(out["enhanced"], ref["enhanced"]) <= TIGHT
+    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT_PP
+    assert maxerr(out["enhanced"], ref["enhanced"]) <= TIGHT_PP
 
 
 def test_dcepp_stage_ops_vs_oracle(cuda_dev):
@@ -126,8 +127,8 @@ def test_dcepp_full_size_1080p_vs_oracle_and_properties(cuda_dev):
     m = load_into(P.ZeroDCEpp_RE(scale_factor=12), sd).to(cuda_dev)
     out = m({"image": x.to(cuda_dev)})
     ref = O.zero_dcepp_forward(x, sd, scale_factor=12)
-    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT
-    assert maxerr(out["enhanced"], ref["enhanced"]) <= TIGHT
+    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT_PP
+    assert maxerr(out["enhanced"], ref["enhanced"]) <= TIGHT_PP
     # zero weights + zero bias => adjust == 0 and enhanced == x exactly, at full 4K size
     z = load_into(P.ZeroDCEpp_RE(scale_factor=12), {k: torch.zeros_like(v) for k, v in sd.items()}).to(cuda_dev)
     x4k = O.synthetic_lowlight(1, 2160, 3840, seed=56).to(cuda_dev)
@@ -146,7 +147,7 @@ def test_dcepp_weight_cache_invalidation(cuda_dev):
     load_into(m, sd)
     b = m({"image": x})["enhanced"]
     assert not torch.equal(a, b)
-    assert maxerr(b, O.zero_dcepp_forward(x.cpu(), sd, 12)["enhanced"]) <= TIGHT
+    assert maxerr(b, O.zero_dcepp_forward(x.cpu(), sd, 12)["enhanced"]) <= TIGHT_PP
 
 
 # ------------------------------------------------------------------ Zero-DCE (fp32 mode)
