@@ -9,6 +9,7 @@
 #include <math.h>
 
 #include "common.cuh"
+#include "tcgen05.cuh"
 
 namespace b200 {
 
@@ -20,32 +21,43 @@ struct SciWeights {
 static_assert(sizeof(SciWeights) == B200_SCI_PACKED_FLOATS * sizeof(float), "packed size");
 
 constexpr int S_TH = 16, S_TW = 32;
-constexpr int SX_H = S_TH + 6, SX_W = S_TW + 6;  // 22 x 38
+constexpr int SX_H = S_TH + 6, SX_W = 44;         // 22 rows x (4 + 32 + 8) columns: image column x0 - 4 at column 0,
+                                                  // so every row is eleven 16-byte cp.async chunks
 constexpr int S1_H = S_TH + 4, S1_W = S_TW + 4;  // 20 x 36
 constexpr int S2_H = S_TH + 2, S2_W = S_TW + 2;  // 18 x 34
 
-// 3x3x3 -> 3 convolution at one position; `in` points at the top-left tap of channel 0
+// 3x3x3 -> 3 convolution at TWO vertically adjacent positions (rows r, r+1 of the same column) on the packed fp32
+// pipe: each FFMA2 carries one weight (scalar broadcast) times the value pair (in[r+ky][..], in[r+1+ky][..]).
+// `in` points at the top-left tap of channel 0 for the upper position.  out[co] = (upper, lower).
 template <int IN_W, int IN_PLANE>
-__device__ __forceinline__ void conv3(const float* __restrict__ in, const float* w, const float* bias, float out[3]) {
-    out[0] = bias[0];
-    out[1] = bias[1];
-    out[2] = bias[2];
+__device__ __forceinline__ void conv3_pair(const float* __restrict__ in, const float* w, const float* bias,
+                                           float2 out[3]) {
 #pragma unroll
-    for (int ci = 0; ci < 3; ++ci)
+    for (int co = 0; co < 3; ++co) out[co] = make_float2(bias[co], bias[co]);
 #pragma unroll
-        for (int ky = 0; ky < 3; ++ky)
+    for (int ci = 0; ci < 3; ++ci) {
 #pragma unroll
-            for (int kx = 0; kx < 3; ++kx) {
-                const float v = in[ci * IN_PLANE + ky * IN_W + kx];
+        for (int kx = 0; kx < 3; ++kx) {
+            float v[4];
 #pragma unroll
-                for (int co = 0; co < 3; ++co) out[co] = fmaf(w[((co * 3 + ci) * 3 + ky) * 3 + kx], v, out[co]);
+            for (int rr = 0; rr < 4; ++rr) v[rr] = in[ci * IN_PLANE + rr * IN_W + kx];
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky) {
+                const float2 vp = make_float2(v[ky], v[ky + 1]);
+#pragma unroll
+                for (int co = 0; co < 3; ++co) {
+                    const float wv = w[((co * 3 + ci) * 3 + ky) * 3 + kx];
+                    out[co] = __ffma2_rn(make_float2(wv, wv), vp, out[co]);
+                }
             }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256)
 sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* __restrict__ r,
                  const __grid_constant__ SciWeights wt, int H, int W) {
-    __shared__ float sx[3 * SX_H * SX_W];
+    __shared__ __align__(16) float sx[3 * SX_H * SX_W];
     __shared__ float s1[3 * S1_H * S1_W];
     __shared__ float s2[3 * S2_H * S2_W];
     const int t = threadIdx.x;
@@ -54,59 +66,79 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
     const size_t plane = (size_t)H * W;
     const float* xb = x + (size_t)b * 3 * plane;
 
-    for (int idx = t; idx < 3 * SX_H * SX_W; idx += 256) {
-        const int c = idx / (SX_H * SX_W);
-        const int rem = idx - c * (SX_H * SX_W);
-        const int rr = rem / SX_W, cc = rem - rr * SX_W;
-        const int yy = y0 - 3 + rr, xx = x0 - 3 + cc;
-        float v = 0.f;
-        if (yy >= 0 && yy < H && xx >= 0 && xx < W) v = __ldg(xb + c * plane + (size_t)yy * W + xx);
-        sx[idx] = v;
+    {   // x halo tile via cp.async (all loads in flight at once); zero fill outside the image = the conv's zero padding
+        const uint32_t sh = tc::smem_u32(sx);
+        if ((W & 3) == 0) {
+            for (int i = t; i < 3 * SX_H * (SX_W / 4); i += 256) {
+                const int p = i / (SX_W / 4), j = i - p * (SX_W / 4);
+                const int c = p / SX_H, rr = p - c * SX_H;
+                const int yy = y0 - 3 + rr, xx = x0 - 4 + 4 * j;
+                const bool ok = yy >= 0 && yy < H && xx >= 0 && xx < W;
+                tc::cp_async16(sh + (p * SX_W + 4 * j) * 4, xb + (ok ? c * plane + (size_t)yy * W + xx : (size_t)0), ok);
+            }
+        } else {
+            for (int i = t; i < 3 * SX_H * SX_W; i += 256) {
+                const int p = i / SX_W, cc = i - p * SX_W;
+                const int c = p / SX_H, rr = p - c * SX_H;
+                const int yy = y0 - 3 + rr, xx = x0 - 4 + cc;
+                const bool ok = yy >= 0 && yy < H && xx >= 0 && xx < W;
+                tc::cp_async4(sh + i * 4, xb + (ok ? c * plane + (size_t)yy * W + xx : (size_t)0), ok);
+            }
+        }
+        tc::cp_async_commit();
+        tc::cp_async_wait<0>();
     }
     __syncthreads();
     // fea1 = relu(conv(x)) on the 20x36 region; zero outside the image (that is the next conv's zero padding)
-    for (int idx = t; idx < S1_H * S1_W; idx += 256) {
-        const int rr = idx / S1_W, cc = idx - rr * S1_W;
+    for (int idx = t; idx < (S1_H / 2) * S1_W; idx += 256) {
+        const int rp = idx / S1_W, cc = idx - rp * S1_W;
+        const int rr = 2 * rp;
         const int yy = y0 - 2 + rr, xx = x0 - 2 + cc;
-        float o[3] = {0.f, 0.f, 0.f};
-        if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-            conv3<SX_W, SX_H * SX_W>(sx + rr * SX_W + cc, wt.w1, wt.b1, o);
-            o[0] = fmaxf(o[0], 0.f);
-            o[1] = fmaxf(o[1], 0.f);
-            o[2] = fmaxf(o[2], 0.f);
+        float2 o[3];
+        conv3_pair<SX_W, SX_H * SX_W>(sx + rr * SX_W + cc + 1, wt.w1, wt.b1, o);
+        const bool xin = xx >= 0 && xx < W;
+        const bool in0 = xin && yy >= 0 && yy < H, in1 = xin && yy + 1 >= 0 && yy + 1 < H;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            s1[c * S1_H * S1_W + rr * S1_W + cc] = in0 ? fmaxf(o[c].x, 0.f) : 0.f;
+            s1[c * S1_H * S1_W + (rr + 1) * S1_W + cc] = in1 ? fmaxf(o[c].y, 0.f) : 0.f;
         }
-        s1[idx] = o[0];
-        s1[S1_H * S1_W + idx] = o[1];
-        s1[2 * S1_H * S1_W + idx] = o[2];
     }
     __syncthreads();
     // fea2 = fea1 + relu(bn(conv(fea1))) on the 18x34 region
-    for (int idx = t; idx < S2_H * S2_W; idx += 256) {
-        const int rr = idx / S2_W, cc = idx - rr * S2_W;
+    for (int idx = t; idx < (S2_H / 2) * S2_W; idx += 256) {
+        const int rp = idx / S2_W, cc = idx - rp * S2_W;
+        const int rr = 2 * rp;
         const int yy = y0 - 1 + rr, xx = x0 - 1 + cc;
-        float o[3] = {0.f, 0.f, 0.f};
-        if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-            conv3<S1_W, S1_H * S1_W>(s1 + rr * S1_W + cc, wt.w2, wt.b2, o);
-            const int ctr = (rr + 1) * S1_W + cc + 1;
-            o[0] = s1[ctr] + fmaxf(o[0], 0.f);
-            o[1] = s1[S1_H * S1_W + ctr] + fmaxf(o[1], 0.f);
-            o[2] = s1[2 * S1_H * S1_W + ctr] + fmaxf(o[2], 0.f);
+        float2 o[3];
+        conv3_pair<S1_W, S1_H * S1_W>(s1 + rr * S1_W + cc, wt.w2, wt.b2, o);
+        const bool xin = xx >= 0 && xx < W;
+        const bool in0 = xin && yy >= 0 && yy < H, in1 = xin && yy + 1 >= 0 && yy + 1 < H;
+        const int ctr = (rr + 1) * S1_W + cc + 1;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            s2[c * S2_H * S2_W + rr * S2_W + cc] = in0 ? s1[c * S1_H * S1_W + ctr] + fmaxf(o[c].x, 0.f) : 0.f;
+            s2[c * S2_H * S2_W + (rr + 1) * S2_W + cc] =
+                in1 ? s1[c * S1_H * S1_W + ctr + S1_W] + fmaxf(o[c].y, 0.f) : 0.f;
         }
-        s2[idx] = o[0];
-        s2[S2_H * S2_W + idx] = o[1];
-        s2[2 * S2_H * S2_W + idx] = o[2];
     }
     __syncthreads();
-    for (int idx = t; idx < S_TH * S_TW; idx += 256) {
-        const int rr = idx / S_TW, cc = idx - rr * S_TW;
-        const int yy = y0 + rr, xx = x0 + cc;
-        if (yy < H && xx < W) {
-            float o[3];
-            conv3<S2_W, S2_H * S2_W>(s2 + rr * S2_W + cc, wt.w3, wt.b3, o);
+    for (int idx = t; idx < (S_TH / 2) * S_TW; idx += 256) {
+        const int rp = idx / S_TW, cc = idx - rp * S_TW;
+        const int rr = 2 * rp;
+        const int xx = x0 + cc;
+        if (xx >= W) continue;
+        float2 o[3];
+        conv3_pair<S2_W, S2_H * S2_W>(s2 + rr * S2_W + cc, wt.w3, wt.b3, o);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int yy = y0 + rr + half;
+            if (yy >= H) continue;
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-                const float xin = sx[c * SX_H * SX_W + (rr + 3) * SX_W + cc + 3];
-                const float sg = 1.f / (1.f + expf(-o[c]));
+                const float xin = sx[c * SX_H * SX_W + (rr + half + 3) * SX_W + cc + 4];
+                const float ov = half ? o[c].y : o[c].x;
+                const float sg = 1.f / (1.f + expf(-ov));
                 const float il = fminf(fmaxf(sg + xin, 0.0001f), 1.f);
                 const float rv = fminf(fmaxf(__fdiv_rn(xin, il), 0.f), 1.f);
                 const size_t off = ((size_t)(b * 3 + c)) * plane + (size_t)yy * W + xx;
