@@ -4,26 +4,29 @@
 // an input row r (128 pixels of one strip, all Cin channels) contributes to the three output rows r+1, r, r-1
 // through the filter rows dy = 0, 1, 2, so for every (dx, 16-channel chunk) ONE
 //     tcgen05.mma.cta_group::1.kind::f16   M = 128 pixels, N = 96 = 3 output rows x 32 couts, K = 16
-// accumulates into three ADJACENT 32-column fp32 accumulator blocks of a TMEM ring (bf16 x bf16 -> fp32).
-// The MMA runs in **TS mode**: the activation operand A lives in TMEM (lane = pixel, one 32-bit column = two
-// bf16 channels); only the 3 KB weight tile B is read from shared memory.  With N this small an SS-mode MMA would
-// need more shared-memory bandwidth for A than an SM has.  A 3x3 tap's dx shift cannot be a TMEM lane shift, so the
-// loader warps write three lane-shifted copies (dx = -1, 0, +1) of each input row:
-//     global NHWC bf16 --TMA (4-D tile, 64B swizzle, zero fill outside the image)--> smem ring
-//       --LDS.128 (conflict-free through the swizzle)--> registers --tcgen05.st--> TMEM A slot (3 copies).
-// Rows stream top to bottom inside a strip: no halo recompute in y, one input row lives in TMEM for one MMA batch.
-// An accumulator block is complete after the input row below it has been consumed; the epilogue drains it,
-// re-zeroes it (every MMA accumulates) and hands it back.
+// accumulates into three ADJACENT 32-column fp32 accumulator blocks of a 16-block ring that fills all 512 TMEM
+// columns (bf16 x bf16 -> fp32).  Both operands are read from shared memory (SS mode):
+//   * A = the activation row exactly as TMA wrote it: global NHWC bf16 --cp.async.bulk.tensor (4-D tile of 130
+//     pixels x 32 channels, SWIZZLE_64B, zero fill outside the image = the conv's zero padding)--> smem ring.
+//     The tile IS the canonical K-major SWIZZLE_64B operand layout (one 64-byte row per pixel); a tap's dx shift is
+//     the descriptor start address advanced by dx rows, its 16-channel chunk by 32 bytes.  No register staging,
+//     no im2col, no copies: measured 56 clk per N=96 MMA against 48 clk with A in TMEM (tools/exp/ss_probe.cu),
+//     i.e. the 7 KB of A + B per MMA run at the 128 B/clk shared-memory limit.
+//   * B = the layer's weights, resident in smem as K-major core-matrix tiles [N = dy*32 + cout][K = 16].
+// Rows stream top to bottom inside a strip: no halo recompute in y.  An accumulator block is complete after the
+// input row below it has been consumed; the epilogue drains it, re-zeroes it (every MMA accumulates) and hands it
+// back.
 //
-// Warp roles (576 threads, 1 persistent CTA per SM, 512 TMEM columns):
-//   warps 0-7    loaders, two per TMEM lane quarter, alternating input rows
+// Warp roles (1 persistent CTA per SM):
+//   warps 0-7    epilogue, two per TMEM lane quarter, alternating output rows: tcgen05.ld -> bias + ReLU -> bf16
+//                NHWC store; layer 7: tanh -> `adjust` (NCHW fp32) + the 8-iteration curve on x -> `enhanced`
 //   warp  8      MMA issuer: warp-uniform control flow, one elected lane issues tcgen05.mma / tcgen05.commit
-//                (-> empty[slot], acc_full[block])
+//                (-> stage_empty[s], acc_full[block])
 //   warp  9      TMA producer: one elected lane, expect_tx + cp.async.bulk.tensor per input row and source
-//   warps 10-17  epilogue, two per lane quarter, alternating output rows: tcgen05.ld -> bias + ReLU -> bf16 NHWC
-//                store; layer 7: tanh -> `adjust` (NCHW fp32) + the 8-iteration curve on x -> `enhanced`
-// Layer 1 (Cin = 3) runs the same pipeline with K padded to 16 (one chunk): its loaders read the fp32 NCHW input
-// directly (coalesced along x, one row ahead) and rewrite only the two non-zero TMEM columns of each dx copy.
+//   warps 10-17  layer 1 only (Cin = 3): A-tile builders.  The 3 x 3 (dx, channel) taps of a pixel are folded into
+//                K (k = dx*3 + c, padded to 16), so layer 1 is ONE K=16 MMA per input row; the builders read the
+//                fp32 NCHW input (coalesced along x, three rows in flight per group) and write bf16 core-matrix
+//                tiles into the smem ring (generic-proxy stores + fence.proxy.async).
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -35,22 +38,34 @@ namespace b200 {
 using namespace tc;
 
 constexpr int TC_M = 128;            // pixels per strip = MMA M = TMEM lanes
-constexpr int TC_NSLOT = 3;          // TMEM A slots (input rows)
-constexpr int TC_NB = 6;             // accumulator blocks (32 columns each) in the TMEM ring; even
-constexpr int TC_ACC_COLS = TC_NB * 32;
-constexpr int TC_NST = 8;            // TMA smem stages (input rows); even
+constexpr int TC_NB = 16;            // accumulator blocks (32 columns each): the whole TMEM; even
 constexpr int TC_SPX = TC_M + 2;     // staged pixels per row (halo of 1 on each side)
 constexpr int TC_SRC_BYTES = TC_SPX * 64;          // TMA box bytes per source per row (8320)
 constexpr int TC_SRC_STRIDE = 8704;                // smem bytes per source per stage (17 x 512: keeps the swizzle phase)
-constexpr int TC_THREADS = 576;
-static_assert((2 * TC_NST + 2 * TC_NSLOT + 2 * TC_NB) * 8 <= 384, "mbarrier area");
+constexpr int TC_A1_BYTES = 4096;                  // layer 1: one [128 px][K = 16] bf16 tile per input row
+constexpr int TC_BAR_BYTES = 512;
+constexpr int TC_MIN_SMEM = 120 * 1024;            // > half an SM: one CTA per SM (each CTA owns all of TMEM)
+
+template <int NSRC, bool FIRST>
+__host__ __device__ constexpr int tc_nst() {       // smem stages (input rows in flight)
+    return FIRST ? 8 : (NSRC == 2 ? 10 : 16);
+}
+template <int NSRC, bool FIRST>
+__host__ __device__ constexpr int tc_stage_bytes() {
+    return FIRST ? TC_A1_BYTES : NSRC * TC_SRC_STRIDE;
+}
+template <bool FIRST>
+__host__ __device__ constexpr int tc_threads() {
+    return FIRST ? 576 : 320;
+}
 
 // packed weights per layer: B tiles then 32 fp32 biases.
-//   per (dx, kc) one tile [N=96 = dy*32 + cout][K=16] (3 KB); layer 0 has one K chunk (3 channels, zero padded)
+//   layers 2-7: per (dx, kc) one tile [N=96 = dy*32 + cout][K=16] (3 KB);  layer 1: ONE tile with k = dx*3 + cin
 // element (n, kk) of a tile at byte (n/8)*256 + (kk/8)*128 + (n%8)*16 + (kk%8)*2   (K-major core matrices,
 // LBO = 128, SBO = 256)
 __host__ __device__ constexpr int tc_kc(int l) { return l == 0 ? 1 : (l <= 3 ? 2 : 4); }
-__host__ __device__ constexpr int tc_wbytes(int l) { return 3 * tc_kc(l) * 3072; }
+__host__ __device__ constexpr int tc_ntiles(int l) { return l == 0 ? 1 : 3 * tc_kc(l); }
+__host__ __device__ constexpr int tc_wbytes(int l) { return tc_ntiles(l) * 3072; }
 __host__ __device__ constexpr int tc_layer_bytes(int l) { return tc_wbytes(l) + 128; }
 __host__ __device__ constexpr int tc_layer_offset(int l) {
     int o = 0;
@@ -71,14 +86,20 @@ __global__ void dce_tc_pack_kernel(TcPackArgs a, uint8_t* __restrict__ packed, i
     const int cout = l == 6 ? cout_last : 32;
     uint8_t* base = packed + tc_layer_offset(l);
     __nv_bfloat16* tiles = reinterpret_cast<__nv_bfloat16*>(base);
-    const int n_el = 3 * kc_n * 1536;
+    const int n_el = tc_ntiles(l) * 1536;
     for (int i = threadIdx.x; i < n_el; i += blockDim.x) {
         const int tile = i / 1536, e = i - tile * 1536;
-        const int dx = tile / kc_n, kc = tile - dx * kc_n;
         const int n = e >> 4, kk = e & 15;  // n = dy*32 + cout
         const int dy = n >> 5, oc = n & 31;
-        const int ci = kc * 16 + kk;
-        const float v = (oc < cout && ci < cin) ? a.w[l][(oc * cin + ci) * 9 + dy * 3 + dx] : 0.f;
+        float v = 0.f;
+        if (l == 0) {
+            const int dx = kk / 3, ci = kk - dx * 3;  // k = dx*3 + cin, k >= 9 is padding
+            if (kk < 9 && oc < cout) v = a.w[0][(oc * 3 + ci) * 9 + dy * 3 + dx];
+        } else {
+            const int dx = tile / kc_n, kc = tile - dx * kc_n;
+            const int ci = kc * 16 + kk;
+            if (oc < cout && ci < cin) v = a.w[l][(oc * cin + ci) * 9 + dy * 3 + dx];
+        }
         tiles[tile * 1536 + (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7)] = __float2bfloat16_rn(v);
     }
     float* bias = reinterpret_cast<float*>(base + tc_wbytes(l));
@@ -97,42 +118,49 @@ struct TcArgs {
 
 template <int NSRC, bool FIRST>
 __host__ __device__ constexpr int tc_wbytes_t() {
-    return FIRST ? 3 * 3072 : 3 * 2 * NSRC * 3072;
+    return FIRST ? 3072 : 3 * 2 * NSRC * 3072;
 }
 template <int NSRC, bool FIRST>
 constexpr int tc_smem_bytes() {
-    // weights | bias 128 | barriers 384 | tmem addr 16 | pad to 1024 | stages
-    return tc_wbytes_t<NSRC, FIRST>() + 128 + 384 + 16 + 1024 +
-           (FIRST ? 0 : TC_NST * NSRC * TC_SRC_STRIDE);
+    // weights | bias 128 | barriers | tmem addr 16 | pad to 1024 | stages
+    constexpr int need = tc_wbytes_t<NSRC, FIRST>() + 128 + TC_BAR_BYTES + 16 + 1024 +
+                         tc_nst<NSRC, FIRST>() * tc_stage_bytes<NSRC, FIRST>();
+    return need < TC_MIN_SMEM ? TC_MIN_SMEM : need;
 }
 
 __device__ __forceinline__ int tc_pos(uint32_t o) { return TC_NB - 1 - (int)(o % TC_NB); }
 
+// flattened (item, row) iterator of one layer-1 builder group: every second input row of this CTA's items
+struct TcRowIt {
+    int item, ri, nin, b, y0, x0;
+    uint32_t g;  // running input-row index of this CTA (ring position)
+    bool valid;
+};
+
 template <int NSRC, bool FIRST, bool LAST>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(tc_threads<FIRST>(), 1)
 dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1) {
-    constexpr int KC = FIRST ? 1 : 2 * NSRC;            // K chunks of 16 per (dy, dx)
+    constexpr int KC = FIRST ? 1 : 2 * NSRC;            // K chunks of 16 per dx
     constexpr int NDY = 3;                              // output rows one input row feeds
-    constexpr int NDX = 3;
+    constexpr int NDX = FIRST ? 1 : 3;                  // layer 1 folds dx into K
+    constexpr int NST = tc_nst<NSRC, FIRST>();
+    constexpr int STAGE = tc_stage_bytes<NSRC, FIRST>();
     constexpr int WBYTES = tc_wbytes_t<NSRC, FIRST>();
     constexpr int TILE = 3072;
-    constexpr int COPY_COLS = FIRST ? 8 : 16 * NSRC;    // TMEM columns of one dx copy
-    constexpr int SLOT_COLS = NDX * COPY_COLS;
-    static_assert(TC_ACC_COLS + TC_NSLOT * SLOT_COLS <= 512, "TMEM budget");
+    constexpr int NTHREADS = tc_threads<FIRST>();
+    static_assert((2 * NST + 2 * TC_NB) * 8 <= TC_BAR_BYTES, "mbarrier area");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* s_w = smem_raw;
     float* s_bias = reinterpret_cast<float*>(smem_raw + WBYTES);
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(smem_raw + WBYTES + 128);
-    uint64_t* stage_full = s_bar;                                   // [NST]   TMA complete_tx (1 arrival + bytes)
-    uint64_t* stage_empty = s_bar + TC_NST;                         // [NST]   loaders of one parity (128)
-    uint64_t* full = s_bar + 2 * TC_NST;                            // [NSLOT] loaders of one parity (128)
-    uint64_t* empty = s_bar + 2 * TC_NST + TC_NSLOT;                // [NSLOT] MMA commit (1)
-    uint64_t* acc_full = s_bar + 2 * TC_NST + 2 * TC_NSLOT;         // [NB]    MMA commit (1)
-    uint64_t* acc_empty = s_bar + 2 * TC_NST + 2 * TC_NSLOT + TC_NB;  // [NB]  epilogue warps of one parity (128)
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + WBYTES + 128 + 384);
+    uint64_t* stage_full = s_bar;                       // [NST] TMA complete_tx (1 + bytes) / 128 builder threads
+    uint64_t* stage_empty = s_bar + NST;                // [NST] MMA commit (1)
+    uint64_t* acc_full = s_bar + 2 * NST;               // [NB]  MMA commit (1)
+    uint64_t* acc_empty = s_bar + 2 * NST + TC_NB;      // [NB]  epilogue warps of one parity (128)
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + WBYTES + 128 + TC_BAR_BYTES);
     // stage area: 1024-byte aligned in the shared window (swizzle phase = address bits 7-8)
-    const uint32_t stage_u32 = (smem_u32(smem_raw + WBYTES + 128 + 384 + 16) + 1023u) & ~1023u;
+    const uint32_t stage_u32 = (smem_u32(smem_raw + WBYTES + 128 + TC_BAR_BYTES + 16) + 1023u) & ~1023u;
     uint8_t* s_stage = smem_raw + (stage_u32 - smem_u32(smem_raw));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -143,18 +171,14 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     {
         const uint4* g = reinterpret_cast<const uint4*>(args.wpack);
         uint4* s = reinterpret_cast<uint4*>(smem_raw);
-        for (int i = tid; i < (WBYTES + 128) / 16; i += TC_THREADS) s[i] = __ldg(g + i);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // B tiles are read through the async proxy
+        for (int i = tid; i < (WBYTES + 128) / 16; i += NTHREADS) s[i] = __ldg(g + i);
+        fence_proxy_async_smem();  // B tiles are read through the async proxy
     }
     if (warp == 8) {
         if (lane == 0) {
-            for (int i = 0; i < TC_NST; ++i) {
-                mbar_init(&stage_full[i], 1);
-                mbar_init(&stage_empty[i], 128);
-            }
-            for (int i = 0; i < TC_NSLOT; ++i) {
-                mbar_init(&full[i], 128);
-                mbar_init(&empty[i], 1);
+            for (int i = 0; i < NST; ++i) {
+                mbar_init(&stage_full[i], FIRST ? 128 : 1);
+                mbar_init(&stage_empty[i], 1);
             }
             for (int i = 0; i < TC_NB; ++i) {
                 mbar_init(&acc_full[i], 1);
@@ -173,8 +197,8 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     __syncthreads();
     tc_fence_after();
     const uint32_t tbase = *s_tmem;
-    if (warp >= 10 && warp < 14) {  // every MMA accumulates: start from zeroed accumulator blocks
-        const uint32_t tl = tbase + ((uint32_t)((warp & 3) * 32) << 16);
+    if (warp < 4) {  // every MMA accumulates: start from zeroed accumulator blocks
+        const uint32_t tl = tbase + ((uint32_t)(warp * 32) << 16);
         for (int i = 0; i < TC_NB; ++i) tmem_zero32(tl + i * 32);
         tc_wait_st();
     }
@@ -183,209 +207,8 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     tc_fence_after();
 
     if (warp < 8) {
-        // =========================== LOADERS ===========================
-        const int q = warp & 3, par = warp >> 2;
-        const int t = q * 32 + lane;  // pixel in strip = TMEM lane
-        const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16) + TC_ACC_COLS;
-        uint32_t g_base = 0;
-        if constexpr (FIRST) {
-            // Layer 1: Cin = 3, K padded to 16 (8 TMEM columns per dx copy, only the first two are non-zero and are
-            // the only ones rewritten).  Each lane reads its 3 x 3 (dx, channel) fp32 values straight from the NCHW
-            // input (coalesced along x), one row ahead of the one it is converting.
-            for (int sl = par; sl < TC_NSLOT; sl += 2) {  // zero the padding columns of every slot once
-                const uint32_t z[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-                tmem_st16(tlane + sl * SLOT_COLS, z);
-                tmem_st16(tlane + sl * SLOT_COLS + 8, z);
-            }
-            tc_wait_st();
-            named_bar_sync(1, 256);
-            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-                const int strip = item % args.nstrip;
-                const int seg = (item / args.nstrip) % args.nseg;
-                const int b = item / (args.nstrip * args.nseg);
-                const int y0 = seg * R, xx = strip * TC_M + t;
-                const int nin = min(R, H - y0) + 2;
-                const float* xin = args.x + (size_t)b * 3 * H * W;
-                auto load_row = [&](int y, float (&v)[9]) {
-                    const bool yok = y >= 0 && y < H;
-#pragma unroll
-                    for (int dx = 0; dx < 3; ++dx) {
-                        const int xs = xx + dx - 1;
-                        const bool ok = yok && xs >= 0 && xs < W;
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) v[dx * 3 + c] = ok ? __ldg(xin + ((size_t)c * H + y) * W + xs) : 0.f;
-                    }
-                };
-                int ri = (int)((g_base ^ (uint32_t)par) & 1);  // first input row of this item with (g & 1) == par
-                float nxt[9];
-                if (ri < nin) load_row(y0 - 1 + ri, nxt);
-                for (; ri < nin; ri += 2) {
-                    float cur[9];
-#pragma unroll
-                    for (int i = 0; i < 9; ++i) cur[i] = nxt[i];
-                    if (ri + 2 < nin) load_row(y0 - 1 + ri + 2, nxt);
-                    const uint32_t g = g_base + ri;
-                    const uint32_t slot = g % TC_NSLOT, use = g / TC_NSLOT;
-                    if (use > 0) mbar_wait(&empty[slot], (use - 1) & 1);
-                    tc_fence_after();
-#pragma unroll
-                    for (int dx = 0; dx < 3; ++dx) {
-                        __nv_bfloat162 h0 = __floats2bfloat162_rn(cur[dx * 3], cur[dx * 3 + 1]);
-                        __nv_bfloat162 h1 = __floats2bfloat162_rn(cur[dx * 3 + 2], 0.f);
-                        tmem_st2(tlane + slot * SLOT_COLS + dx * COPY_COLS, *reinterpret_cast<uint32_t*>(&h0),
-                                 *reinterpret_cast<uint32_t*>(&h1));
-                    }
-                    tc_wait_st();
-                    tc_fence_before();
-                    mbar_arrive(&full[slot]);
-                }
-                g_base += nin;
-            }
-        } else {
-            // per-thread swizzled smem offsets of the three pixels (dx copies) this lane feeds:
-            // TMA SWIZZLE_64B stores 16-byte chunk c of pixel p at  p*64 + ((c ^ ((p >> 1) & 3)) << 4)
-            uint32_t poff[3], psw[3];
-#pragma unroll
-            for (int dx = 0; dx < 3; ++dx) {
-                const int p = t + dx;
-                poff[dx] = p * 64;
-                psw[dx] = (p >> 1) & 3;
-            }
-            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-                const int seg = (item / args.nstrip) % args.nseg;
-                const int nin = min(R, H - seg * R) + 2;
-                for (int ri = 0; ri < nin; ++ri) {
-                    const uint32_t g = g_base + ri;
-                    if ((int)(g & 1) != par) continue;
-                    const uint32_t s = g % TC_NST, us = g / TC_NST;
-                    mbar_wait(&stage_full[s], us & 1);
-                    const uint32_t slot = g % TC_NSLOT, use = g / TC_NSLOT;
-                    if (use > 0) mbar_wait(&empty[slot], (use - 1) & 1);
-                    tc_fence_after();
-                    const uint8_t* st = s_stage + s * (NSRC * TC_SRC_STRIDE);
-#pragma unroll
-                    for (int src = 0; src < NSRC; ++src) {
-#pragma unroll
-                        for (int dx = 0; dx < 3; ++dx) {
-                            const uint8_t* pp = st + src * TC_SRC_STRIDE + poff[dx];
-                            const uint4 q0 = *reinterpret_cast<const uint4*>(pp + ((0 ^ psw[dx]) << 4));
-                            const uint4 q1 = *reinterpret_cast<const uint4*>(pp + ((1 ^ psw[dx]) << 4));
-                            const uint4 q2 = *reinterpret_cast<const uint4*>(pp + ((2 ^ psw[dx]) << 4));
-                            const uint4 q3 = *reinterpret_cast<const uint4*>(pp + ((3 ^ psw[dx]) << 4));
-                            const uint32_t pk[16] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w,
-                                                     q2.x, q2.y, q2.z, q2.w, q3.x, q3.y, q3.z, q3.w};
-                            tmem_st16(tlane + slot * SLOT_COLS + dx * COPY_COLS + src * 16, pk);
-                        }
-                    }
-                    tc_wait_st();
-                    tc_fence_before();
-                    mbar_arrive(&full[slot]);
-                    mbar_arrive(&stage_empty[s]);
-                }
-                g_base += nin;
-            }
-        }
-    } else if (warp == 9) {
-        // =========================== TMA PRODUCER ===========================
-        // warp-uniform control flow, one elected lane issues expect_tx + the bulk tensor copies
-        if constexpr (!FIRST) {
-            const bool leader = elect_one();
-            uint32_t s = 0, spar = 0;  // stage ring position / phase parity of the NEXT fill
-            bool first_round = true;
-            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-                const int strip = item % args.nstrip;
-                const int seg = (item / args.nstrip) % args.nseg;
-                const int b = item / (args.nstrip * args.nseg);
-                const int y0 = seg * R, x0 = strip * TC_M;
-                const int nin = min(R, H - y0) + 2;
-                for (int ri = 0; ri < nin; ++ri) {
-                    if (!first_round) mbar_wait(&stage_empty[s], spar ^ 1);
-                    if (leader) {
-                        mbar_arrive_expect_tx(&stage_full[s], NSRC * TC_SRC_BYTES);
-                        const uint32_t dst = stage_u32 + s * (NSRC * TC_SRC_STRIDE);
-                        tma_load_4d(dst, &tm0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
-                        if (NSRC == 2)
-                            tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
-                    }
-                    __syncwarp();
-                    if (++s == TC_NST) {
-                        s = 0;
-                        spar ^= 1;
-                        first_round = false;
-                    }
-                }
-            }
-        }
-    } else if (warp == 8) {
-        // =========================== MMA ISSUER ===========================
-        // The whole warp runs the (warp-uniform) control flow so that addresses and descriptors stay in uniform
-        // registers; one elected lane issues every tcgen05.mma / tcgen05.commit.
-        constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
-        constexpr uint32_t IDESC_FULL = IDESC0 | ((uint32_t)(NDY * 32 >> 3) << 17);
-        const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_w), 128, 256);
-        const bool leader = elect_one();
-        uint32_t slot = 0, spar = 0;  // A-slot ring position and phase parity
-        uint32_t o_base = 0;
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int seg = (item / args.nstrip) % args.nseg;
-            const int nout = min(R, H - seg * R);
-            const int nin = nout + NDY - 1;
-            uint32_t on = o_base % TC_NB, upar = (o_base / TC_NB) & 1;  // block ring position / use parity of row o_base+ri
-            for (int ri = 0; ri < nin; ++ri) {
-                mbar_wait(&full[slot], spar);
-                const int pn = TC_NB - 1 - (int)on;  // block opened by this input row (output row ri, dy = 0)
-                if (ri < nout && o_base + ri >= TC_NB) mbar_wait(&acc_empty[pn], upar ^ 1);
-                tc_fence_after();
-                const uint32_t abase = tbase + TC_ACC_COLS + slot * SLOT_COLS;
-                if (ri >= NDY - 1 && ri < nout && pn + NDY <= TC_NB) {
-                    // interior row, no ring wrap: one N = 32*NDY MMA per (dx, kc)
-                    if (leader) {
-                        const uint32_t d = tbase + pn * 32;
-#pragma unroll
-                        for (int dx = 0; dx < NDX; ++dx)
-#pragma unroll
-                            for (int kc = 0; kc < KC; ++kc)
-                                mma_ts(d, abase + dx * COPY_COLS + kc * 8,
-                                       bdesc0 + (uint64_t)(((dx * KC + kc) * TILE) >> 4), IDESC_FULL, 1u);
-                    }
-                } else if (leader) {
-                    // segment borders (output row j = ri - dy must lie in [0, nout)) and ring wrap: split into groups
-                    int dy = max(0, ri - (nout - 1));
-                    const int dy_hi = min(NDY - 1, ri);
-                    while (dy <= dy_hi) {
-                        const int p0 = (pn + dy) % TC_NB;
-                        const int cnt = min(dy_hi - dy + 1, TC_NB - p0);
-                        const uint32_t idesc = IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17);
-                        const uint32_t d = tbase + p0 * 32;
-                        const uint64_t bd = bdesc0 + (uint64_t)((dy * 1024) >> 4);
-#pragma unroll
-                        for (int dx = 0; dx < NDX; ++dx)
-#pragma unroll
-                            for (int kc = 0; kc < KC; ++kc)
-                                mma_ts(d, abase + dx * COPY_COLS + kc * 8,
-                                       bd + (uint64_t)(((dx * KC + kc) * TILE) >> 4), idesc, 1u);
-                        dy += cnt;
-                    }
-                }
-                if (leader) {
-                    tc_commit(&empty[slot]);
-                    if (ri >= NDY - 1) tc_commit(&acc_full[(pn + NDY - 1) % TC_NB]);
-                }
-                __syncwarp();
-                if (++slot == TC_NSLOT) {
-                    slot = 0;
-                    spar ^= 1;
-                }
-                if (++on == TC_NB) {
-                    on = 0;
-                    upar ^= 1;
-                }
-            }
-            o_base += nout;
-        }
-    } else {
         // =========================== EPILOGUE ===========================
-        const int q = warp & 3, par = (warp - 10) >> 2;
+        const int q = warp & 3, par = warp >> 2;
         const int m = q * 32 + lane;
         const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
         float bias[32];
@@ -399,9 +222,8 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
             const int b = item / (args.nstrip * args.nseg);
             const int y0 = seg * R, xx = strip * TC_M + m;
             const int nout = min(R, H - y0);
-            for (int j = 0; j < nout; ++j) {
+            for (int j = (int)((o_base ^ (uint32_t)par) & 1); j < nout; j += 2) {
                 const uint32_t o = o_base + j;
-                if ((int)(o & 1) != par) continue;
                 const int p = tc_pos(o);
                 mbar_wait(&acc_full[p], (o / TC_NB) & 1);
                 tc_fence_after();
@@ -453,6 +275,183 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                 }
             }
             o_base += nout;
+        }
+    } else if (warp == 8) {
+        // =========================== MMA ISSUER ===========================
+        // The whole warp runs the (warp-uniform) control flow so that addresses and descriptors stay in uniform
+        // registers; one elected lane issues every tcgen05.mma / tcgen05.commit.
+        constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
+        constexpr uint32_t IDESC_FULL = IDESC0 | ((uint32_t)(NDY * 32 >> 3) << 17);
+        const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_w), 128, 256);
+        // A descriptor of stage 0, tap (dx = 0, chunk 0); a stage / source / dx / chunk offset is added to the
+        // 14-bit (address >> 4) field, which cannot carry: the whole window is < 256 KB
+        const uint64_t adesc0 = FIRST ? smem_desc_kmajor(stage_u32, 128, 256) : smem_desc_sw64(stage_u32);
+        const bool leader = elect_one();
+        uint32_t s = 0, sph = 0;  // stage ring position and phase parity
+        uint32_t o_base = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int seg = (item / args.nstrip) % args.nseg;
+            const int nout = min(R, H - seg * R);
+            const int nin = nout + NDY - 1;
+            uint32_t on = o_base % TC_NB, upar = (o_base / TC_NB) & 1;  // block ring position / use parity of row o_base+ri
+            for (int ri = 0; ri < nin; ++ri) {
+                mbar_wait(&stage_full[s], sph);
+                const int pn = TC_NB - 1 - (int)on;  // block opened by this input row (output row ri, dy = 0)
+                if (ri < nout && o_base + ri >= TC_NB) mbar_wait(&acc_empty[pn], upar ^ 1);
+                tc_fence_after();
+                const uint64_t adesc = adesc0 + (uint64_t)((s * STAGE) >> 4);
+                auto a_of = [&](int dx, int kc) -> uint64_t {  // compile-time offsets after unrolling
+                    return FIRST ? adesc : adesc + (uint64_t)(((kc >> 1) * TC_SRC_STRIDE + dx * 64 + (kc & 1) * 32) >> 4);
+                };
+                if (ri >= NDY - 1 && ri < nout && pn + NDY <= TC_NB) {
+                    // interior row, no ring wrap: one N = 32*NDY MMA per (dx, kc)
+                    if (leader) {
+                        const uint32_t d = tbase + pn * 32;
+#pragma unroll
+                        for (int dx = 0; dx < NDX; ++dx)
+#pragma unroll
+                            for (int kc = 0; kc < KC; ++kc)
+                                mma_ss(d, a_of(dx, kc), bdesc0 + (uint64_t)(((dx * KC + kc) * TILE) >> 4), IDESC_FULL, 1u);
+                    }
+                } else if (leader) {
+                    // segment borders (output row j = ri - dy must lie in [0, nout)) and ring wrap: split into groups
+                    int dy = max(0, ri - (nout - 1));
+                    const int dy_hi = min(NDY - 1, ri);
+                    while (dy <= dy_hi) {
+                        const int p0 = (pn + dy) % TC_NB;
+                        const int cnt = min(dy_hi - dy + 1, TC_NB - p0);
+                        const uint32_t idesc = IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17);
+                        const uint32_t d = tbase + p0 * 32;
+                        const uint64_t bd = bdesc0 + (uint64_t)((dy * 1024) >> 4);
+#pragma unroll
+                        for (int dx = 0; dx < NDX; ++dx)
+#pragma unroll
+                            for (int kc = 0; kc < KC; ++kc)
+                                mma_ss(d, a_of(dx, kc), bd + (uint64_t)(((dx * KC + kc) * TILE) >> 4), idesc, 1u);
+                        dy += cnt;
+                    }
+                }
+                if (leader) {
+                    tc_commit(&stage_empty[s]);
+                    if (ri >= NDY - 1) tc_commit(&acc_full[(pn + NDY - 1) % TC_NB]);
+                }
+                __syncwarp();
+                if (++s == NST) {
+                    s = 0;
+                    sph ^= 1;
+                }
+                if (++on == TC_NB) {
+                    on = 0;
+                    upar ^= 1;
+                }
+            }
+            o_base += nout;
+        }
+    } else if (warp == 9) {
+        // =========================== TMA PRODUCER ===========================
+        // warp-uniform control flow, one elected lane issues expect_tx + the bulk tensor copies
+        if constexpr (!FIRST) {
+            const bool leader = elect_one();
+            uint32_t s = 0, spar = 0;  // stage ring position / phase parity of the NEXT fill
+            bool first_round = true;
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+                const int strip = item % args.nstrip;
+                const int seg = (item / args.nstrip) % args.nseg;
+                const int b = item / (args.nstrip * args.nseg);
+                const int y0 = seg * R, x0 = strip * TC_M;
+                const int nin = min(R, H - y0) + 2;
+                for (int ri = 0; ri < nin; ++ri) {
+                    if (!first_round) mbar_wait(&stage_empty[s], spar ^ 1);
+                    if (leader) {
+                        mbar_arrive_expect_tx(&stage_full[s], NSRC * TC_SRC_BYTES);
+                        const uint32_t dst = stage_u32 + s * STAGE;
+                        tma_load_4d(dst, &tm0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                        if (NSRC == 2)
+                            tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                    }
+                    __syncwarp();
+                    if (++s == NST) {
+                        s = 0;
+                        spar ^= 1;
+                        first_round = false;
+                    }
+                }
+            }
+        }
+    } else {
+        // =========================== LAYER-1 A-TILE BUILDERS ===========================
+        if constexpr (FIRST) {
+            const int grp = (warp - 10) >> 2;                 // rows with (g & 1) == grp
+            const int t = ((warp - 10) & 3) * 32 + lane;      // pixel in strip = A-tile row
+            auto setup = [&](TcRowIt& it) {
+                it.valid = it.item < n_items;
+                if (!it.valid) return;
+                const int strip = it.item % args.nstrip;
+                const int seg = (it.item / args.nstrip) % args.nseg;
+                it.b = it.item / (args.nstrip * args.nseg);
+                it.y0 = seg * R;
+                it.x0 = strip * TC_M;
+                it.nin = min(R, H - it.y0) + 2;
+            };
+            auto step = [&](TcRowIt& it) {  // two rows further in this CTA's flattened row sequence
+                it.ri += 2;
+                it.g += 2;
+                while (it.valid && it.ri >= it.nin) {
+                    it.ri -= it.nin;
+                    it.item += gridDim.x;
+                    setup(it);
+                }
+            };
+            auto load_row = [&](const TcRowIt& it, float (&v)[9]) {
+                if (!it.valid) return;
+                const int y = it.y0 - 1 + it.ri;
+                const bool yok = y >= 0 && y < H;
+                const float* xin = args.x + (size_t)it.b * 3 * H * W;
+#pragma unroll
+                for (int dx = 0; dx < 3; ++dx) {
+                    const int xs = it.x0 + t + dx - 1;
+                    const bool ok = yok && xs >= 0 && xs < W;
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) v[dx * 3 + c] = ok ? __ldg(xin + ((size_t)c * H + y) * W + xs) : 0.f;
+                }
+            };
+            auto emit = [&](const TcRowIt& it, const float (&v)[9]) {
+                const uint32_t s = it.g % NST, lap = it.g / NST;
+                if (lap > 0) mbar_wait(&stage_empty[s], (lap - 1) & 1);
+                auto pk = [](float a, float b) {
+                    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+                    return *reinterpret_cast<uint32_t*>(&h);
+                };
+                uint8_t* row = s_stage + s * STAGE + (t >> 3) * 256 + (t & 7) * 16;
+                *reinterpret_cast<uint4*>(row) = make_uint4(pk(v[0], v[1]), pk(v[2], v[3]), pk(v[4], v[5]), pk(v[6], v[7]));
+                *reinterpret_cast<uint4*>(row + 128) = make_uint4(pk(v[8], 0.f), 0u, 0u, 0u);
+                fence_proxy_async_smem();
+                mbar_arrive(&stage_full[s]);
+            };
+            TcRowIt cv;
+            cv.item = blockIdx.x;
+            cv.ri = grp;
+            cv.g = (uint32_t)grp;
+            cv.nin = 0;
+            cv.b = cv.y0 = cv.x0 = 0;
+            setup(cv);  // nin >= 3 > grp
+            TcRowIt ld = cv;
+            float buf[3][9];
+            load_row(ld, buf[0]);
+            step(ld);
+            load_row(ld, buf[1]);
+            step(ld);
+            while (cv.valid) {
+#pragma unroll
+                for (int u = 0; u < 3; ++u) {
+                    if (cv.valid) {
+                        load_row(ld, buf[(u + 2) % 3]);
+                        step(ld);
+                        emit(cv, buf[u]);
+                        step(cv);
+                    }
+                }
+            }
         }
     }
 
@@ -523,7 +522,7 @@ static int tc_launch(const TcArgs& a, const void* s0, const void* s1, cudaStream
     }
     const long long items = (long long)a.B * a.nseg * a.nstrip;
     const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
-    kern<<<grid, TC_THREADS, smem, s>>>(a, m0, m1);
+    kern<<<grid, tc_threads<FIRST>(), smem, s>>>(a, m0, m1);
     return launch_status();
 }
 

@@ -85,6 +85,27 @@ __device__ __forceinline__ uint64_t smem_desc_kmajor(uint32_t saddr, uint32_t lb
            ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46);
 }
 
+// Shared-memory matrix descriptor for a K-major operand in the TMA SWIZZLE_64B layout: rows of 64 bytes (32 bf16),
+// 8-row groups 512 bytes apart (SBO), 16-byte chunks XOR-ed with address bits 7-8.  The swizzle is a function of the
+// absolute shared-memory address, so the start address may be advanced by whole rows (64 B) or by 32 B (the second
+// K=16 half of a row) without a base offset (measured: tools/exp/utccp_probe.cu, tools/exp/ss_probe.cu).
+__device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(512 >> 4) << 32) | (1ull << 46) |
+           (4ull << 61);
+}
+
+// ---- MMA: D[tmem] (+)= A[smem] * B[smem]   (cta_group::1, kind::f16, issued by ONE thread) -------
+__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                       uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+        :
+        : "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(0u)
+        : "memory");
+}
+
 // ---- MMA: D[tmem] (+)= A[tmem] * B[smem]   (cta_group::1, kind::f16, issued by ONE thread) -------
 __device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
                                        uint32_t accumulate) {
@@ -158,6 +179,7 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

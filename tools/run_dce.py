@@ -13,7 +13,8 @@ dev = torch.device("cuda:0")
 m = P.ZeroDCE_RE(precision=prec).to(dev)
 g = torch.Generator(device=dev).manual_seed(1)
 x = (0.02 + 0.3 * torch.rand(frames, 3, 1080, 1920, device=dev, generator=g)).contiguous()
-m({"image": x})
+for _ in range(3):
+    out = m({"image": x})
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
