@@ -42,13 +42,16 @@ constexpr int TC_NB = 16;            // accumulator blocks (32 columns each): th
 constexpr int TC_SPX = TC_M + 2;     // staged pixels per row (halo of 1 on each side)
 constexpr int TC_SRC_BYTES = TC_SPX * 64;          // TMA box bytes per source per row (8320)
 constexpr int TC_SRC_STRIDE = 8704;                // smem bytes per source per stage (17 x 512: keeps the swizzle phase)
-constexpr int TC_A1_BYTES = 4096;                  // layer 1: one [128 px][K = 16] bf16 tile per input row
+constexpr int TC_A1_SBO = 272;                     // layer 1 A tile: 8-row group pitch (256 + 16: conflict-free stores)
+constexpr int TC_A1_BYTES = 16 * TC_A1_SBO;        // layer 1: one [128 px][K = 16] bf16 tile per input row
 constexpr int TC_BAR_BYTES = 512;
+constexpr int TC_OUT_BYTES = TC_M * 64;            // one output row tile [128 px][32 ch] bf16 (TMA-store staging)
+constexpr int TC_NOUT = 3;                         // staging tiles per epilogue parity group
 constexpr int TC_MIN_SMEM = 120 * 1024;            // > half an SM: one CTA per SM (each CTA owns all of TMEM)
 
 template <int NSRC, bool FIRST>
 __host__ __device__ constexpr int tc_nst() {       // smem stages (input rows in flight)
-    return FIRST ? 8 : (NSRC == 2 ? 10 : 16);
+    return NSRC == 2 ? 8 : 16;
 }
 template <int NSRC, bool FIRST>
 __host__ __device__ constexpr int tc_stage_bytes() {
@@ -120,11 +123,11 @@ template <int NSRC, bool FIRST>
 __host__ __device__ constexpr int tc_wbytes_t() {
     return FIRST ? 3072 : 3 * 2 * NSRC * 3072;
 }
-template <int NSRC, bool FIRST>
+template <int NSRC, bool FIRST, bool LAST>
 constexpr int tc_smem_bytes() {
-    // weights | bias 128 | barriers | tmem addr 16 | pad to 1024 | stages
+    // weights | bias 128 | barriers | tmem addr 16 | pad to 1024 | output staging (2 x TC_NOUT tiles) | stages
     constexpr int need = tc_wbytes_t<NSRC, FIRST>() + 128 + TC_BAR_BYTES + 16 + 1024 +
-                         tc_nst<NSRC, FIRST>() * tc_stage_bytes<NSRC, FIRST>();
+                         (LAST ? 0 : 2 * TC_NOUT * TC_OUT_BYTES) + tc_nst<NSRC, FIRST>() * tc_stage_bytes<NSRC, FIRST>();
     return need < TC_MIN_SMEM ? TC_MIN_SMEM : need;
 }
 
@@ -139,7 +142,8 @@ struct TcRowIt {
 
 template <int NSRC, bool FIRST, bool LAST>
 __global__ void __launch_bounds__(tc_threads<FIRST>(), 1)
-dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1) {
+dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
+                    const __grid_constant__ CUtensorMap tmo) {
     constexpr int KC = FIRST ? 1 : 2 * NSRC;            // K chunks of 16 per dx
     constexpr int NDY = 3;                              // output rows one input row feeds
     constexpr int NDX = FIRST ? 1 : 3;                  // layer 1 folds dx into K
@@ -154,13 +158,15 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     uint8_t* s_w = smem_raw;
     float* s_bias = reinterpret_cast<float*>(smem_raw + WBYTES);
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(smem_raw + WBYTES + 128);
-    uint64_t* stage_full = s_bar;                       // [NST] TMA complete_tx (1 + bytes) / 128 builder threads
+    uint64_t* stage_full = s_bar;                       // [NST] TMA complete_tx (1 + bytes) / the 32 lanes of a builder warp
     uint64_t* stage_empty = s_bar + NST;                // [NST] MMA commit (1)
     uint64_t* acc_full = s_bar + 2 * NST;               // [NB]  MMA commit (1)
     uint64_t* acc_empty = s_bar + 2 * NST + TC_NB;      // [NB]  epilogue warps of one parity (128)
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + WBYTES + 128 + TC_BAR_BYTES);
     // stage area: 1024-byte aligned in the shared window (swizzle phase = address bits 7-8)
-    const uint32_t stage_u32 = (smem_u32(smem_raw + WBYTES + 128 + TC_BAR_BYTES + 16) + 1023u) & ~1023u;
+    const uint32_t out_u32 = (smem_u32(smem_raw + WBYTES + 128 + TC_BAR_BYTES + 16) + 1023u) & ~1023u;
+    uint8_t* s_out = smem_raw + (out_u32 - smem_u32(smem_raw));
+    const uint32_t stage_u32 = out_u32 + (LAST ? 0 : 2 * TC_NOUT * TC_OUT_BYTES);
     uint8_t* s_stage = smem_raw + (stage_u32 - smem_u32(smem_raw));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -177,7 +183,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     if (warp == 8) {
         if (lane == 0) {
             for (int i = 0; i < NST; ++i) {
-                mbar_init(&stage_full[i], FIRST ? 128 : 1);
+                mbar_init(&stage_full[i], FIRST ? 32 : 1);
                 mbar_init(&stage_empty[i], 1);
             }
             for (int i = 0; i < TC_NB; ++i) {
@@ -189,9 +195,10 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         __syncwarp();
         tmem_alloc(s_tmem, 512);
     }
-    if (!FIRST && warp == 9 && lane == 0) {
-        tma_prefetch_desc(&tm0);
+    if (warp == 9 && lane == 0) {
+        if (!FIRST) tma_prefetch_desc(&tm0);
         if (NSRC == 2) tma_prefetch_desc(&tm1);
+        if (!LAST) tma_prefetch_desc(&tmo);
     }
     tc_fence_before();
     __syncthreads();
@@ -214,7 +221,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         float bias[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) bias[i] = s_bias[i];
-        uint32_t o_base = 0;
+        uint32_t o_base = 0, obuf = 0;
         const size_t plane = (size_t)H * W;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int strip = item % args.nstrip;
@@ -235,8 +242,10 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                 tc_fence_before();
                 mbar_arrive(&acc_empty[p]);
                 const int y = y0 + j;
-                if (xx >= W) continue;
                 if constexpr (!LAST) {
+                    // bias + ReLU -> bf16, staged in the TMA SWIZZLE_64B layout (16-byte chunk c of pixel m at
+                    // m*64 + ((c ^ ((m >> 1) & 3)) << 4): conflict-free 128-bit stores), then ONE bulk tensor store
+                    // of the [128 px][32 ch] row by an elected lane; columns >= W are clipped by the TMA unit.
                     uint32_t pk[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
@@ -245,12 +254,25 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                         __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
                         pk[i] = *reinterpret_cast<uint32_t*>(&h);
                     }
-                    uint4* dp = reinterpret_cast<uint4*>(args.dst + (((size_t)b * H + y) * W + xx) * 32);
-                    dp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    dp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-                    dp[2] = make_uint4(pk[8], pk[9], pk[10], pk[11]);
-                    dp[3] = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+                    const uint32_t ob = (uint32_t)(par * TC_NOUT + (int)obuf) * TC_OUT_BYTES;
+                    uint8_t* op = s_out + ob + m * 64;
+                    const int sw = (m >> 1) & 3;
+                    *reinterpret_cast<uint4*>(op + ((0 ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4*>(op + ((1 ^ sw) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
+                    *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+                    fence_proxy_async_smem();
+                    named_bar_sync(1 + par, 128);
+                    if (q == 0 && lane == 0) {
+                        tma_store_4d(&tmo, out_u32 + ob, 0, strip * TC_M, y, b);
+                        tma_store_commit();
+                        // the tile written two rows from now is the one stored one row ago: its read must be over
+                        // before this thread reaches the next row's barrier
+                        tma_store_wait_read<1>();
+                    }
+                    if (++obuf == TC_NOUT) obuf = 0;
                 } else {
+                    if (xx >= W) continue;
                     const int iters = args.iters;
                     const size_t pix = (size_t)y * W + xx;
                     float* ap = args.adjust ? args.adjust + (size_t)b * 3 * iters * plane + pix : nullptr;
@@ -285,7 +307,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_w), 128, 256);
         // A descriptor of stage 0, tap (dx = 0, chunk 0); a stage / source / dx / chunk offset is added to the
         // 14-bit (address >> 4) field, which cannot carry: the whole window is < 256 KB
-        const uint64_t adesc0 = FIRST ? smem_desc_kmajor(stage_u32, 128, 256) : smem_desc_sw64(stage_u32);
+        const uint64_t adesc0 = FIRST ? smem_desc_kmajor(stage_u32, 128, TC_A1_SBO) : smem_desc_sw64(stage_u32);
         const bool leader = elect_one();
         uint32_t s = 0, sph = 0;  // stage ring position and phase parity
         uint32_t o_base = 0;
@@ -380,9 +402,12 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         }
     } else {
         // =========================== LAYER-1 A-TILE BUILDERS ===========================
+        // One warp per input row (rows g = bw mod 8), 4 adjacent pixels per lane: 3 x 128-bit loads per lane and row
+        // (scalar when W % 4 != 0 or at the right edge), the two halo pixels of the strip by lanes 0 / 31, the
+        // neighbours' pixels by warp shuffle at conversion time so the loads of the next row stay in flight.
         if constexpr (FIRST) {
-            const int grp = (warp - 10) >> 2;                 // rows with (g & 1) == grp
-            const int t = ((warp - 10) & 3) * 32 + lane;      // pixel in strip = A-tile row
+            const int bw = warp - 10;
+            const int px0 = lane * 4;
             auto setup = [&](TcRowIt& it) {
                 it.valid = it.item < n_items;
                 if (!it.valid) return;
@@ -393,59 +418,91 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                 it.x0 = strip * TC_M;
                 it.nin = min(R, H - it.y0) + 2;
             };
-            auto step = [&](TcRowIt& it) {  // two rows further in this CTA's flattened row sequence
-                it.ri += 2;
-                it.g += 2;
+            auto step = [&](TcRowIt& it) {  // eight rows further in this CTA's flattened row sequence
+                it.ri += 8;
+                it.g += 8;
                 while (it.valid && it.ri >= it.nin) {
                     it.ri -= it.nin;
                     it.item += gridDim.x;
                     setup(it);
                 }
             };
-            auto load_row = [&](const TcRowIt& it, float (&v)[9]) {
+            // v[c*6 + k]: k = 1..4 this lane's pixels, k = 0 / 5 the strip's left / right halo pixel (lanes 0 / 31)
+            auto load_row = [&](const TcRowIt& it, float (&v)[18]) {
+#pragma unroll
+                for (int i = 0; i < 18; ++i) v[i] = 0.f;
                 if (!it.valid) return;
                 const int y = it.y0 - 1 + it.ri;
-                const bool yok = y >= 0 && y < H;
-                const float* xin = args.x + (size_t)it.b * 3 * H * W;
+                if (y < 0 || y >= H) return;
+                const int xs = it.x0 + px0;
+                const float* row = args.x + ((size_t)it.b * 3 * H + y) * W;
 #pragma unroll
-                for (int dx = 0; dx < 3; ++dx) {
-                    const int xs = it.x0 + t + dx - 1;
-                    const bool ok = yok && xs >= 0 && xs < W;
+                for (int c = 0; c < 3; ++c) {
+                    const float* rp = row + (size_t)c * H * W;
+                    if ((W & 3) == 0 && xs + 3 < W) {
+                        const float4 q4 = __ldg(reinterpret_cast<const float4*>(rp + xs));
+                        v[c * 6 + 1] = q4.x;
+                        v[c * 6 + 2] = q4.y;
+                        v[c * 6 + 3] = q4.z;
+                        v[c * 6 + 4] = q4.w;
+                    } else {
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) v[dx * 3 + c] = ok ? __ldg(xin + ((size_t)c * H + y) * W + xs) : 0.f;
+                        for (int k = 0; k < 4; ++k)
+                            if (xs + k < W) v[c * 6 + 1 + k] = __ldg(rp + xs + k);
+                    }
+                    if (lane == 0 && xs > 0) v[c * 6] = __ldg(rp + xs - 1);
+                    if (lane == 31 && xs + 4 < W) v[c * 6 + 5] = __ldg(rp + xs + 4);
                 }
             };
-            auto emit = [&](const TcRowIt& it, const float (&v)[9]) {
+            auto emit = [&](const TcRowIt& it, float (&v)[18]) {
                 const uint32_t s = it.g % NST, lap = it.g / NST;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float l = __shfl_up_sync(0xffffffffu, v[c * 6 + 4], 1);
+                    const float r = __shfl_down_sync(0xffffffffu, v[c * 6 + 1], 1);
+                    if (lane != 0) v[c * 6] = l;
+                    if (lane != 31) v[c * 6 + 5] = r;
+                }
                 if (lap > 0) mbar_wait(&stage_empty[s], (lap - 1) & 1);
                 auto pk = [](float a, float b) {
                     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
                     return *reinterpret_cast<uint32_t*>(&h);
                 };
-                uint8_t* row = s_stage + s * STAGE + (t >> 3) * 256 + (t & 7) * 16;
-                *reinterpret_cast<uint4*>(row) = make_uint4(pk(v[0], v[1]), pk(v[2], v[3]), pk(v[4], v[5]), pk(v[6], v[7]));
-                *reinterpret_cast<uint4*>(row + 128) = make_uint4(pk(v[8], 0.f), 0u, 0u, 0u);
+                // tile row p at (p / 8) * TC_A1_SBO + (p % 8) * 16, k = 8..15 at + 128;  k = dx*3 + c
+                uint8_t* tp = s_stage + s * STAGE + (lane >> 1) * TC_A1_SBO + (lane & 1) * 64;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    // e(c, dx) = v[c*6 + j + dx]
+                    *reinterpret_cast<uint4*>(tp + j * 16) =
+                        make_uint4(pk(v[0 + j], v[6 + j]), pk(v[12 + j], v[0 + j + 1]), pk(v[6 + j + 1], v[12 + j + 1]),
+                                   pk(v[0 + j + 2], v[6 + j + 2]));
+                    *reinterpret_cast<uint4*>(tp + j * 16 + 128) = make_uint4(pk(v[12 + j + 2], 0.f), 0u, 0u, 0u);
+                }
                 fence_proxy_async_smem();
                 mbar_arrive(&stage_full[s]);
             };
             TcRowIt cv;
             cv.item = blockIdx.x;
-            cv.ri = grp;
-            cv.g = (uint32_t)grp;
+            cv.ri = 0;
+            cv.g = 0;
             cv.nin = 0;
             cv.b = cv.y0 = cv.x0 = 0;
-            setup(cv);  // nin >= 3 > grp
+            setup(cv);
+            // advance to this warp's first row (row index bw of the flattened sequence)
+            if (cv.valid) {
+                cv.ri = bw - 8;
+                cv.g = (uint32_t)(bw - 8);
+                step(cv);
+            }
             TcRowIt ld = cv;
-            float buf[3][9];
+            float buf[2][18];
             load_row(ld, buf[0]);
-            step(ld);
-            load_row(ld, buf[1]);
             step(ld);
             while (cv.valid) {
 #pragma unroll
-                for (int u = 0; u < 3; ++u) {
+                for (int u = 0; u < 2; ++u) {
                     if (cv.valid) {
-                        load_row(ld, buf[(u + 2) % 3]);
+                        load_row(ld, buf[u ^ 1]);
                         step(ld);
                         emit(cv, buf[u]);
                         step(cv);
@@ -456,6 +513,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     }
 
     // ---- teardown ----
+    if (!LAST && warp < 8 && (warp & 3) == 0 && lane == 0) tma_store_wait<0>();  // smem must outlive the bulk stores
     tc_fence_before();
     __syncthreads();
     if (warp == 8) {
@@ -490,12 +548,12 @@ static tc_encode_fn tc_encoder() {
 
 // NHWC bf16 [B,H,W,32] as a 4-D tensor (c, x, y, b); box = 32 channels x 130 pixels of one row; 64-byte swizzle;
 // coordinates outside the image (x = -1, x >= W, y = -1, y >= H) are zero-filled = the conv's zero padding.
-static int tc_make_map(CUtensorMap* m, const void* base, int B, int H, int W) {
+static int tc_make_map(CUtensorMap* m, const void* base, int B, int H, int W, int box_px = TC_SPX) {
     tc_encode_fn enc = tc_encoder();
     if (!enc) return B200_ERR_LAUNCH;
     const cuuint64_t dims[4] = {32, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
     const cuuint64_t strides[3] = {64, (cuuint64_t)W * 64, (cuuint64_t)H * W * 64};
-    const cuuint32_t box[4] = {32, (cuuint32_t)TC_SPX, 1, 1};
+    const cuuint32_t box[4] = {32, (cuuint32_t)box_px, 1, 1};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -506,23 +564,25 @@ static int tc_make_map(CUtensorMap* m, const void* base, int B, int H, int W) {
 template <int NSRC, bool FIRST, bool LAST>
 static int tc_launch(const TcArgs& a, const void* s0, const void* s1, cudaStream_t s) {
     auto kern = dce_tc_layer_kernel<NSRC, FIRST, LAST>;
-    constexpr int smem = tc_smem_bytes<NSRC, FIRST>();
+    constexpr int smem = tc_smem_bytes<NSRC, FIRST, LAST>();
     static_assert(smem <= 227 * 1024, "shared memory budget");
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
         (void)cudaGetLastError();
         return B200_ERR_LAUNCH;
     }
-    CUtensorMap m0, m1;
+    CUtensorMap m0, m1, mo;
     memset(&m0, 0, sizeof(m0));
     memset(&m1, 0, sizeof(m1));
+    memset(&mo, 0, sizeof(mo));
+    int rc;
     if (!FIRST) {
-        int rc;
         if ((rc = tc_make_map(&m0, s0, a.B, a.H, a.W))) return rc;
         if (NSRC == 2 && (rc = tc_make_map(&m1, s1, a.B, a.H, a.W))) return rc;
     }
+    if (!LAST && (rc = tc_make_map(&mo, a.dst, a.B, a.H, a.W, TC_M))) return rc;  // output row tiles (bulk stores)
     const long long items = (long long)a.B * a.nseg * a.nstrip;
     const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
-    kern<<<grid, tc_threads<FIRST>(), smem, s>>>(a, m0, m1);
+    kern<<<grid, tc_threads<FIRST>(), smem, s>>>(a, m0, m1, mo);
     return launch_status();
 }
 
