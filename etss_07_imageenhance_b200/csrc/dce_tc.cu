@@ -131,8 +131,6 @@ constexpr int tc_smem_bytes() {
     return need < TC_MIN_SMEM ? TC_MIN_SMEM : need;
 }
 
-__device__ __forceinline__ int tc_pos(uint32_t o) { return TC_NB - 1 - (int)(o % TC_NB); }
-
 // flattened (item, row) iterator of one layer-1 builder group: every second input row of this CTA's items
 struct TcRowIt {
     int item, ri, nin, b, y0, x0;
@@ -152,6 +150,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     constexpr int WBYTES = tc_wbytes_t<NSRC, FIRST>();
     constexpr int TILE = 3072;
     constexpr int NTHREADS = tc_threads<FIRST>();
+    static_assert((NST & (NST - 1)) == 0 && TC_NB == 16, "rings are indexed with masks / shifts of the row counter");
     static_assert((2 * NST + 2 * TC_NB) * 8 <= TC_BAR_BYTES, "mbarrier area");
 
     extern __shared__ uint8_t smem_raw[];
@@ -221,7 +220,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         float bias[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) bias[i] = s_bias[i];
-        uint32_t o_base = 0, obuf = 0;
+        uint32_t g_base = 0, obuf = 0;  // g = running input-row index of this CTA: ring position of every role
         const size_t plane = (size_t)H * W;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int strip = item % args.nstrip;
@@ -229,10 +228,17 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
             const int b = item / (args.nstrip * args.nseg);
             const int y0 = seg * R, xx = strip * TC_M + m;
             const int nout = min(R, H - y0);
-            for (int j = (int)((o_base ^ (uint32_t)par) & 1); j < nout; j += 2) {
-                const uint32_t o = o_base + j;
-                const int p = tc_pos(o);
-                mbar_wait(&acc_full[p], (o / TC_NB) & 1);
+            // output row j lives in the block opened by input row g_base + j; the two extra input rows of an item
+            // open blocks that stay unused for this lap (phases are still completed so that every barrier's parity
+            // is a function of g alone)
+            for (int j = (int)((g_base ^ (uint32_t)par) & 1); j < nout + 2; j += 2) {
+                const uint32_t g = g_base + j;
+                const int p = TC_NB - 1 - (int)(g & (TC_NB - 1));
+                mbar_wait(&acc_full[p], (g >> 4) & 1);
+                if (j >= nout) {
+                    mbar_arrive(&acc_empty[p]);
+                    continue;
+                }
                 tc_fence_after();
                 uint32_t v[32];
                 tmem_ld32(tlane + p * 32, v);
@@ -296,7 +302,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                     for (int c = 0; c < 3; ++c) ep[(size_t)c * plane] = yv[c];
                 }
             }
-            o_base += nout;
+            g_base += nout + 2;
         }
     } else if (warp == 8) {
         // =========================== MMA ISSUER ===========================
@@ -309,19 +315,20 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         // 14-bit (address >> 4) field, which cannot carry: the whole window is < 256 KB
         const uint64_t adesc0 = FIRST ? smem_desc_kmajor(stage_u32, 128, TC_A1_SBO) : smem_desc_sw64(stage_u32);
         const bool leader = elect_one();
-        uint32_t s = 0, sph = 0;  // stage ring position and phase parity
-        uint32_t o_base = 0;
+        uint32_t g = 0;  // running input-row index: stage g % NST, block 15 - g % 16, parities from g / NST, g / 16
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int seg = (item / args.nstrip) % args.nseg;
             const int nout = min(R, H - seg * R);
             const int nin = nout + NDY - 1;
-            uint32_t on = o_base % TC_NB, upar = (o_base / TC_NB) & 1;  // block ring position / use parity of row o_base+ri
-            for (int ri = 0; ri < nin; ++ri) {
-                mbar_wait(&stage_full[s], sph);
-                const int pn = TC_NB - 1 - (int)on;  // block opened by this input row (output row ri, dy = 0)
-                if (ri < nout && o_base + ri >= TC_NB) mbar_wait(&acc_empty[pn], upar ^ 1);
+#pragma unroll 2
+            for (int ri = 0; ri < nin; ++ri, ++g) {
+                const uint32_t st = g & (NST - 1);
+                const int pn = TC_NB - 1 - (int)(g & (TC_NB - 1));  // block opened by this input row (dy = 0)
+                mbar_wait(&stage_full[st], (g / NST) & 1);
+                // also for the two unused blocks of an item: no barrier may run more than one phase ahead of its waiters
+                if (g >= TC_NB) mbar_wait(&acc_empty[pn], ((g >> 4) & 1) ^ 1);
                 tc_fence_after();
-                const uint64_t adesc = adesc0 + (uint64_t)((s * STAGE) >> 4);
+                const uint64_t adesc = adesc0 + (uint64_t)((st * STAGE) >> 4);
                 auto a_of = [&](int dx, int kc) -> uint64_t {  // compile-time offsets after unrolling
                     return FIRST ? adesc : adesc + (uint64_t)(((kc >> 1) * TC_SRC_STRIDE + dx * 64 + (kc & 1) * 32) >> 4);
                 };
@@ -340,7 +347,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                     int dy = max(0, ri - (nout - 1));
                     const int dy_hi = min(NDY - 1, ri);
                     while (dy <= dy_hi) {
-                        const int p0 = (pn + dy) % TC_NB;
+                        const int p0 = (pn + dy) & (TC_NB - 1);
                         const int cnt = min(dy_hi - dy + 1, TC_NB - p0);
                         const uint32_t idesc = IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17);
                         const uint32_t d = tbase + p0 * 32;
@@ -354,49 +361,36 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                     }
                 }
                 if (leader) {
-                    tc_commit(&stage_empty[s]);
-                    if (ri >= NDY - 1) tc_commit(&acc_full[(pn + NDY - 1) % TC_NB]);
+                    tc_commit(&stage_empty[st]);
+                    if (ri >= NDY - 1) tc_commit(&acc_full[(pn + NDY - 1) & (TC_NB - 1)]);
+                    if (ri >= nout) tc_commit(&acc_full[pn]);  // block unused this lap: complete its phase
                 }
                 __syncwarp();
-                if (++s == NST) {
-                    s = 0;
-                    sph ^= 1;
-                }
-                if (++on == TC_NB) {
-                    on = 0;
-                    upar ^= 1;
-                }
             }
-            o_base += nout;
         }
     } else if (warp == 9) {
         // =========================== TMA PRODUCER ===========================
         // warp-uniform control flow, one elected lane issues expect_tx + the bulk tensor copies
         if constexpr (!FIRST) {
             const bool leader = elect_one();
-            uint32_t s = 0, spar = 0;  // stage ring position / phase parity of the NEXT fill
-            bool first_round = true;
+            uint32_t g = 0;
             for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
                 const int strip = item % args.nstrip;
                 const int seg = (item / args.nstrip) % args.nseg;
                 const int b = item / (args.nstrip * args.nseg);
                 const int y0 = seg * R, x0 = strip * TC_M;
                 const int nin = min(R, H - y0) + 2;
-                for (int ri = 0; ri < nin; ++ri) {
-                    if (!first_round) mbar_wait(&stage_empty[s], spar ^ 1);
+                for (int ri = 0; ri < nin; ++ri, ++g) {
+                    const uint32_t st = g & (NST - 1);
+                    if (g >= NST) mbar_wait(&stage_empty[st], ((g / NST) & 1) ^ 1);
                     if (leader) {
-                        mbar_arrive_expect_tx(&stage_full[s], NSRC * TC_SRC_BYTES);
-                        const uint32_t dst = stage_u32 + s * STAGE;
-                        tma_load_4d(dst, &tm0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                        mbar_arrive_expect_tx(&stage_full[st], NSRC * TC_SRC_BYTES);
+                        const uint32_t dst = stage_u32 + st * STAGE;
+                        tma_load_4d(dst, &tm0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[st]);
                         if (NSRC == 2)
-                            tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[s]);
+                            tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[st]);
                     }
                     __syncwarp();
-                    if (++s == NST) {
-                        s = 0;
-                        spar ^= 1;
-                        first_round = false;
-                    }
                 }
             }
         }
@@ -455,7 +449,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                 }
             };
             auto emit = [&](const TcRowIt& it, float (&v)[18]) {
-                const uint32_t s = it.g % NST, lap = it.g / NST;
+                const uint32_t s = it.g & (NST - 1), lap = it.g / NST;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     const float l = __shfl_up_sync(0xffffffffu, v[c * 6 + 4], 1);
