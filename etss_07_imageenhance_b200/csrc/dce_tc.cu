@@ -17,13 +17,14 @@
 // input row below it has been consumed; the epilogue drains it, re-zeroes it (every MMA accumulates) and hands it
 // back.
 //
-// Warp roles (1 persistent CTA per SM):
-//   warps 0-7    epilogue, two per TMEM lane quarter, alternating output rows: tcgen05.ld -> bias + ReLU -> bf16
-//                NHWC store; layer 7: tanh -> `adjust` (NCHW fp32) + the 8-iteration curve on x -> `enhanced`
-//   warp  8      MMA issuer: warp-uniform control flow, one elected lane issues tcgen05.mma / tcgen05.commit
+// Warp roles (persistent CTAs; layers 2-7: two CTAs per SM with 8 accumulator blocks each, see tc_ctas):
+//   warps 0-3    epilogue, one per TMEM lane quarter (layer 1: warps 0-7, two groups alternating output rows):
+//                tcgen05.ld -> bias + ReLU -> bf16 row staged in smem -> bulk tensor store; layer 7: tanh -> `adjust`
+//                (NCHW fp32) + the 8-iteration curve on x -> `enhanced`
+//   next warp    MMA issuer: warp-uniform control flow, one elected lane issues tcgen05.mma / tcgen05.commit
 //                (-> stage_empty[s], acc_full[block])
-//   warp  9      TMA producer: one elected lane, expect_tx + cp.async.bulk.tensor per input row and source
-//   warps 10-17  layer 1 only (Cin = 3): A-tile builders.  The 3 x 3 (dx, channel) taps of a pixel are folded into
+//   next warp    TMA producer: one elected lane, expect_tx + cp.async.bulk.tensor per input row and source
+//   8 more warps layer 1 only (Cin = 3): A-tile builders.  The 3 x 3 (dx, channel) taps of a pixel are folded into
 //                K (k = dx*3 + c, padded to 16), so layer 1 is ONE K=16 MMA per input row; the builders read the
 //                fp32 NCHW input (coalesced along x, three rows in flight per group) and write bf16 core-matrix
 //                tiles into the smem ring (generic-proxy stores + fence.proxy.async).
@@ -38,7 +39,6 @@ namespace b200 {
 using namespace tc;
 
 constexpr int TC_M = 128;            // pixels per strip = MMA M = TMEM lanes
-constexpr int TC_NB = 16;            // accumulator blocks (32 columns each): the whole TMEM; even
 constexpr int TC_SPX = TC_M + 2;     // staged pixels per row (halo of 1 on each side)
 constexpr int TC_SRC_BYTES = TC_SPX * 64;          // TMA box bytes per source per row (8320)
 constexpr int TC_SRC_STRIDE = 8704;                // smem bytes per source per stage (17 x 512: keeps the swizzle phase)
@@ -46,12 +46,23 @@ constexpr int TC_A1_SBO = 272;                     // layer 1 A tile: 8-row grou
 constexpr int TC_A1_BYTES = 16 * TC_A1_SBO;        // layer 1: one [128 px][K = 16] bf16 tile per input row
 constexpr int TC_BAR_BYTES = 512;
 constexpr int TC_OUT_BYTES = TC_M * 64;            // one output row tile [128 px][32 ch] bf16 (TMA-store staging)
-constexpr int TC_NOUT = 3;                         // staging tiles per epilogue parity group
+constexpr int TC_NOUT = 2;                         // staging tiles per epilogue group (double buffer)
+constexpr int TC_SMEM_2CTA = 113 * 1024;           // per-CTA budget when two CTAs share an SM (227 KB + 1 KB reserved each)
 constexpr int TC_MIN_SMEM = 120 * 1024;            // > half an SM: one CTA per SM (each CTA owns all of TMEM)
 
+// Layers 2-7 run TWO CTAs per SM, each with half of TMEM (8 accumulator blocks), its own MMA-issuing warp, TMA
+// producer and four epilogue warps: one issuing warp cannot keep the tensor pipe busy (its per-row control flow costs
+// more cycles than the row's MMAs), two interleave.  Layer 1 (one MMA per row, eight A-tile builder warps) keeps one
+// CTA per SM with the whole TMEM.
+template <bool FIRST>
+__host__ __device__ constexpr int tc_ctas() { return FIRST ? 1 : 2; }
+template <bool FIRST>
+__host__ __device__ constexpr int tc_nb() { return FIRST ? 16 : 8; }      // accumulator blocks (32 columns each)
+template <bool FIRST>
+__host__ __device__ constexpr int tc_epg() { return FIRST ? 2 : 1; }      // epilogue groups of 4 warps (alternating rows)
 template <int NSRC, bool FIRST>
-__host__ __device__ constexpr int tc_nst() {       // smem stages (input rows in flight)
-    return NSRC == 2 ? 8 : 16;
+__host__ __device__ constexpr int tc_nst() {       // smem stages (input rows in flight) per CTA
+    return FIRST ? 16 : (NSRC == 2 ? 3 : 8);
 }
 template <int NSRC, bool FIRST>
 __host__ __device__ constexpr int tc_stage_bytes() {
@@ -59,7 +70,7 @@ __host__ __device__ constexpr int tc_stage_bytes() {
 }
 template <bool FIRST>
 __host__ __device__ constexpr int tc_threads() {
-    return FIRST ? 576 : 320;
+    return FIRST ? 576 : 192;  // 4 x EPG epilogue warps + MMA + TMA (+ 8 builders)
 }
 
 // packed weights per layer: B tiles then 32 fp32 biases.
@@ -125,10 +136,12 @@ __host__ __device__ constexpr int tc_wbytes_t() {
 }
 template <int NSRC, bool FIRST, bool LAST>
 constexpr int tc_smem_bytes() {
-    // weights | bias 128 | barriers | tmem addr 16 | pad to 1024 | output staging (2 x TC_NOUT tiles) | stages
+    // weights | bias 128 | barriers | tmem addr 16 | pad to 1024 | output staging (EPG x TC_NOUT tiles) | stages
     constexpr int need = tc_wbytes_t<NSRC, FIRST>() + 128 + TC_BAR_BYTES + 16 + 1024 +
-                         (LAST ? 0 : 2 * TC_NOUT * TC_OUT_BYTES) + tc_nst<NSRC, FIRST>() * tc_stage_bytes<NSRC, FIRST>();
-    return need < TC_MIN_SMEM ? TC_MIN_SMEM : need;
+                         (LAST ? 0 : tc_epg<FIRST>() * TC_NOUT * TC_OUT_BYTES) +
+                         tc_nst<NSRC, FIRST>() * tc_stage_bytes<NSRC, FIRST>();
+    static_assert(FIRST || need <= TC_SMEM_2CTA, "two CTAs per SM");
+    return FIRST && need < TC_MIN_SMEM ? TC_MIN_SMEM : need;
 }
 
 // flattened (item, row) iterator of one layer-1 builder group: every second input row of this CTA's items
@@ -139,7 +152,7 @@ struct TcRowIt {
 };
 
 template <int NSRC, bool FIRST, bool LAST>
-__global__ void __launch_bounds__(tc_threads<FIRST>(), 1)
+__global__ void __launch_bounds__(tc_threads<FIRST>(), tc_ctas<FIRST>())
 dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
                     const __grid_constant__ CUtensorMap tmo) {
     constexpr int KC = FIRST ? 1 : 2 * NSRC;            // K chunks of 16 per dx
@@ -150,7 +163,12 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     constexpr int WBYTES = tc_wbytes_t<NSRC, FIRST>();
     constexpr int TILE = 3072;
     constexpr int NTHREADS = tc_threads<FIRST>();
-    static_assert((NST & (NST - 1)) == 0 && TC_NB == 16, "rings are indexed with masks / shifts of the row counter");
+    constexpr int TC_NB = tc_nb<FIRST>();               // accumulator ring: block NB-1 - g % NB, parity (g / NB) & 1
+    constexpr int NB_SH = FIRST ? 4 : 3;
+    constexpr int EPG = tc_epg<FIRST>();
+    constexpr int W_MMA = 4 * EPG, W_TMA = W_MMA + 1, W_BUILD = W_MMA + 2;  // warp roles
+    static_assert((1 << NB_SH) == TC_NB, "accumulator ring is indexed with masks / shifts of the row counter");
+    static_assert(!FIRST || (NST & (NST - 1)) == 0, "layer-1 builders index the stage ring with a mask");
     static_assert((2 * NST + 2 * TC_NB) * 8 <= TC_BAR_BYTES, "mbarrier area");
 
     extern __shared__ uint8_t smem_raw[];
@@ -165,7 +183,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     // stage area: 1024-byte aligned in the shared window (swizzle phase = address bits 7-8)
     const uint32_t out_u32 = (smem_u32(smem_raw + WBYTES + 128 + TC_BAR_BYTES + 16) + 1023u) & ~1023u;
     uint8_t* s_out = smem_raw + (out_u32 - smem_u32(smem_raw));
-    const uint32_t stage_u32 = out_u32 + (LAST ? 0 : 2 * TC_NOUT * TC_OUT_BYTES);
+    const uint32_t stage_u32 = out_u32 + (LAST ? 0 : EPG * TC_NOUT * TC_OUT_BYTES);
     uint8_t* s_stage = smem_raw + (stage_u32 - smem_u32(smem_raw));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -179,7 +197,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         for (int i = tid; i < (WBYTES + 128) / 16; i += NTHREADS) s[i] = __ldg(g + i);
         fence_proxy_async_smem();  // B tiles are read through the async proxy
     }
-    if (warp == 8) {
+    if (warp == W_MMA) {
         if (lane == 0) {
             for (int i = 0; i < NST; ++i) {
                 mbar_init(&stage_full[i], FIRST ? 32 : 1);
@@ -192,9 +210,9 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
             mbar_fence_init();
         }
         __syncwarp();
-        tmem_alloc(s_tmem, 512);
+        tmem_alloc(s_tmem, TC_NB * 32);
     }
-    if (warp == 9 && lane == 0) {
+    if (warp == W_TMA && lane == 0) {
         if (!FIRST) tma_prefetch_desc(&tm0);
         if (NSRC == 2) tma_prefetch_desc(&tm1);
         if (!LAST) tma_prefetch_desc(&tmo);
@@ -212,7 +230,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     __syncthreads();
     tc_fence_after();
 
-    if (warp < 8) {
+    if (warp < W_MMA) {
         // =========================== EPILOGUE ===========================
         const int q = warp & 3, par = warp >> 2;
         const int m = q * 32 + lane;
@@ -231,10 +249,10 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
             // output row j lives in the block opened by input row g_base + j; the two extra input rows of an item
             // open blocks that stay unused for this lap (phases are still completed so that every barrier's parity
             // is a function of g alone)
-            for (int j = (int)((g_base ^ (uint32_t)par) & 1); j < nout + 2; j += 2) {
+            for (int j = EPG == 2 ? (int)((g_base ^ (uint32_t)par) & 1) : 0; j < nout + 2; j += EPG) {
                 const uint32_t g = g_base + j;
                 const int p = TC_NB - 1 - (int)(g & (TC_NB - 1));
-                mbar_wait(&acc_full[p], (g >> 4) & 1);
+                mbar_wait(&acc_full[p], (g >> NB_SH) & 1);
                 if (j >= nout) {
                     mbar_arrive(&acc_empty[p]);
                     continue;
@@ -272,9 +290,10 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                     if (q == 0 && lane == 0) {
                         tma_store_4d(&tmo, out_u32 + ob, 0, strip * TC_M, y, b);
                         tma_store_commit();
-                        // the tile written two rows from now is the one stored one row ago: its read must be over
-                        // before this thread reaches the next row's barrier
-                        tma_store_wait_read<1>();
+                        // the other tile is written during the next row by threads that only passed THIS row's
+                        // barrier, the tile stored now during the row after: this store's read must be over before
+                        // this thread reaches the next barrier
+                        tma_store_wait_read<0>();
                     }
                     if (++obuf == TC_NOUT) obuf = 0;
                 } else {
@@ -304,7 +323,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
             }
             g_base += nout + 2;
         }
-    } else if (warp == 8) {
+    } else if (warp == W_MMA) {
         // =========================== MMA ISSUER ===========================
         // The whole warp runs the (warp-uniform) control flow so that addresses and descriptors stay in uniform
         // registers; one elected lane issues every tcgen05.mma / tcgen05.commit.
@@ -315,18 +334,18 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         // 14-bit (address >> 4) field, which cannot carry: the whole window is < 256 KB
         const uint64_t adesc0 = FIRST ? smem_desc_kmajor(stage_u32, 128, TC_A1_SBO) : smem_desc_sw64(stage_u32);
         const bool leader = elect_one();
-        uint32_t g = 0;  // running input-row index: stage g % NST, block 15 - g % 16, parities from g / NST, g / 16
+        uint32_t g = 0;            // running input-row index: block NB-1 - g % NB, parity (g / NB) & 1
+        uint32_t st = 0, sph = 0;  // stage ring position / phase parity
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int seg = (item / args.nstrip) % args.nseg;
             const int nout = min(R, H - seg * R);
             const int nin = nout + NDY - 1;
 #pragma unroll 2
             for (int ri = 0; ri < nin; ++ri, ++g) {
-                const uint32_t st = g & (NST - 1);
                 const int pn = TC_NB - 1 - (int)(g & (TC_NB - 1));  // block opened by this input row (dy = 0)
-                mbar_wait(&stage_full[st], (g / NST) & 1);
+                mbar_wait(&stage_full[st], sph);
                 // also for the two unused blocks of an item: no barrier may run more than one phase ahead of its waiters
-                if (g >= TC_NB) mbar_wait(&acc_empty[pn], ((g >> 4) & 1) ^ 1);
+                if (g >= TC_NB) mbar_wait(&acc_empty[pn], ((g >> NB_SH) & 1) ^ 1);
                 tc_fence_after();
                 const uint64_t adesc = adesc0 + (uint64_t)((st * STAGE) >> 4);
                 auto a_of = [&](int dx, int kc) -> uint64_t {  // compile-time offsets after unrolling
@@ -366,23 +385,27 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                     if (ri >= nout) tc_commit(&acc_full[pn]);  // block unused this lap: complete its phase
                 }
                 __syncwarp();
+                if (++st == NST) {
+                    st = 0;
+                    sph ^= 1;
+                }
             }
         }
-    } else if (warp == 9) {
+    } else if (warp == W_TMA) {
         // =========================== TMA PRODUCER ===========================
         // warp-uniform control flow, one elected lane issues expect_tx + the bulk tensor copies
         if constexpr (!FIRST) {
             const bool leader = elect_one();
-            uint32_t g = 0;
+            uint32_t st = 0, sph = 0;  // stage ring position / phase parity of the fill in progress
+            bool lap0 = true;
             for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
                 const int strip = item % args.nstrip;
                 const int seg = (item / args.nstrip) % args.nseg;
                 const int b = item / (args.nstrip * args.nseg);
                 const int y0 = seg * R, x0 = strip * TC_M;
                 const int nin = min(R, H - y0) + 2;
-                for (int ri = 0; ri < nin; ++ri, ++g) {
-                    const uint32_t st = g & (NST - 1);
-                    if (g >= NST) mbar_wait(&stage_empty[st], ((g / NST) & 1) ^ 1);
+                for (int ri = 0; ri < nin; ++ri) {
+                    if (!lap0) mbar_wait(&stage_empty[st], sph ^ 1);
                     if (leader) {
                         mbar_arrive_expect_tx(&stage_full[st], NSRC * TC_SRC_BYTES);
                         const uint32_t dst = stage_u32 + st * STAGE;
@@ -391,6 +414,11 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                             tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[st]);
                     }
                     __syncwarp();
+                    if (++st == NST) {
+                        st = 0;
+                        sph ^= 1;
+                        lap0 = false;
+                    }
                 }
             }
         }
@@ -400,7 +428,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         // (scalar when W % 4 != 0 or at the right edge), the two halo pixels of the strip by lanes 0 / 31, the
         // neighbours' pixels by warp shuffle at conversion time so the loads of the next row stay in flight.
         if constexpr (FIRST) {
-            const int bw = warp - 10;
+            const int bw = warp - W_BUILD;
             const int px0 = lane * 4;
             auto setup = [&](TcRowIt& it) {
                 it.valid = it.item < n_items;
@@ -507,12 +535,12 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     }
 
     // ---- teardown ----
-    if (!LAST && warp < 8 && (warp & 3) == 0 && lane == 0) tma_store_wait<0>();  // smem must outlive the bulk stores
+    if (!LAST && warp < W_MMA && (warp & 3) == 0 && lane == 0) tma_store_wait<0>();  // smem must outlive the bulk stores
     tc_fence_before();
     __syncthreads();
-    if (warp == 8) {
+    if (warp == W_MMA) {
         tc_fence_after();
-        tmem_dealloc(tbase, 512);
+        tmem_dealloc(tbase, TC_NB * 32);
     }
 }
 
@@ -575,7 +603,8 @@ static int tc_launch(const TcArgs& a, const void* s0, const void* s1, cudaStream
     }
     if (!LAST && (rc = tc_make_map(&mo, a.dst, a.B, a.H, a.W, TC_M))) return rc;  // output row tiles (bulk stores)
     const long long items = (long long)a.B * a.nseg * a.nstrip;
-    const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
+    const long long slots = (long long)B200_NUM_SMS * tc_ctas<FIRST>();  // persistent CTAs: one resident wave
+    const int grid = (int)(items < slots ? items : slots);
     kern<<<grid, tc_threads<FIRST>(), smem, s>>>(a, m0, m1, mo);
     return launch_status();
 }

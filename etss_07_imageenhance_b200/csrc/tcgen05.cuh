@@ -106,6 +106,28 @@ __device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_
         : "memory");
 }
 
+// Same, guarded by a per-thread predicate INSIDE the instruction stream: the call site stays in warp-uniform control
+// flow (no branch around the MMA), so descriptors and addresses can live in uniform registers.
+__device__ __forceinline__ void mma_ss_pred(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t issue) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "setp.ne.b32 q, %4, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%6, %6, %6, %6}, p;\n\t}"
+        :
+        : "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(issue), "r"(1u), "r"(0u)
+        : "memory");
+}
+__device__ __forceinline__ void tc_commit_pred(uint64_t* bar, uint32_t issue) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %1, 0;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)),
+        "r"(issue)
+        : "memory");
+}
+
 // ---- MMA: D[tmem] (+)= A[tmem] * B[smem]   (cta_group::1, kind::f16, issued by ONE thread) -------
 __device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
                                        uint32_t accumulate) {
