@@ -72,7 +72,7 @@ constexpr int K1_TH = 8, K1_TW = 32, K1_HS = 36;  // halo row stride (34 used)
 template <int CS, int NSRC, int NOUT, bool FIRST, bool TANH>
 __global__ void __launch_bounds__(256, 2)
 dcepp_layer_kernel(const float* __restrict__ srcA, const float* __restrict__ srcB, float* __restrict__ dst,
-                   const float* __restrict__ wl, int h, int w, int H, int W, float sf_scale) {
+                   const float* __restrict__ wl, int h, int w, int H, int W, float sf_scale, int* __restrict__ sync) {
     constexpr int CIN = CS * NSRC;
     constexpr int COUT_PAD = 4 * NOUT;
     constexpr int COUT = TANH ? 3 : 32;
@@ -88,6 +88,15 @@ dcepp_layer_kernel(const float* __restrict__ srcA, const float* __restrict__ src
     const int t = threadIdx.x;
     const int b = blockIdx.z;
     const int y0 = blockIdx.y * K1_TH, x0 = blockIdx.x * K1_TW;
+
+    // layer 1 shares its tile grid with dcepp_net_kernel: clear that launch's work counter and this tile's five
+    // "published" flags (the net launch follows this one in stream order)
+    if (FIRST && sync != nullptr) {
+        static_assert(K1_TH == MM_TH && K1_TW == MM_TW, "layer 1 and the net kernel tile the map identically");
+        const int tpf = gridDim.x * gridDim.y, tile = (b * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        if (t < 5) sync[MM_FLAG0 + t * (gridDim.z * tpf) + tile] = 0;
+        if (tile == 0 && t == 5) sync[0] = 0;
+    }
 
     // weights -> smem  (layout in global == layout in smem, except the 16B alignment gap for CIN=3)
     {
@@ -233,7 +242,7 @@ constexpr size_t k1_smem_bytes() {
 
 template <int CS, int NSRC, int NOUT, bool FIRST, bool TANH>
 static int launch_k1(const float* a, const float* b2, float* dst, const float* wl, int B, int h, int w, int H, int W,
-                     float sf_scale, cudaStream_t s) {
+                     float sf_scale, int* sync, cudaStream_t s) {
     auto kern = dcepp_layer_kernel<CS, NSRC, NOUT, FIRST, TANH>;
     constexpr size_t smem = k1_smem_bytes<CS, NSRC, NOUT>();
     if (smem > 48 * 1024) {
@@ -241,7 +250,7 @@ static int launch_k1(const float* a, const float* b2, float* dst, const float* w
         if (e != cudaSuccess) return B200_ERR_LAUNCH;
     }
     dim3 grid((w + K1_TW - 1) / K1_TW, (h + K1_TH - 1) / K1_TH, B);
-    kern<<<grid, 256, smem, s>>>(a, b2, dst, wl, h, w, H, W, sf_scale);
+    kern<<<grid, 256, smem, s>>>(a, b2, dst, wl, h, w, H, W, sf_scale, sync);
     return launch_status();
 }
 
@@ -348,13 +357,13 @@ extern "C" int b200_dcepp_pack_weights(const float* const* dw_w, const float* co
     return launch_status();
 }
 
-// workspace: 5 feature-map buffers [B,32,h,w] + the low-res / full-res 3-channel map
+// workspace: 5 feature-map buffers [B,32,h,w] | the low-res / full-res 3-channel map | the net launch's sync words
 extern "C" size_t b200_dcepp_workspace_bytes(int B, int H, int W, int sf) {
     if (B <= 0 || H <= 0 || W <= 0 || sf <= 0) return 0;
     const size_t h = H / sf, w = W / sf;
     const size_t fmap = align_up((size_t)B * 32 * h * w * sizeof(float), 256);
     const size_t amap = align_up((size_t)B * 3 * h * w * sizeof(float), 256);
-    return 5 * fmap + amap;
+    return 5 * fmap + amap + align_up(mm_sync_words(B, (int)h, (int)w) * sizeof(int), 256);
 }
 
 extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_lr, int B, int H, int W, int sf,
@@ -366,7 +375,8 @@ extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_l
     if (!aligned16(x) || !aligned16(packed) || !aligned16(a_lr) || !aligned16(workspace)) return B200_ERR_MISALIGNED;
     const int h = H / sf, w = W / sf;
     const size_t fmap = align_up((size_t)B * 32 * h * w * sizeof(float), 256);
-    if (workspace_bytes < 5 * fmap) return B200_ERR_WORKSPACE;
+    const size_t amap = align_up((size_t)B * 3 * h * w * sizeof(float), 256);
+    if (workspace_bytes < b200_dcepp_workspace_bytes(B, H, W, sf)) return B200_ERR_WORKSPACE;
     cudaStream_t s = (cudaStream_t)stream;
     char* ws = (char*)workspace;
     float* x1 = (float*)(ws + 0 * fmap);
@@ -376,15 +386,22 @@ extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_l
     float* x5 = (float*)(ws + 4 * fmap);
     float* x6 = x4;  // x4 is dead once layer 5 has run
     const float sfs = (float)sf;
+    int* sync = (int*)(ws + 5 * fmap + amap);
     int rc;
-    if ((rc = launch_k1<3, 1, 8, true, false>(x, nullptr, x1, packed + pp_layer_offset(0), B, h, w, H, W, sfs, s))) return rc;
+    if ((rc = launch_k1<3, 1, 8, true, false>(x, nullptr, x1, packed + pp_layer_offset(0), B, h, w, H, W, sfs, sync, s)))
+        return rc;
     const uint32_t* mm = reinterpret_cast<const uint32_t*>(packed + PP_TOTAL_FLOATS);
-    if ((rc = launch_mm<1, 4, false>(x1, nullptr, x2, mm + mm_offset(1), B, h, w, s))) return rc;
-    if ((rc = launch_mm<1, 4, false>(x2, nullptr, x3, mm + mm_offset(2), B, h, w, s))) return rc;
-    if ((rc = launch_mm<1, 4, false>(x3, nullptr, x4, mm + mm_offset(3), B, h, w, s))) return rc;
-    if ((rc = launch_mm<2, 4, false>(x3, x4, x5, mm + mm_offset(4), B, h, w, s))) return rc;
-    if ((rc = launch_mm<2, 4, false>(x2, x5, x6, mm + mm_offset(5), B, h, w, s))) return rc;
-    if ((rc = launch_mm<2, 1, true>(x1, x6, a_lr, mm + mm_offset(6), B, h, w, s))) return rc;
+    MmNetArgs a;  // e_conv2..7 (zero_dcepp.py:191-196): x2 x3 x4 | cat(x3,x4) -> x5 | cat(x2,x5) -> x6 | cat(x1,x6) -> x_r
+    const float* sa[6] = {x1, x2, x3, x3, x2, x1};
+    const float* sb[6] = {nullptr, nullptr, nullptr, x4, x5, x6};
+    float* ds[6] = {x2, x3, x4, x5, x6, a_lr};
+    for (int l = 0; l < 6; ++l) {
+        a.srcA[l] = sa[l];
+        a.srcB[l] = sb[l];
+        a.dst[l] = ds[l];
+        a.wl[l] = mm + mm_offset(l + 1);
+    }
+    if ((rc = launch_mm_net(a, B, h, w, sync, s))) return rc;
     return B200_OK;
 }
 

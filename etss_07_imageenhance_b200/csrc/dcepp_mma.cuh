@@ -92,13 +92,14 @@ constexpr int mm_smem_bytes() {
     return 4 * (MM_HALO_FLOATS + NSRC * 32 * 12 + 32 + NSRC * 2 * NT * 128);
 }
 
-// srcA / srcB: [B,32,h,w] fp32 planes (torch.cat never materialised); dst: [B,COUT,h,w]; wl: this layer's block
+// One 8 x 32 output tile of one layer.  srcA / srcB: [B,32,h,w] fp32 planes (torch.cat never materialised);
+// dst: [B,COUT,h,w]; wl: this layer's packed block; mm_smem: mm_smem_bytes<NSRC, NT>() of shared memory.
+// Every thread of the 256-thread CTA must call it (it synchronises the CTA).
 template <int NSRC, int NT, bool TANH>
-__global__ void __launch_bounds__(256, 3)
-dcepp_mma_layer_kernel(const float* __restrict__ srcA, const float* __restrict__ srcB, float* __restrict__ dst,
-                       const uint32_t* __restrict__ wl, int h, int w) {
+__device__ __forceinline__ void mm_tile(const float* __restrict__ srcA, const float* __restrict__ srcB,
+                                        float* __restrict__ dst, const uint32_t* __restrict__ wl, int h, int w, int b,
+                                        int y0, int x0, uint32_t* mm_smem) {
     constexpr int CIN = 32 * NSRC, KT = CIN / 16, COUT = TANH ? 3 : 32;
-    extern __shared__ __align__(16) uint32_t mm_smem[];
     float* s_halo = reinterpret_cast<float*>(mm_smem);
     float* s_dw = s_halo + MM_HALO_FLOATS;            // [CIN][12]
     float* s_pb = s_dw + CIN * 12;                    // [32]
@@ -106,8 +107,6 @@ dcepp_mma_layer_kernel(const float* __restrict__ srcA, const float* __restrict__
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int g = lane >> 2, c = lane & 3;
-    const int b = blockIdx.z;
-    const int y0 = blockIdx.y * MM_TH, x0 = blockIdx.x * MM_TW;
     const int wy = (warp >> 2) * 4, wx = (warp & 3) * 8;
 
     {  // weights -> smem (same layout as the packed block)
@@ -125,31 +124,34 @@ dcepp_mma_layer_kernel(const float* __restrict__ srcA, const float* __restrict__
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[mt][nt][i] = 0.f;
 
+    const size_t plane = (size_t)h * w;
 #pragma unroll 1
     for (int s = 0; s < NSRC; ++s) {
-        const float* src = (s == 0 ? srcA : srcB) + (size_t)b * 32 * h * w;
+        const float* src = (s == 0 ? srcA : srcB) + (size_t)b * 32 * plane;
         __syncthreads();  // previous source's halo consumers are done (and weights are visible on the first pass)
         // ---- halo tile: 32 channels x 10 rows x (1 + 32 + 1) columns, zero padded, via cp.async ----
         {
             const uint32_t sh = tc::smem_u32(s_halo);
             if ((w & 3) == 0) {
-                // interior: 8 x 16-byte chunks per (channel, row)
-                for (int i = t; i < 320 * 8; i += 256) {
-                    const int p = i >> 3, j = i & 7;
-                    const int ch = p / 10, rr = p - ch * 10;
-                    const int yy = y0 - 1 + rr, xa = x0 + 4 * j;
-                    const bool ok = yy >= 0 && yy < h && xa < w;
-                    const float* gp = src + (ok ? ((size_t)ch * h + yy) * w + xa : (size_t)0);
-                    tc::cp_async16(sh + (ch * MM_S + rr * MM_P + MM_C0 + 1 + 4 * j) * 4, gp, ok);
+                // interior: thread = (channel t/8, 16-byte chunk t%8), one chunk per halo row: no index division
+                const int ch = t >> 3, j = t & 7;
+                const int xa = x0 + 4 * j;
+                const bool xok = xa < w;
+                const float* gp = src + (size_t)ch * plane + xa;
+                const uint32_t sp = sh + (ch * MM_S + MM_C0 + 1 + 4 * j) * 4;
+#pragma unroll
+                for (int rr = 0; rr < 10; ++rr) {
+                    const int yy = y0 - 1 + rr;
+                    const bool ok = xok && yy >= 0 && yy < h;
+                    tc::cp_async16(sp + rr * MM_P * 4, ok ? gp + (ptrdiff_t)yy * w : src, ok);
                 }
-                // the two edge columns x0 - 1 and x0 + 32
-                for (int i = t; i < 320 * 2; i += 256) {
-                    const int p = i >> 1, e = i & 1;
-                    const int ch = p / 10, rr = p - ch * 10;
-                    const int yy = y0 - 1 + rr, xa = e ? x0 + 32 : x0 - 1;
-                    const bool ok = yy >= 0 && yy < h && xa >= 0 && xa < w;
-                    const float* gp = src + (ok ? ((size_t)ch * h + yy) * w + xa : (size_t)0);
-                    tc::cp_async4(sh + (ch * MM_S + rr * MM_P + MM_C0 + (e ? 33 : 0)) * 4, gp, ok);
+                // the two edge columns x0 - 1 and x0 + 32: thread = (channel, 8 of the 20 (row, side) slots)
+                for (int e = j; e < 20; e += 8) {
+                    const int rr = e >> 1, side = e & 1;
+                    const int yy = y0 - 1 + rr, xe = side ? x0 + 32 : x0 - 1;
+                    const bool ok = yy >= 0 && yy < h && xe >= 0 && xe < w;
+                    tc::cp_async4(sh + (ch * MM_S + rr * MM_P + MM_C0 + (side ? 33 : 0)) * 4,
+                                  ok ? src + (size_t)ch * plane + (size_t)yy * w + xe : src, ok);
                 }
             } else {
                 for (int i = t; i < 320 * 34; i += 256) {
@@ -215,39 +217,129 @@ dcepp_mma_layer_kernel(const float* __restrict__ srcA, const float* __restrict__
     }
 
     // ---- epilogue: bias + activation, NCHW stores.  acc[mt][nt] = {(row g, n 2c), (g, 2c+1), (g+8, 2c), (g+8, 2c+1)}
+    // one base pointer per thread, then constant multiples of the plane / row pitch
     const int xx = x0 + wx + g;
-    if (xx >= w) return;
+    if (xx < w) {
+        float* dp = dst + ((size_t)b * COUT + 2 * c) * plane + (size_t)(y0 + wy) * w + xx;
+        const int rows = h - (y0 + wy);  // valid rows of this warp's 4
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt) {
+        for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            const int yy = y0 + wy + 2 * mt + half;
-            if (yy >= h) continue;
+            for (int e = 0; e < 2; ++e) {
+                const int oc = nt * 8 + 2 * c + e;
+                if (COUT < 32 && oc >= COUT) continue;
+                const float pb = s_pb[oc];
+                float* q = dp + (size_t)(nt * 8 + e) * plane;
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) {
-#pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int oc = nt * 8 + 2 * c + e;
-                    if (oc >= COUT) continue;
-                    const float u = acc[mt][nt][half * 2 + e] + s_pb[oc];
-                    dst[((size_t)(b * COUT + oc) * h + yy) * w + xx] = TANH ? tanhf(u) : fmaxf(u, 0.f);
+                for (int r = 0; r < 4; ++r) {  // image row y0 + wy + r = m-tile r / 2, half r % 2
+                    const float u = acc[r >> 1][nt][(r & 1) * 2 + e] + pb;
+                    if (r < rows) q[(size_t)r * w] = TANH ? tanhf(u) : fmaxf(u, 0.f);
                 }
             }
         }
     }
 }
 
-template <int NSRC, int NT, bool TANH>
-static int launch_mm(const float* a, const float* b2, float* dst, const uint32_t* wl, int B, int h, int w,
-                     cudaStream_t s) {
-    auto kern = dcepp_mma_layer_kernel<NSRC, NT, TANH>;
-    constexpr int smem = mm_smem_bytes<NSRC, NT>();
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+// ------------------------------------------------------------------------------------------------
+// Layers 2..7 as ONE persistent launch.  The 6 x (B x tiles) output tiles form a single layer-major work
+// list; CTAs draw tile numbers from a global counter and a tile of layer l starts as soon as the (up to)
+// nine layer l-1 tiles under its halo have been published -- no launch boundary, no wave tail between
+// layers, and the last tiles of layer l overlap the first tiles of layer l+1.  Deadlock-free: a CTA
+// only ever waits on tiles with smaller numbers, and those were drawn earlier by CTAs that are resident
+// (grid <= one resident wave) and wait only on still smaller numbers.
+//
+// sync words (caller's workspace, zeroed by layer 1's launch): [0] = work counter, [MM_FLAG0 + q] = tile q
+// of layers 2..6 published (layer 7 has no consumer in this launch).
+// ------------------------------------------------------------------------------------------------
+constexpr int MM_FLAG0 = 32;  // flags start one 128-byte line after the counter
+
+struct MmNetArgs {
+    const float* srcA[6];
+    const float* srcB[6];
+    float* dst[6];
+    const uint32_t* wl[6];
+};
+
+__host__ __device__ inline size_t mm_sync_words(int B, int h, int w) {
+    const size_t tiles = (size_t)B * ((h + MM_TH - 1) / MM_TH) * ((w + MM_TW - 1) / MM_TW);
+    return MM_FLAG0 + 5 * tiles;
+}
+
+__device__ __forceinline__ int mm_ld_acquire(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mm_st_release(int* p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+constexpr int MM_NET_SMEM = mm_smem_bytes<2, 4>();
+
+__global__ void __launch_bounds__(256, 3)
+dcepp_net_kernel(MmNetArgs a, int B, int h, int w, int* __restrict__ sync) {
+    extern __shared__ __align__(16) uint32_t mm_smem[];
+    __shared__ int s_q;
+    const int t = threadIdx.x;
+    const int ntx = (w + MM_TW - 1) / MM_TW, nty = (h + MM_TH - 1) / MM_TH;
+    const int tpf = ntx * nty, tpl = B * tpf, total = 6 * tpl;
+    int* flags = sync + MM_FLAG0;
+    for (;;) {
+        __syncthreads();  // every thread has read s_q / finished with the previous tile's smem
+        if (t == 0) s_q = atomicAdd(sync, 1);
+        __syncthreads();
+        const int q = s_q;
+        if (q >= total) break;
+        const int l = q / tpl, r = q - l * tpl;
+        const int b = r / tpf, r2 = r - b * tpf;
+        const int tyi = r2 / ntx, txi = r2 - tyi * ntx;
+        if (l > 0) {
+            if (t < 9) {  // the nine layer l-1 tiles under this tile's halo
+                const int ny = tyi + t / 3 - 1, nx = txi + t % 3 - 1;
+                if (ny >= 0 && ny < nty && nx >= 0 && nx < ntx) {
+                    const int* f = flags + (size_t)(l - 1) * tpl + b * tpf + ny * ntx + nx;
+                    while (mm_ld_acquire(f) == 0) __nanosleep(40);
+                }
+            }
+            __syncthreads();
+        }
+        const int y0 = tyi * MM_TH, x0 = txi * MM_TW;
+        const float *sa = nullptr, *sb = nullptr;  // selected with constant indices: the kernel parameters stay in
+        float* ds = nullptr;                       // the constant bank (a dynamic index would spill them to the stack)
+        const uint32_t* wl = nullptr;
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            if (i == l) sa = a.srcA[i], sb = a.srcB[i], ds = a.dst[i], wl = a.wl[i];
+        if (l < 3)
+            mm_tile<1, 4, false>(sa, nullptr, ds, wl, h, w, b, y0, x0, mm_smem);
+        else if (l < 5)
+            mm_tile<2, 4, false>(sa, sb, ds, wl, h, w, b, y0, x0, mm_smem);
+        else
+            mm_tile<2, 1, true>(sa, sb, ds, wl, h, w, b, y0, x0, mm_smem);
+        if (l < 5) {
+            __syncthreads();  // all of this tile's stores are issued
+            if (t == 0) mm_st_release(flags + q, 1);
+        }
+    }
+}
+
+static int launch_mm_net(const MmNetArgs& a, int B, int h, int w, int* sync, cudaStream_t s) {
+    auto kern = dcepp_net_kernel;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MM_NET_SMEM) != cudaSuccess) {
         (void)cudaGetLastError();
         return B200_ERR_LAUNCH;
     }
-    dim3 grid((w + MM_TW - 1) / MM_TW, (h + MM_TH - 1) / MM_TH, B);
-    kern<<<grid, 256, smem, s>>>(a, b2, dst, wl, h, w);
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, MM_NET_SMEM) != cudaSuccess || occ < 1) {
+        (void)cudaGetLastError();
+        return B200_ERR_LAUNCH;  // the wait-on-earlier-tiles scheme needs every CTA resident
+    }
+    int dev = 0, sms = B200_NUM_SMS;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long total = 6LL * B * ((h + MM_TH - 1) / MM_TH) * ((w + MM_TW - 1) / MM_TW);
+    long long grid = (long long)sms * occ;
+    if (grid > total) grid = total;
+    kern<<<(unsigned)grid, 256, MM_NET_SMEM, s>>>(a, B, h, w, sync);
     return launch_status();
 }
 
