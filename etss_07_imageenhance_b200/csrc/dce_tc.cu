@@ -34,6 +34,7 @@
 #include "common.cuh"
 #include "dce_tc.cuh"
 #include "tcgen05.cuh"
+#include "tma_host.cuh"
 
 namespace b200 {
 using namespace tc;
@@ -549,29 +550,10 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
 // ------------------------------------------------------------------------------------------------
 static size_t tc_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-typedef CUresult (*tc_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency)
-static tc_encode_fn tc_encoder() {
-    static tc_encode_fn fn = []() -> tc_encode_fn {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
-            q != cudaDriverEntryPointSuccess) {
-            (void)cudaGetLastError();
-            return nullptr;
-        }
-        return reinterpret_cast<tc_encode_fn>(p);
-    }();
-    return fn;
-}
-
 // NHWC bf16 [B,H,W,32] as a 4-D tensor (c, x, y, b); box = 32 channels x 130 pixels of one row; 64-byte swizzle;
 // coordinates outside the image (x = -1, x >= W, y = -1, y >= H) are zero-filled = the conv's zero padding.
 static int tc_make_map(CUtensorMap* m, const void* base, int B, int H, int W, int box_px = TC_SPX) {
-    tc_encode_fn enc = tc_encoder();
+    tma_encode_fn enc = tma_encoder();
     if (!enc) return B200_ERR_LAUNCH;
     const cuuint64_t dims[4] = {32, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
     const cuuint64_t strides[3] = {64, (cuuint64_t)W * 64, (cuuint64_t)H * W * 64};

@@ -208,28 +208,43 @@ dcepp_layer_kernel(const float* __restrict__ srcA, const float* __restrict__ src
         }
     }
 
-    // ---- epilogue: bias + activation, NCHW stores (4 consecutive px per thread per output plane) ----
+    // ---- epilogue: bias + activation; 4 consecutive px per thread ----
     const int r = pg >> 3, c4 = (pg & 7) * 4;
     const int yy = y0 + r, xx = x0 + c4;
     if (yy >= h) return;
+    if (!TANH) {
+        // channel-pair interleaved feature map [B][16][h][wp] float2 (dcepp_mma.cuh): this thread's NOUT outputs are
+        // NOUT/2 whole pairs; 4 px of a pair = 32 contiguous bytes
+        const int wp = mm_pitch(w);
 #pragma unroll
-    for (int o = 0; o < NOUT; ++o) {
-        const int oc = og * NOUT + o;
-        if (oc >= COUT) continue;
-        const float bias = s_pwb[oc];
-        float v[4];
-#pragma unroll
-        for (int p = 0; p < 4; ++p) {
-            float u = ((o & 1) ? acc[p][o >> 1].y : acc[p][o >> 1].x) + bias;
-            v[p] = TANH ? tanhf(u) : fmaxf(u, 0.f);
-        }
-        float* d = dst + ((size_t)(b * COUT + oc) * h + yy) * w + xx;
-        if ((w & 3) == 0 && xx + 3 < w) {
-            *reinterpret_cast<float4*>(d) = make_float4(v[0], v[1], v[2], v[3]);
-        } else {
+        for (int o2 = 0; o2 < NOUT / 2; ++o2) {
+            const float2 bias = *reinterpret_cast<const float2*>(s_pwb + og * NOUT + 2 * o2);
+            float2 v[4];
 #pragma unroll
             for (int p = 0; p < 4; ++p)
-                if (xx + p < w) d[p] = v[p];
+                v[p] = make_float2(fmaxf(acc[p][o2].x + bias.x, 0.f), fmaxf(acc[p][o2].y + bias.y, 0.f));
+            float2* d = reinterpret_cast<float2*>(dst) + ((size_t)(b * 16 + og * (NOUT / 2) + o2) * h + yy) * wp + xx;
+            if (xx + 3 < w) {
+                reinterpret_cast<float4*>(d)[0] = make_float4(v[0].x, v[0].y, v[1].x, v[1].y);
+                reinterpret_cast<float4*>(d)[1] = make_float4(v[2].x, v[2].y, v[3].x, v[3].y);
+            } else {
+#pragma unroll
+                for (int p = 0; p < 4; ++p)
+                    if (xx + p < w) d[p] = v[p];
+            }
+        }
+    } else {
+#pragma unroll
+        for (int o = 0; o < NOUT; ++o) {
+            const int oc = og * NOUT + o;
+            if (oc >= COUT) continue;
+            const float bias = s_pwb[oc];
+            float* d = dst + ((size_t)(b * COUT + oc) * h + yy) * w + xx;
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const float u = ((o & 1) ? acc[p][o >> 1].y : acc[p][o >> 1].x) + bias;
+                if (xx + p < w) d[p] = tanhf(u);
+            }
         }
     }
 }
@@ -335,6 +350,8 @@ dcepp_apply_scalar_kernel(const float* __restrict__ x, const float* __restrict__
 }
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+// one feature map: [B][16 channel pairs][h][mm_pitch(w)] float2
+static size_t fmap_bytes(int B, int h, int w) { return align_up((size_t)B * 16 * h * mm_pitch(w) * sizeof(float2), 256); }
 
 }  // namespace b200
 
@@ -361,7 +378,7 @@ extern "C" int b200_dcepp_pack_weights(const float* const* dw_w, const float* co
 extern "C" size_t b200_dcepp_workspace_bytes(int B, int H, int W, int sf) {
     if (B <= 0 || H <= 0 || W <= 0 || sf <= 0) return 0;
     const size_t h = H / sf, w = W / sf;
-    const size_t fmap = align_up((size_t)B * 32 * h * w * sizeof(float), 256);
+    const size_t fmap = fmap_bytes(B, (int)h, (int)w);
     const size_t amap = align_up((size_t)B * 3 * h * w * sizeof(float), 256);
     return 5 * fmap + amap + align_up(mm_sync_words(B, (int)h, (int)w) * sizeof(int), 256);
 }
@@ -374,7 +391,7 @@ extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_l
     if (B > 65535) return B200_ERR_UNSUPPORTED;
     if (!aligned16(x) || !aligned16(packed) || !aligned16(a_lr) || !aligned16(workspace)) return B200_ERR_MISALIGNED;
     const int h = H / sf, w = W / sf;
-    const size_t fmap = align_up((size_t)B * 32 * h * w * sizeof(float), 256);
+    const size_t fmap = fmap_bytes(B, h, w);
     const size_t amap = align_up((size_t)B * 3 * h * w * sizeof(float), 256);
     if (workspace_bytes < b200_dcepp_workspace_bytes(B, H, W, sf)) return B200_ERR_WORKSPACE;
     cudaStream_t s = (cudaStream_t)stream;
@@ -392,16 +409,13 @@ extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_l
         return rc;
     const uint32_t* mm = reinterpret_cast<const uint32_t*>(packed + PP_TOTAL_FLOATS);
     MmNetArgs a;  // e_conv2..7 (zero_dcepp.py:191-196): x2 x3 x4 | cat(x3,x4) -> x5 | cat(x2,x5) -> x6 | cat(x1,x6) -> x_r
-    const float* sa[6] = {x1, x2, x3, x3, x2, x1};
-    const float* sb[6] = {nullptr, nullptr, nullptr, x4, x5, x6};
     float* ds[6] = {x2, x3, x4, x5, x6, a_lr};
     for (int l = 0; l < 6; ++l) {
-        a.srcA[l] = sa[l];
-        a.srcB[l] = sb[l];
         a.dst[l] = ds[l];
         a.wl[l] = mm + mm_offset(l + 1);
     }
-    if ((rc = launch_mm_net(a, B, h, w, sync, s))) return rc;
+    float* maps[5] = {x1, x2, x3, x4, x5};
+    if ((rc = launch_mm_net(a, maps, B, h, w, sync, s))) return rc;
     return B200_OK;
 }
 
@@ -460,7 +474,7 @@ extern "C" int b200_dcepp_forward(const float* x, const float* packed, float* en
     if (H % sf != 0 || W % sf != 0) return B200_ERR_BAD_SHAPE;
     if (workspace_bytes < b200_dcepp_workspace_bytes(B, H, W, sf)) return B200_ERR_WORKSPACE;
     const int h = H / sf, w = W / sf;
-    const size_t fmap = align_up((size_t)B * 32 * h * w * sizeof(float), 256);
+    const size_t fmap = fmap_bytes(B, h, w);
     float* a_ws = (float*)((char*)workspace + 5 * fmap);
     int rc;
     if (sf == 1) {
