@@ -66,7 +66,7 @@ __host__ __device__ constexpr int mm_offset(int l) {
 }
 constexpr int MM_TOTAL_WORDS = mm_offset(7);
 constexpr int MM_W_WORDS_MAX = mm_words(4);
-constexpr int MM_NET_SMEM = MM_NS * MM_STAGE_BYTES + MM_W_WORDS_MAX * 4 + 2 * MM_NS * 8 + 16;
+constexpr int MM_NET_SMEM = MM_NS * MM_STAGE_BYTES + MM_W_WORDS_MAX * 4 + 2 * MM_NS * 8 + 4 * 16 + 16;
 
 __device__ __forceinline__ uint32_t mm_pack_bf16x2(float lo_elem, float hi_elem) {
     __nv_bfloat162 h = __floats2bfloat162_rn(lo_elem, hi_elem);  // .x (low 16 bits) = lo_elem
@@ -177,25 +177,30 @@ __device__ __forceinline__ void mm_tile(const uint8_t* ring, uint64_t* full, uin
             const float2 wk[9] = {make_float2(q0.x, q0.y), make_float2(q0.z, q0.w), make_float2(q1.x, q1.y),
                                   make_float2(q1.z, q1.w), make_float2(q2.x, q2.y), make_float2(q2.z, q2.w),
                                   make_float2(q3.x, q3.y), make_float2(q3.z, q3.w), make_float2(q4.x, q4.y)};
-            float2 o[4];
-#pragma unroll
-            for (int oo = 0; oo < 4; ++oo) o[oo] = make_float2(q4.z, q4.w);  // depthwise bias
+            // three independent partial sums per output (one per filter column): 12 short dependency chains instead
+            // of 4 long ones keep the packed-FMA pipe fed at 4-5 warps per scheduler
+            float2 o[4][3];
             const float2* hp = st + p * MM_PS + wy * MM_HC + wx + g + (MM_XOFF - 1);
 #pragma unroll
             for (int r = 0; r < 6; ++r) {
-                const float2 v0 = hp[r * MM_HC], v1 = hp[r * MM_HC + 1], v2 = hp[r * MM_HC + 2];
+                const float2 v[3] = {hp[r * MM_HC], hp[r * MM_HC + 1], hp[r * MM_HC + 2]};
 #pragma unroll
                 for (int dy = 0; dy < 3; ++dy) {
                     const int oo = r - dy;
                     if (oo >= 0 && oo < 4) {
-                        o[oo] = __ffma2_rn(wk[dy * 3 + 0], v0, o[oo]);
-                        o[oo] = __ffma2_rn(wk[dy * 3 + 1], v1, o[oo]);
-                        o[oo] = __ffma2_rn(wk[dy * 3 + 2], v2, o[oo]);
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx) {
+                            if (dy == 0)
+                                o[oo][dx] = dx == 0 ? __ffma2_rn(wk[dx], v[dx], make_float2(q4.z, q4.w))  // + bias
+                                                    : __fmul2_rn(wk[dx], v[dx]);
+                            else
+                                o[oo][dx] = __ffma2_rn(wk[dy * 3 + dx], v[dx], o[oo][dx]);
+                        }
                     }
                 }
             }
 #pragma unroll
-            for (int oo = 0; oo < 4; ++oo) val[j2][oo] = o[oo];
+            for (int oo = 0; oo < 4; ++oo) val[j2][oo] = __fadd2_rn(__fadd2_rn(o[oo][0], o[oo][1]), o[oo][2]);
         }
         __syncwarp();  // every lane's shared loads of this stage have returned
         if (lane == 0) tc::mbar_arrive(&empty[slot]);
@@ -258,7 +263,8 @@ dcepp_net_kernel(const MmNetArgs a, const __grid_constant__ CUtensorMap tm1, con
     float* s_w = reinterpret_cast<float*>(mm_smem + MM_NS * MM_STAGE_BYTES);
     uint64_t* full = reinterpret_cast<uint64_t*>(s_w + MM_W_WORDS_MAX);
     uint64_t* empty = full + MM_NS;
-    volatile int* s_tq = reinterpret_cast<volatile int*>(empty + MM_NS);  // tile numbers, producer -> consumers
+    // tile descriptors, producer -> consumers: {tile number q (-1 = end), layer + 8 * frame, y0, x0}
+    volatile int4* s_tq = reinterpret_cast<volatile int4*>(empty + MM_NS);
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int ntx = (w + MM_TW - 1) / MM_TW, nty = (h + MM_TH - 1) / MM_TH;
@@ -293,7 +299,7 @@ dcepp_net_kernel(const MmNetArgs a, const __grid_constant__ CUtensorMap tm1, con
                 const int slot = pk % MM_NS;
                 if (pk >= MM_NS) tc::mbar_wait(&empty[slot], ((pk / MM_NS) - 1) & 1);
                 if (lane == 0) {
-                    s_tq[tk & 3] = -1;
+                    s_tq[tk & 3].x = -1;
                     tc::mbar_arrive(&full[slot]);
                 }
                 break;
@@ -320,7 +326,8 @@ dcepp_net_kernel(const MmNetArgs a, const __grid_constant__ CUtensorMap tm1, con
                 if (pk >= MM_NS) tc::mbar_wait(&empty[slot], ((pk / MM_NS) - 1) & 1);
                 if (lane == 0) {
                     if (i == 0) {
-                        s_tq[tk & 3] = q;
+                        volatile int4* d = &s_tq[tk & 3];
+                        d->x = q, d->y = l + 8 * b, d->z = tyi * MM_TH, d->w = txi * MM_TW;
                         tc::fence_proxy_async_all();  // the acquired tiles were written through the generic proxy
                     }
                     tc::mbar_arrive_expect_tx(&full[slot], MM_STAGE_BYTES);
@@ -338,11 +345,10 @@ dcepp_net_kernel(const MmNetArgs a, const __grid_constant__ CUtensorMap tm1, con
     int ck = 0, tk = 0, cur_l = -1;
     for (;;) {
         tc::mbar_wait(&full[ck % MM_NS], (ck / MM_NS) & 1);  // the tile's first stage (or the end marker)
-        const int q = s_tq[tk & 3];
+        const int q = s_tq[tk & 3].x;
         if (q < 0) break;
-        const int l = q / tpl, r = q - l * tpl;
-        const int b = r / tpf, r2 = r - b * tpf;
-        const int tyi = r2 / ntx, txi = r2 - tyi * ntx;
+        const int lb = s_tq[tk & 3].y, y0 = s_tq[tk & 3].z, x0 = s_tq[tk & 3].w;
+        const int l = lb & 7, b = lb >> 3;
         const uint32_t* wl = nullptr;  // selected with constant indices: the kernel parameters stay in the constant
         float* ds = nullptr;           // bank (a dynamic index would copy them to the stack)
 #pragma unroll
@@ -355,14 +361,13 @@ dcepp_net_kernel(const MmNetArgs a, const __grid_constant__ CUtensorMap tm1, con
             tc::named_bar_sync(1, 256);
             cur_l = l;
         }
-        const int y0 = tyi * MM_TH, x0 = txi * MM_TW;
         if (l < 3)
             mm_tile<1, 4, false>(ring, full, empty, ck, s_w, ds, h, w, wp, b, y0, x0);
         else if (l < 5)
             mm_tile<2, 4, false>(ring, full, empty, ck, s_w, ds, h, w, wp, b, y0, x0);
         else
             mm_tile<2, 1, true>(ring, full, empty, ck, s_w, ds, h, w, wp, b, y0, x0);
-        tc::named_bar_sync(1, 256);  // all of this tile's stores are issued; nobody reads the weights any more
+        tc::named_bar_sync(1, 256);  // all of this tile's stores are issued
         if (l < 5 && t == 0) mm_st_release(flags + q, 1);
         ++tk;
     }
