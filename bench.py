@@ -383,7 +383,7 @@ def run_b200(args) -> None:
                     "d2h_bytes_per_step": host_out.numel() * 4, "ms_per_step": e2e_ms / e2e_steps,
                     "path": "FramePipeline(wire=f32): pinned host x -> H2D -> b200_dcepp_forward -> D2H enhanced, "
                             "2-frame chunks on 3 streams", "matches_device_result": e2e_ok, "u8_wire": u8},
-            "gpu_launches": args.steps * 8,
+            "gpu_launches": args.steps * 3,  # layer-1 kernel + persistent net kernel + full-resolution pass
             "roofline": {"bound": "hbm", "kernel": "dcepp_apply_vec4_kernel<true>", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                          "peak_source": hbm_src, "bytes_per_launch": px_step * BYTES_PER_PX,
