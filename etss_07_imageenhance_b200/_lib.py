@@ -47,6 +47,7 @@ _SIGNATURES = {
     "b200_sci_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "b200_u8hwc_to_f32nchw": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "b200_f32nchw_to_u8hwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "b200_resize_bilinear": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
 }
 EXPORTS = tuple(_SIGNATURES)
 

@@ -173,6 +173,31 @@ int curve_per_iter_unaligned_ok(const float* x, const float* a, float* y, int B,
     return launch_curve<true>(x, a, y, B, C, H, W, iters, (void*)s, false);
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Bilinear resize, align_corners=False, no antialias: core.resize -> kornia resize -> F.interpolate(size=...,
+// mode="bilinear") (core/image/geometry/transform.py:218-228), the pre/post step of VisionModel.infer
+// (vision/model.py:100-121).  ATen's index math (area_pixel_compute_source_index with scale = in / out) and its
+// evaluation order  h0*(w0*v00 + w1*v01) + h1*(w0*v10 + w1*v11).  One thread per output pixel, all planes of it.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+resize_bilinear_kernel(const float* __restrict__ src, float* __restrict__ dst, int planes, int Hi, int Wi, int Ho,
+                       int Wo, float sh, float sw) {
+    const long long n = (long long)Ho * Wo;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+        const int X = (int)(i % Wo), Y = (int)(i / Wo);
+        const Tap ty = tap_half_pixel(Y, sh, Hi), tx = tap_half_pixel(X, sw, Wi);
+        const size_t o00 = (size_t)ty.i0 * Wi + tx.i0, o01 = (size_t)ty.i0 * Wi + tx.i1;
+        const size_t o10 = (size_t)ty.i1 * Wi + tx.i0, o11 = (size_t)ty.i1 * Wi + tx.i1;
+        for (int p = 0; p < planes; ++p) {
+            const float* s = src + (size_t)p * Hi * Wi;
+            const float top = __fadd_rn(__fmul_rn(tx.w0, __ldg(s + o00)), __fmul_rn(tx.w1, __ldg(s + o01)));
+            const float bot = __fadd_rn(__fmul_rn(tx.w0, __ldg(s + o10)), __fmul_rn(tx.w1, __ldg(s + o11)));
+            dst[(size_t)p * n + i] = __fadd_rn(__fmul_rn(ty.w0, top), __fmul_rn(ty.w1, bot));
+        }
+    }
+}
+
 }  // namespace b200
 
 extern "C" int b200_curve_shared(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters,
@@ -206,5 +231,18 @@ extern "C" int b200_f32nchw_to_u8hwc(const float* src, uint8_t* dst, int B, int 
     long long blocks = ((long long)B * (hw / 4) + 255) / 256;
     if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
     b200::f32nchw_to_u8hwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, B, hw);
+    return b200::launch_status();
+}
+
+extern "C" int b200_resize_bilinear(const float* src, float* dst, int planes, int Hin, int Win, int Hout, int Wout,
+                                    void* stream) {
+    if (!src || !dst) return B200_ERR_NULL;
+    if (planes <= 0 || Hin <= 0 || Win <= 0 || Hout <= 0 || Wout <= 0) return B200_ERR_BAD_SHAPE;
+    // ATen area_pixel_compute_scale<float>(in, out, align_corners=false, scale=nullopt) = (float)in / out
+    const float sh = (float)Hin / (float)Hout, sw = (float)Win / (float)Wout;
+    long long blocks = ((long long)Hout * Wout + 255) / 256;
+    if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
+    b200::resize_bilinear_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, planes, Hin, Win, Hout,
+                                                                                    Wout, sh, sw);
     return b200::launch_status();
 }

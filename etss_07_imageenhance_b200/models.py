@@ -165,19 +165,40 @@ class _EnhancementModel(nn.Module):
     def device(self) -> torch.device:
         return next(self.parameters()).device
 
-    def infer(self, datapoint: dict, *args, **kwargs) -> dict:
-        """`VisionModel.infer` (vision/model.py:76-127) without the resize-to-multiple-of-32 step: moves
-        tensors to the model's device, runs `forward`, reports wall time under "time" (the reference
-        uses an unsynchronised `Timer`; this one synchronises so the number means something)."""
+    def infer(self, datapoint: dict, image_size: Any = 512, resize: bool = False, *args, **kwargs) -> dict:
+        """`VisionModel.infer` (vision/model.py:76-127): every image tensor of the datapoint is resized to
+        `image_size` (`resize=True`) or up to the next multiple of 32 (`core.resize(v, divisible_by=32)`,
+        core/image/utils.py:381-382 rounds with ceil), moved to the model's device, run through `forward`, and every
+        image in the outputs whose size differs from the input's is resized back to (h0, w0).  The resize is
+        `torch.ops.b200dce.resize_bilinear` (F.interpolate bilinear, align_corners=False -- what kornia's resize
+        calls).  "time" is the forward's wall time (the reference uses an unsynchronised `Timer`; this one
+        synchronises so the number means something) and is inserted FIRST so that `outputs.popitem()` still
+        yields "enhanced" (predict.py:91-98)."""
         self.assert_datapoint(datapoint)
-        dp = {k: (v.to(self.device) if isinstance(v, torch.Tensor) else v) for k, v in datapoint.items()}
+        h0, w0 = datapoint["image"].shape[-2:]
+        if resize:
+            th, tw = (image_size, image_size) if isinstance(image_size, int) else tuple(image_size)[-2:]
+        else:
+            th, tw = -(-h0 // 32) * 32, -(-w0 // 32) * 32
+        dp = {}
+        for k, v in datapoint.items():
+            if isinstance(v, torch.Tensor):
+                v = v.to(self.device)
+                if v.dim() == 4 and v.is_floating_point() and tuple(v.shape[-2:]) != (th, tw):
+                    v = torch.ops.b200dce.resize_bilinear(v.float(), th, tw)
+            dp[k] = v
         torch.cuda.synchronize(self.device)
         t0 = time.perf_counter()
         outputs = self.forward(datapoint=dp, *args, **kwargs)
         torch.cuda.synchronize(self.device)
-        outputs = {"time": time.perf_counter() - t0, **outputs}
-        # predict.py:91-98 pops "time" then takes the LAST item as the image to save
-        return outputs
+        elapsed = time.perf_counter() - t0
+        self.assert_outputs(outputs)
+        out = {"time": elapsed}
+        for k, v in outputs.items():
+            if isinstance(v, torch.Tensor) and v.dim() == 4 and tuple(v.shape[-2:]) != (h0, w0):
+                v = torch.ops.b200dce.resize_bilinear(v.contiguous(), h0, w0)
+            out[k] = v
+        return out
 
     # ---- packed-weight cache: rebuilt when any parameter's storage / version / device changes
     def _params_key(self, tensors) -> tuple:

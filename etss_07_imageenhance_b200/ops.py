@@ -22,7 +22,7 @@ from ._lib import PRECISIONS, check, lib, ptr_array
 
 __all__ = [
     "curve_shared", "curve_per_iter", "dcepp_pack", "dcepp_forward", "dcepp_lowres", "dcepp_apply",
-    "dce_pack", "dce_forward", "sci_pack", "sci_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc",
+    "dce_pack", "dce_forward", "sci_pack", "sci_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
     "current_stream_ptr", "require_device",
 ]
 
@@ -347,3 +347,25 @@ def f32nchw_to_u8hwc(image: Tensor) -> Tensor:
 def _(image):
     B, _, H, W = image.shape
     return image.new_empty(B, H, W, 3, dtype=torch.uint8)
+
+
+# ----------------------------------------------------------------------------- infer()'s resize (SURVEY §8f-2)
+@torch.library.custom_op("b200dce::resize_bilinear", mutates_args=(), device_types="cuda")
+def resize_bilinear(image: Tensor, height: int, width: int) -> Tensor:
+    """[B,C,H,W] float32 -> [B,C,height,width]: core.resize (core/image/geometry/transform.py:104-235) ->
+    F.interpolate(size=..., mode="bilinear", align_corners=False, antialias=False)."""
+    image = _img(image, "image", channels=None)
+    if height <= 0 or width <= 0:
+        raise ValueError(f"b200dce::resize_bilinear: bad target size {(height, width)}")
+    B, C, H, W = image.shape
+    out = torch.empty(B, C, height, width, dtype=torch.float32, device=image.device)
+    if B * C:
+        with torch.cuda.device(image.device):
+            check(lib().b200_resize_bilinear(image.data_ptr(), out.data_ptr(), B * C, H, W, height, width,
+                                             current_stream_ptr()), "b200_resize_bilinear")
+    return out
+
+
+@resize_bilinear.register_fake
+def _(image, height, width):
+    return image.new_empty(image.shape[0], image.shape[1], height, width)

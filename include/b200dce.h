@@ -152,6 +152,16 @@ int b200_sci_forward(const float* x, const float* packed_host, float* illu_or_nu
 int b200_u8hwc_to_f32nchw(const uint8_t* src, float* dst, int B, int H, int W, void* stream);
 int b200_f32nchw_to_u8hwc(const float* src, uint8_t* dst, int B, int H, int W, void* stream);
 
+/* ------------------------------------------------------------------------- *
+ * "next" rows: the resize of VisionModel.infer
+ * (src/mon/vision/model.py:100-121): core.resize(v, divisible_by=32) before the
+ * forward and core.resize(v, (h0, w0)) after it =
+ * src/mon/core/image/geometry/transform.py:104-235 -> kornia resize ->
+ * F.interpolate(size=(Hout, Wout), mode="bilinear", align_corners=False,
+ * antialias=False).  src [planes,Hin,Win] -> dst [planes,Hout,Wout], fp32.
+ * ------------------------------------------------------------------------- */
+int b200_resize_bilinear(const float* src, float* dst, int planes, int Hin, int Win, int Hout, int Wout, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

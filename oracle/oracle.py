@@ -31,6 +31,8 @@ restatements of ATen's `upsample_bilinear2d` index math
 """
 from __future__ import annotations
 
+import math
+
 import numpy as np
 import torch
 import torch.nn.functional as F
@@ -294,6 +296,25 @@ def bilinear_up_ref(a: np.ndarray, H: int, W: int) -> np.ndarray:
             out[:, :, Y, X] = wy0 * (wx0 * a[:, :, y0, x0] + wx1 * a[:, :, y0, x1]) + \
                 wy1 * (wx0 * a[:, :, y1, x0] + wx1 * a[:, :, y1, x1])
     return out
+
+
+def infer_resize(x: torch.Tensor, size=None, divisible_by: int = 32) -> torch.Tensor:
+    """core.resize(image, size | divisible_by=32) for tensors (core/image/geometry/transform.py:104-235 with
+    core/image/utils.py:381-382: ceil to the next multiple) -> kornia.geometry.transform.resize ->
+    F.interpolate(size=..., mode="bilinear", align_corners=None, antialias=False)."""
+    if size is None:
+        h, w = x.shape[-2:]
+        size = (int(math.ceil(h / divisible_by) * divisible_by), int(math.ceil(w / divisible_by) * divisible_by))
+    return F.interpolate(x, size=tuple(size), mode="bilinear", align_corners=None, antialias=False)
+
+
+def infer(forward, x: torch.Tensor) -> dict:
+    """VisionModel.infer (vision/model.py:76-127) around a `forward(x) -> dict` restatement: resize up to a multiple
+    of 32, forward, resize every image output back to the input size."""
+    h0, w0 = x.shape[-2:]
+    out = forward(infer_resize(x))
+    return {k: (infer_resize(v, (h0, w0)) if isinstance(v, torch.Tensor) and v.dim() == 4 and
+                tuple(v.shape[-2:]) != (h0, w0) else v) for k, v in out.items()}
 
 
 def psnr(a: torch.Tensor, b: torch.Tensor) -> float:

@@ -294,3 +294,33 @@ def test_frame_pipeline_matches_direct_forward(cuda_dev, wire):
         ref = torch.ops.b200dce.f32nchw_to_u8hwc(m({"image": x})["enhanced"]).cpu()
         assert torch.equal(host_out, ref)
     assert pipe.launches > 0
+
+
+# ------------------------------------------------------------------ VisionModel.infer resize shim
+@pytest.mark.parametrize("hin,win,hout,wout", [(50, 70, 64, 96), (64, 96, 50, 70), (1080, 1920, 1088, 1920),
+                                               (37, 45, 37, 45), (5, 7, 64, 32), (33, 17, 1, 1)])
+def test_resize_bilinear_vs_aten(cuda_dev, hin, win, hout, wout):
+    x = O.synthetic_lowlight(2, hin, win, seed=77)
+    ref = O.infer_resize(x, (hout, wout))
+    got = torch.ops.b200dce.resize_bilinear(x.to(cuda_dev), hout, wout)
+    assert got.shape == ref.shape
+    assert maxerr(got, ref) <= 1e-6
+
+
+@pytest.mark.parametrize("H,W", [(50, 70), (64, 96), (100, 36)])
+def test_infer_resizes_to_multiple_of_32_and_back(cuda_dev, H, W):
+    x = O.synthetic_lowlight(2, H, W, seed=78)
+    sd = O.make_dcepp_state_dict(23, "stress")
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=1), sd).to(cuda_dev)
+    out = m.infer({"image": x})                      # CPU tensor in: infer moves it to the model's device
+    ref = O.infer(lambda t: O.zero_dcepp_forward(t, sd, scale_factor=1), x)
+    assert list(out.keys()) == ["time", "adjust", "enhanced"] and out["time"] > 0
+    out.pop("time")
+    k, v = out.popitem()                             # predict.py:91-98 takes the last item as the image to save
+    assert k == "enhanced" and v.shape == x.shape
+    assert maxerr(v, ref["enhanced"]) <= TIGHT_PP
+    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT_PP
+    # resize=True: fixed square model input (image_size), outputs back at the input size
+    out2 = m.infer({"image": x}, image_size=64, resize=True)
+    ref2 = O.infer_resize(O.zero_dcepp_forward(O.infer_resize(x, (64, 64)), sd, scale_factor=1)["enhanced"], (H, W))
+    assert maxerr(out2["enhanced"], ref2) <= TIGHT_PP

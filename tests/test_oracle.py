@@ -93,3 +93,12 @@ def test_synthetic_input_is_deterministic_and_in_range():
     a = O.synthetic_lowlight(2, 24, 36, seed=1)
     b = O.synthetic_lowlight(2, 24, 36, seed=1)
     assert torch.equal(a, b) and a.min() == 0.0 and a.max() == 1.0
+
+
+def test_infer_resize_rounds_up_to_multiple_of_32():
+    x = O.synthetic_lowlight(1, 50, 70, seed=3)
+    assert O.infer_resize(x).shape[-2:] == (64, 96)                  # core/image/utils.py:381-382 (ceil)
+    assert O.infer_resize(x[..., :32, :64]).shape[-2:] == (32, 64)   # already divisible: identity size
+    assert torch.equal(O.infer_resize(x[..., :32, :64]), x[..., :32, :64])
+    out = O.infer(lambda t: {"adjust": t * 0.5, "enhanced": t.clamp(0, 1)}, x)
+    assert out["enhanced"].shape == x.shape and list(out.keys()) == ["adjust", "enhanced"]
