@@ -351,3 +351,24 @@ def test_infer_resizes_to_multiple_of_32_and_back(cuda_dev, H, W):
     out2 = m.infer({"image": x}, image_size=64, resize=True)
     ref2 = O.infer_resize(O.zero_dcepp_forward(O.infer_resize(x, (64, 64)), sd, scale_factor=1)["enhanced"], (H, W))
     assert maxerr(out2["enhanced"], ref2) <= TIGHT_PP
+
+
+def test_dcepp_batch_stream_matches_direct_forward(cuda_dev):
+    """sched.DceppBatchStream (two streams, alternating workspaces) == the model's forward, batch by batch."""
+    sd = O.make_dcepp_state_dict(41, "stress")
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=12), sd).to(cuda_dev)
+    xs = [O.synthetic_lowlight(3, 96, 132, seed=100 + i).to(cuda_dev) for i in range(5)]
+    want = [m({"image": x}) for x in xs]
+    bs = P.DceppBatchStream(m, 3, 96, 132)
+    enh = [torch.empty_like(x) for x in xs]
+    adj = [torch.empty_like(x) for x in xs]
+    bs.begin()
+    for x, e, a in zip(xs, enh, adj):
+        bs.submit(x, e, a)
+    bs.end()
+    torch.cuda.synchronize()
+    for w, e, a in zip(want, enh, adj):
+        assert torch.equal(e, w["enhanced"]) and torch.equal(a, w["adjust"])
+    assert bs.launches == 15
+    with pytest.raises(ValueError):
+        bs.submit(xs[0][:2], enh[0][:2])
