@@ -372,3 +372,43 @@ def test_dcepp_batch_stream_matches_direct_forward(cuda_dev):
     assert bs.launches == 15
     with pytest.raises(ValueError):
         bs.submit(xs[0][:2], enh[0][:2])
+
+
+# ------------------------------------------------------------------ Zero-DCE (bf16x3: 3-term split-bf16 tensor-core mode)
+# fp32-class accuracy on the tensor cores: the fp32-mode contract (max-abs <= 1e-3) applies; measured ~1e-5.
+X3_TIGHT = 2.5e-4
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_dce_bf16x3_golden(cuda_dev, golden, regime):
+    x, sd, outs = golden(f"dce_{regime}")
+    m = load_into(P.ZeroDCE_RE(precision="bf16x3"), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    assert list(out.keys()) == [f"adjust_{i}" for i in range(8)] + ["adjust", "enhanced"]
+    ea, ee = maxerr(out["adjust"], outs["adjust"]), maxerr(out["enhanced"], outs["enhanced"])
+    assert ea <= TOL and ee <= TOL
+    assert ea <= X3_TIGHT and ee <= X3_TIGHT, (ea, ee)
+
+
+@pytest.mark.parametrize("H,W,B,iters", [(37, 45, 3, 8), (8, 32, 1, 8), (1, 1, 1, 8), (19, 70, 2, 3), (64, 64, 10, 1),
+                                         (16, 33, 1, 8)])
+def test_dce_bf16x3_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
+    x = O.synthetic_lowlight(B, H, W, seed=60 + iters)
+    sd = O.make_dce_state_dict(17, "stress", num_iters=iters)
+    m = load_into(P.ZeroDCE_RE(num_iters=iters, precision="bf16x3"), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    ref = O.zero_dce_forward(x, sd, num_iters=iters)
+    assert out["adjust"].shape == (B, 3 * iters, H, W)
+    assert maxerr(out["adjust"], ref["adjust"]) <= X3_TIGHT
+    assert maxerr(out["enhanced"], ref["enhanced"]) <= X3_TIGHT
+
+
+def test_dce_bf16x3_1080p_matches_fp32_mode_and_identity(cuda_dev):
+    x = O.synthetic_lowlight(2, 1080, 1920, seed=9).to(cuda_dev)
+    sd = O.make_dce_state_dict(19, "stress")
+    a = load_into(P.ZeroDCE_RE(precision="fp32"), sd).to(cuda_dev)({"image": x})
+    b = load_into(P.ZeroDCE_RE(precision="bf16x3"), sd).to(cuda_dev)({"image": x})
+    assert maxerr(b["adjust"], a["adjust"].cpu()) <= X3_TIGHT and maxerr(b["enhanced"], a["enhanced"].cpu()) <= X3_TIGHT
+    z = load_into(P.ZeroDCE_RE(precision="bf16x3"), {k: torch.zeros_like(v) for k, v in sd.items()}).to(cuda_dev)
+    o = z({"image": x})
+    assert torch.equal(o["enhanced"], x) and not o["adjust"].any()
