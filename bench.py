@@ -254,6 +254,7 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
     guarded("c3_dcepp_4k_b8_no_adjust", c3_noadj)
     guarded("c4_sci_1080p_b16", c4)
     guarded("c2_dce_fp32_1080p_b2", c2("fp32", 2, 3))
+    guarded("c2_dce_bf16x3_1080p_b16", c2("bf16x3", 16, 3))
     guarded("c2_dce_bf16_1080p_b16", c2("bf16", 16, 5))
     guarded("c1_dcepp_sf1_512", sf1)
     return out
