@@ -121,25 +121,50 @@ dcepp_layer_kernel(const float* __restrict__ srcA, const float* __restrict__ src
         const float* src = s == 0 ? srcA : srcB;
         __syncthreads();  // previous chunk's s_halo / s_dw consumers are done; weights visible on first pass
         // ---- phase 1: halo tile load (zero padding outside the low-res image) ----
-        for (int idx = t; idx < CS * 10 * 34; idx += 256) {
-            const int k = idx / 340;
-            const int rem = idx - k * 340;
-            const int rr = rem / 34, cc = rem - rr * 34;
-            const int yy = y0 - 1 + rr, xx = x0 - 1 + cc;
-            float v = 0.f;
-            if (yy >= 0 && yy < h && xx >= 0 && xx < w) {
-                if (FIRST && (H != h || W != w)) {
-                    // F.interpolate(scale_factor=1/sf, mode="bilinear"), align_corners=False (zero_dcepp.py:188)
+        if (FIRST && (H != h || W != w)) {
+            // F.interpolate(scale_factor=1/sf, mode="bilinear"), align_corners=False (zero_dcepp.py:188): four
+            // full-resolution taps per low-res pixel, gathered straight from HBM.  All of a thread's taps (4 elements
+            // x 4 loads) are issued before the first one is used, so one DRAM round trip covers the whole tile.
+            constexpr int N_EL = CS * 10 * 34, PER = (N_EL + 255) / 256;
+            float v00[PER], v01[PER], v10[PER], v11[PER], wy0[PER], wy1[PER], wx0[PER], wx1[PER];
+#pragma unroll
+            for (int e = 0; e < PER; ++e) {
+                const int idx = t + e * 256;
+                const int k = idx / 340, rem = idx - k * 340;
+                const int rr = rem / 34, cc = rem - rr * 34;
+                const int yy = y0 - 1 + rr, xx = x0 - 1 + cc;
+                v00[e] = v01[e] = v10[e] = v11[e] = 0.f;
+                wy0[e] = wy1[e] = wx0[e] = wx1[e] = 0.f;
+                if (idx < N_EL && yy >= 0 && yy < h && xx >= 0 && xx < w) {
                     const Tap ty = tap_half_pixel(yy, sf_scale, H), tx = tap_half_pixel(xx, sf_scale, W);
                     const float* p = src + ((size_t)(b * CS + k) * H) * W;
-                    const float v00 = __ldg(p + (size_t)ty.i0 * W + tx.i0), v01 = __ldg(p + (size_t)ty.i0 * W + tx.i1);
-                    const float v10 = __ldg(p + (size_t)ty.i1 * W + tx.i0), v11 = __ldg(p + (size_t)ty.i1 * W + tx.i1);
-                    v = ty.w0 * (tx.w0 * v00 + tx.w1 * v01) + ty.w1 * (tx.w0 * v10 + tx.w1 * v11);
-                } else {
-                    v = __ldg(src + ((size_t)(b * CS + k) * h + yy) * w + xx);
+                    v00[e] = __ldg(p + (size_t)ty.i0 * W + tx.i0);
+                    v01[e] = __ldg(p + (size_t)ty.i0 * W + tx.i1);
+                    v10[e] = __ldg(p + (size_t)ty.i1 * W + tx.i0);
+                    v11[e] = __ldg(p + (size_t)ty.i1 * W + tx.i1);
+                    wy0[e] = ty.w0, wy1[e] = ty.w1, wx0[e] = tx.w0, wx1[e] = tx.w1;
                 }
             }
-            s_halo[(k * 10 + rr) * K1_HS + cc] = v;
+#pragma unroll
+            for (int e = 0; e < PER; ++e) {
+                const int idx = t + e * 256;
+                if (idx < N_EL) {
+                    const int k = idx / 340, rem = idx - k * 340;
+                    const int rr = rem / 34, cc = rem - rr * 34;
+                    s_halo[(k * 10 + rr) * K1_HS + cc] =
+                        wy0[e] * (wx0[e] * v00[e] + wx1[e] * v01[e]) + wy1[e] * (wx0[e] * v10[e] + wx1[e] * v11[e]);
+                }
+            }
+        } else {
+            for (int idx = t; idx < CS * 10 * 34; idx += 256) {
+                const int k = idx / 340;
+                const int rem = idx - k * 340;
+                const int rr = rem / 34, cc = rem - rr * 34;
+                const int yy = y0 - 1 + rr, xx = x0 - 1 + cc;
+                float v = 0.f;
+                if (yy >= 0 && yy < h && xx >= 0 && xx < w) v = __ldg(src + ((size_t)(b * CS + k) * h + yy) * w + xx);
+                s_halo[(k * 10 + rr) * K1_HS + cc] = v;
+            }
         }
         __syncthreads();
         // ---- phase 2: depthwise 3x3 (+bias), sliding window down the 8 tile rows ----
