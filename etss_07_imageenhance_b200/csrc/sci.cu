@@ -13,7 +13,8 @@
 //   * fea1 / fea2 are stored ROW-PAIR INTERLEAVED, twice: copy A holds (row 2p, 2p+1), copy B holds (row 2p+1, 2p+2),
 //     so all five pairs a 4-row item needs per (channel, column) are aligned 64-bit shared loads -- no register moves
 //     to assemble operands (the row-major version spent as many MOVs as FFMA2s);
-//   * item counts per layer (7 x 36, 7 x 34, 6 x 32) are just under the 256 threads: one round per layer.
+//   * item counts per layer (7 x 36, 7 x 34, 6 x 32) are just under the 256 threads: one round per layer, a warp
+//     per row group so that its 64-bit shared accesses are conflict free.
 #include <math.h>
 
 #include "common.cuh"
@@ -104,6 +105,22 @@ __device__ __forceinline__ void store_quad(float2* __restrict__ A, float2* __res
     B[(2 * gi + 1) * W_OUT + c].x = o3;
 }
 
+// item (row group gi, column cc) of thread t for a layer with G groups of COLS >= 32 columns: warp gi takes columns
+// 0..31 of its group (consecutive lanes = consecutive columns: conflict-free 64-bit shared accesses), the last warp
+// takes the COLS - 32 leftover columns of every group
+template <int G, int COLS>
+__device__ __forceinline__ bool sci_item(int t, int& gi, int& cc) {
+    static_assert(G <= 7 && COLS >= 32 && (COLS - 32) * G <= 32, "one round of 8 warps");
+    const int warp = t >> 5, lane = t & 31;
+    if (warp < G) {
+        gi = warp, cc = lane;
+        return true;
+    }
+    if (COLS == 32 || warp != 7 || lane >= (COLS - 32) * G) return false;
+    gi = lane / (COLS - 32 > 0 ? COLS - 32 : 1), cc = 32 + lane % (COLS - 32 > 0 ? COLS - 32 : 1);
+    return true;
+}
+
 __global__ void __launch_bounds__(256, 3)
 sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* __restrict__ r,
                  const __grid_constant__ SciWeights wt, int H, int W) {
@@ -143,8 +160,8 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
     }
     __syncthreads();
     // fea1 = relu(conv(x)) on 28 x 36; zero outside the image (that is the next conv's zero padding)
-    if (t < S1_G * S1_W) {
-        const int gi = t / S1_W, cc = t - gi * S1_W;
+    int gi, cc;
+    if (sci_item<S1_G, S1_W>(t, gi, cc)) {
         const int yy = y0 - 2 + 4 * gi, xx = x0 - 2 + cc;
         float2 o[3][2];
         conv3_quad_rowmajor<SX_W, SX_H * SX_W>(sx + (4 * gi) * SX_W + cc + 1, wt.w1, wt.b1, o);
@@ -159,8 +176,7 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
     }
     __syncthreads();
     // fea2 = fea1 + relu(bn(conv(fea1))) on 28 x 34 (rows y0-1 ..; the last two rows feed nothing)
-    if (t < S2_G * S2_W) {
-        const int gi = t / S2_W, cc = t - gi * S2_W;
+    if (sci_item<S2_G, S2_W>(t, gi, cc)) {
         const int yy = y0 - 1 + 4 * gi, xx = x0 - 1 + cc;
         float2 o[3][2];
         conv3_quad<S1_W, S1_RP * S1_W>(s1a + (2 * gi) * S1_W + cc, s1b + (2 * gi) * S1_W + cc, wt.w2, wt.b2, o);
@@ -177,8 +193,7 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
         }
     }
     __syncthreads();
-    if (t < S3_G * S_TW) {
-        const int gi = t / S_TW, cc = t - gi * S_TW;
+    if (sci_item<S3_G, S_TW>(t, gi, cc)) {
         const int xx = x0 + cc;
         if (xx < W) {
             float2 o[3][2];
