@@ -37,7 +37,9 @@ constexpr int S2_G = 7, S2_W = S_TW + 2;   // fea2: rows y0-1 .. y0+26 (the last
 constexpr int S3_G = S_TH / 4;
 constexpr int S1_RP = 2 * S1_G + 1, S2_RP = 2 * S2_G + 1;  // row pairs per plane (+1: the B copy's last half pair, and
                                                             // fea2's unused rows read one pair past fea1's end)
-constexpr int SCI_SMEM = 4 * (3 * SX_H * SX_W) + 8 * 2 * 3 * (S1_RP * S1_W + S2_RP * S2_W);
+// fea2 reuses the x tile's bytes (x is only read by layer 1; the epilogue re-reads its 12 centre values from L2)
+constexpr int SCI_SX_BYTES = 4 * 3 * SX_H * SX_W, SCI_S2_BYTES = 8 * 2 * 3 * S2_RP * S2_W;
+constexpr int SCI_SMEM = (SCI_SX_BYTES > SCI_S2_BYTES ? SCI_SX_BYTES : SCI_S2_BYTES) + 8 * 2 * 3 * S1_RP * S1_W;
 
 // four vertically adjacent outputs (rows b .. b+3 as two pairs) x 3 channels from row-pair planes:
 //   a = copy A at pair row b/2 (rows b, b+1), b2 = copy B at pair row b/2 (rows b+1, b+2); planes are PLANE float2 apart
@@ -121,15 +123,15 @@ __device__ __forceinline__ bool sci_item(int t, int& gi, int& cc) {
     return true;
 }
 
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, 4)
 sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* __restrict__ r,
                  const __grid_constant__ SciWeights wt, int H, int W) {
     extern __shared__ __align__(16) float sci_smem[];
     float* sx = sci_smem;                                                     // [3][SX_H][SX_W]
-    float2* s1a = reinterpret_cast<float2*>(sx + 3 * SX_H * SX_W);            // [3][S1_RP][S1_W]
-    float2* s1b = s1a + 3 * S1_RP * S1_W;
-    float2* s2a = s1b + 3 * S1_RP * S1_W;                                     // [3][S2_RP][S2_W]
+    float2* s2a = reinterpret_cast<float2*>(sci_smem);                        // [3][S2_RP][S2_W], over the dead x tile
     float2* s2b = s2a + 3 * S2_RP * S2_W;
+    float2* s1a = reinterpret_cast<float2*>(sci_smem + (SCI_SMEM - 8 * 2 * 3 * S1_RP * S1_W) / 4);  // [3][S1_RP][S1_W]
+    float2* s1b = s1a + 3 * S1_RP * S1_W;
     const int t = threadIdx.x;
     const int b = blockIdx.z;
     const int y0 = blockIdx.y * S_TH, x0 = blockIdx.x * S_TW;
@@ -204,7 +206,7 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
                 if (yy >= H) continue;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    const float xin = sx[c * SX_H * SX_W + (4 * gi + q + 3) * SX_W + cc + 4];
+                    const float xin = __ldg(xb + c * plane + (size_t)yy * W + xx);
                     const float ov = (q & 1) ? o[c][q >> 1].y : o[c][q >> 1].x;
                     // sigmoid and x / illu on the SFU (ex2.approx / rcp.approx, ~2 ulp): the IEEE-rounded forms cost as
                     // many FMA-pipe instructions per pixel as a whole conv layer; the contract is 1e-3
