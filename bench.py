@@ -366,7 +366,7 @@ def run_b200(args) -> None:
         # u8 wire variant: same frames as HWC uint8 both ways
         u8 = None
         try:
-            pipe8 = P.FramePipeline(model, frames_per_chunk=4, H=H, W=W, wire="u8", slots=3)
+            pipe8 = P.FramePipeline(model, frames_per_chunk=1, H=H, W=W, wire="u8", slots=3)
             hin8 = torch.empty(FRAMES, H, W, 3, dtype=torch.uint8, pin_memory=True)
             hin8.copy_(torch.ops.b200dce.f32nchw_to_u8hwc(x))
             hout8 = torch.empty_like(hin8).pin_memory()
