@@ -411,7 +411,10 @@ def run_b200(args) -> None:
                             "2-frame chunks on 3 streams", "matches_device_result": e2e_ok, "u8_wire": u8},
             "gpu_launches": args.steps * 3,  # layer-1 kernel + persistent net kernel + full-resolution pass
             "roofline": {"bound": "hbm", "kernel": "dcepp_apply_vec4_kernel<true>", "achieved": achieved,
-                         "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                         "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this workload, one
+                         # `ncu --set full` capture (profiles/r01d_ncu_full_dcepp_apply.txt: 400.92 + 739.70 MB)
+                         "traffic": (1140617728 if (FRAMES, H, W) == (16, 1080, 1920) else None),
                          "peak_source": hbm_src, "bytes_per_launch": px_step * BYTES_PER_PX,
                          "kernel_ms": apply_ms, "kernel_share_of_step": apply_ms / ms_per_step,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
