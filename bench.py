@@ -232,6 +232,17 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
         return {"workload": "C4 SCI 16x3x1080x1920 fp32", "ms": ms, "mp_s": px / 1e6 / (ms / 1e3),
                 "hbm_frac_36Bpx": px * 36 / (ms / 1e3) / 1e9 / hbm_peak}
 
+    def c4_ruas(denoise):
+        def run():
+            m = P.RUAS_RE(denoise=denoise).to(dev)
+            x = synth_frames_gpu(16, H, W, SEED + 4, dev)
+            ms = time_steps(lambda: m({"image": x}), 5, 3, dev)
+            px = x.numel() / 3
+            mac = 3 * 372 + (2430 if denoise else 0)  # per pixel: 3 IEM cells (+ stem, 3 NRM cells, tail)
+            return {"workload": f"C4 RUAS ({'3 IEM + denoise' if denoise else '3 IEM'}) 16x3x1080x1920 fp32", "ms": ms,
+                    "mp_s": px / 1e6 / (ms / 1e3), "tflops_fp32_algorithmic": px * 2 * mac / (ms / 1e3) / 1e12}
+        return run
+
     def c2(precision, frames, steps):
         def run():
             m = P.ZeroDCE_RE(precision=precision).to(dev)
@@ -253,6 +264,8 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
     guarded("c3_dcepp_4k_b8", c3)
     guarded("c3_dcepp_4k_b8_no_adjust", c3_noadj)
     guarded("c4_sci_1080p_b16", c4)
+    guarded("c4_ruas_1080p_b16", c4_ruas(True))
+    guarded("c4_ruas_no_denoise_1080p_b16", c4_ruas(False))
     guarded("c2_dce_fp32_1080p_b2", c2("fp32", 2, 3))
     guarded("c2_dce_bf16x3_1080p_b16", c2("bf16x3", 16, 3))
     guarded("c2_dce_bf16_1080p_b16", c2("bf16", 16, 5))

@@ -20,6 +20,7 @@ ERR_WORKSPACE, ERR_LAUNCH, ERR_NO_DEVICE = -5, -6, -7
 PREC_FP32, PREC_BF16, PREC_BF16X3 = 0, 1, 2
 PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3}
 SCI_PACKED_FLOATS = 252
+RUAS_PACKED_FLOATS = 3438
 
 _PP = POINTER(c_void_p)  # const float* const*  (host array of device pointers)
 
@@ -45,6 +46,9 @@ _SIGNATURES = {
                                  c_void_p, c_size_t, c_void_p]),
     "b200_sci_pack_weights_host": (c_int, [c_void_p] * 8 + [c_float, c_void_p, c_void_p, c_void_p]),
     "b200_sci_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "b200_ruas_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200_ruas_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                  c_void_p, c_size_t, c_void_p]),
     "b200_u8hwc_to_f32nchw": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "b200_f32nchw_to_u8hwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "b200_resize_bilinear": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),

@@ -26,7 +26,7 @@ from . import ops
 from ._lib import PRECISIONS
 from .registry import MODELS
 
-__all__ = ["DSConv2d", "DepthwiseSeparableConv2d", "ZeroDCELoss", "ZeroDCE_RE", "ZeroDCEpp_RE", "SCI_RE",
+__all__ = ["DSConv2d", "DepthwiseSeparableConv2d", "ZeroDCELoss", "ZeroDCE_RE", "ZeroDCEpp_RE", "SCI_RE", "RUAS_RE",
            "remap_upstream_dcepp_keys", "WEIGHTS_EXTENSIONS"]
 
 WEIGHTS_EXTENSIONS = (".pt", ".pth", ".onnx")  # src/mon/globals.py:709
@@ -447,3 +447,95 @@ class SCI_RE(_EnhancementModel):
         """Upstream tuple API: `Finetunemodel.forward` returns (i, r) (sci/model.py:155-159)."""
         out = self.forward({"image": x})
         return out["illumination"], out["enhanced"]
+
+
+# --------------------------------------------------------------------------------------------- RUAS
+_RUAS_IEM = ("skip_connect", "resconv_1x1", "resdilconv_3x3", "conv_3x3", "conv_3x3", "skip_connect", "conv_3x3")
+_RUAS_NRM = ("resconv_1x1", "resconv_1x1", "resdilconv_3x3", "skip_connect", "resconv_1x1", "resconv_1x1",
+             "skip_connect")
+
+
+class _RuasOp(nn.Module):
+    """Parameter holder named like upstream's ConvBlock / ResBlock (`.op`, ruas/operations.py:25-45)."""
+
+    def __init__(self, channels: int, op: str):
+        super().__init__()
+        k, dil = (1 if op.endswith("1x1") else 3), (2 if "dil" in op else 1)
+        self.op = nn.Conv2d(channels, channels, k, 1, padding=(k - 1) // 2 * dil, dilation=dil)
+
+
+class _RuasSearchBlock(nn.Module):
+    """Parameter container with upstream SearchBlock's names (ruas/model.py:24-44)."""
+
+    def __init__(self, channels: int, genotype: tuple):
+        super().__init__()
+        for slot, op in zip(("c1_d", "c1_r", "c2_d", "c2_r", "c3_d", "c3_r", "c4"), genotype):
+            setattr(self, slot, nn.Identity() if op == "skip_connect" else _RuasOp(channels, op))
+        self.c5 = nn.Conv2d(4 * channels, channels, 1)
+
+
+class _RuasIEM(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.cell = _RuasSearchBlock(3, _RUAS_IEM)
+
+
+class _RuasEnhanceNetwork(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.iems = nn.ModuleList([_RuasIEM() for _ in range(3)])
+
+
+class _RuasDenoiseNetwork(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.stem = nn.Conv2d(3, 6, 3, 1, 1)
+        self.nrms = nn.ModuleList([_RuasSearchBlock(6, _RUAS_NRM) for _ in range(3)])
+        self.activate = nn.Sequential(nn.Conv2d(6, 3, 3, 1, 1))
+
+
+@MODELS.register(name="ruas_re", arch="ruas")
+class RUAS_RE(_EnhancementModel):
+    """RUAS inference model = upstream `Network` (ruas/model.py:152-206): state_dict keys `enhance_net.iems.{i}.cell.*`
+    and `denoise_net.{stem,nrms.{i}.*,activate.0}.*`, iem_nums = nrm_nums = 3, IEM / NRM genotypes.
+
+    `denoise=True` returns the denoised result as `enhanced` (what upstream's predict saves for the `lol` weights,
+    `u_list[-1]`); `denoise=False` skips the denoise net and returns `u_list[-2]` (the `upe` / `dark` weights)."""
+
+    arch = "ruas"
+
+    def __init__(self, denoise: bool = True, weights: Any = None, *args, **kwargs):
+        kwargs.pop("name", None)
+        super().__init__(name="ruas_re", in_channels=3, weights=weights, *args, **kwargs)
+        self.denoise = bool(denoise)
+        self.enhance_net = _RuasEnhanceNetwork()
+        self.denoise_net = _RuasDenoiseNetwork()
+        self.eval()
+        if self.weights:
+            self.load_weights()
+
+    def packed_weights(self) -> torch.Tensor:
+        key = self._params_key(list(self.parameters()))
+        if self._packed is None or self._packed_key != key:
+            self._packed = ops.ruas_pack(self.state_dict())
+            self._packed_key = key
+        return self._packed
+
+    @torch.no_grad()
+    def forward_lists(self, x: torch.Tensor) -> tuple:
+        """Upstream tuple API: `Network.forward` returns (u_list, t_list) (ruas/model.py:202-206)."""
+        u, t, den, _ = torch.ops.b200dce.ruas_forward(x, self.packed_weights(), self.denoise)
+        u_list = list(u.unbind(0)) + ([den] if self.denoise else [])
+        return u_list, list(t.unbind(0))
+
+    @torch.no_grad()
+    def forward(self, datapoint: dict, *args, **kwargs) -> dict:
+        x = self._image(datapoint)
+        u, t, den, noise = torch.ops.b200dce.ruas_forward(x, self.packed_weights(), self.denoise)
+        out = {"illumination": t[2], "enhanced_no_denoise": u[2]}
+        if self.denoise:
+            out["noise"] = noise
+            out["enhanced"] = den
+        else:
+            out["enhanced"] = out.pop("enhanced_no_denoise")
+        return out

@@ -9,6 +9,7 @@ Replaces the ATen op sequence of
   src/mon/vision/enhance/llie/zero_dce/zero_dce.py:176-188      (dce_forward)
   src/mon/vision/enhance/llie/zero_dce/zero_dcepp.py:186-203    (dcepp_forward, curve_shared)
   src/mon_extra/vision/enhance/llie/sci/model.py:36-45,155-159  (sci_forward)
+  src/mon_extra/vision/enhance/llie/ruas/model.py:46-149,202-206  (ruas_forward)
 """
 from __future__ import annotations
 
@@ -22,7 +23,7 @@ from ._lib import PRECISIONS, check, lib, ptr_array
 
 __all__ = [
     "curve_shared", "curve_per_iter", "dcepp_pack", "dcepp_forward", "dcepp_lowres", "dcepp_apply",
-    "dce_pack", "dce_forward", "sci_pack", "sci_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
+    "dce_pack", "dce_forward", "sci_pack", "sci_forward", "ruas_pack", "ruas_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
     "current_stream_ptr", "require_device",
 ]
 
@@ -308,6 +309,69 @@ def sci_forward(x: Tensor, packed_host: Tensor, return_illu: bool) -> Tuple[Tens
 @sci_forward.register_fake
 def _(x, packed_host, return_illu):
     return (torch.empty_like(x) if return_illu else x.new_empty(0)), torch.empty_like(x)
+
+
+# ----------------------------------------------------------------------------- RUAS
+_RUAS_IEM_SLOTS = ("c1_r.op", "c2_d.op", "c2_r.op", "c3_d.op", "c4.op", "c5")          # genotypes.py:15 (skips own
+_RUAS_NRM_SLOTS = ("c1_d.op", "c1_r.op", "c2_d.op", "c3_d.op", "c3_r.op", "c5")        # :16       no parameters)
+_RUAS_IEM_SHAPES = ((3, 3, 1, 1), (3, 3, 3, 3), (3, 3, 3, 3), (3, 3, 3, 3), (3, 3, 3, 3), (3, 12, 1, 1))
+_RUAS_NRM_SHAPES = ((6, 6, 1, 1), (6, 6, 1, 1), (6, 6, 3, 3), (6, 6, 1, 1), (6, 6, 1, 1), (6, 24, 1, 1))
+
+
+def ruas_pack(sd: dict, prefix: str = "") -> Tensor:
+    """Concatenate upstream `Network` weights (ruas/model.py:152-200 key names) into the 3438-float HOST block of
+    include/b200dce.h (order: 3 IEM cells, stem, 3 NRM cells, activate.0; weight then bias of every conv)."""
+    parts = []
+
+    def take(key, shape):
+        w = sd[prefix + key + ".weight"].detach().to("cpu", torch.float32).contiguous()
+        b = sd[prefix + key + ".bias"].detach().to("cpu", torch.float32).contiguous()
+        if tuple(w.shape) != shape or tuple(b.shape) != shape[:1]:
+            raise NotImplementedError(f"b200dce::ruas_pack: {key} has shape {tuple(w.shape)}, expected {shape} "
+                                      "(the kernels implement the IEM / NRM genotypes with 3 / 6 channels)")
+        parts.extend((w.reshape(-1), b))
+
+    for i in range(3):
+        for slot, shape in zip(_RUAS_IEM_SLOTS, _RUAS_IEM_SHAPES):
+            take(f"enhance_net.iems.{i}.cell.{slot}", shape)
+    take("denoise_net.stem", (6, 3, 3, 3))
+    for i in range(3):
+        for slot, shape in zip(_RUAS_NRM_SLOTS, _RUAS_NRM_SHAPES):
+            take(f"denoise_net.nrms.{i}.{slot}", shape)
+    take("denoise_net.activate.0", (3, 6, 3, 3))
+    packed = torch.cat(parts).contiguous()
+    assert packed.numel() == _lib.RUAS_PACKED_FLOATS
+    return packed
+
+
+@torch.library.custom_op("b200dce::ruas_forward", mutates_args=(), device_types="cuda")
+def ruas_forward(x: Tensor, packed_host: Tensor, denoise: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """x [B,3,H,W] -> (u [3,B,3,H,W], t [3,B,3,H,W], denoised [B,3,H,W], noise [B,3,H,W]); the last two are empty
+    [0] tensors without `denoise`."""
+    x = _img(x, "x")
+    if packed_host.is_cuda or packed_host.numel() != _lib.RUAS_PACKED_FLOATS or packed_host.dtype != torch.float32:
+        raise ValueError("b200dce::ruas_forward: packed_host must be the 3438-float CPU tensor from ruas_pack()")
+    packed_host = packed_host.contiguous()
+    B, _, H, W = x.shape
+    u = x.new_empty(3, B, 3, H, W)
+    t = x.new_empty(3, B, 3, H, W)
+    den = torch.empty_like(x) if denoise else x.new_empty(0)
+    noise = torch.empty_like(x) if denoise else x.new_empty(0)
+    if x.numel():
+        with torch.cuda.device(x.device):
+            nbytes = lib().b200_ruas_workspace_bytes(B, H, W, int(denoise))
+            ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+            check(lib().b200_ruas_forward(x.data_ptr(), packed_host.data_ptr(), u.data_ptr(), t.data_ptr(),
+                                          den.data_ptr() if denoise else None, noise.data_ptr() if denoise else None,
+                                          B, H, W, ws.data_ptr(), nbytes, current_stream_ptr()), "b200_ruas_forward")
+    return u, t, den, noise
+
+
+@ruas_forward.register_fake
+def _(x, packed_host, denoise):
+    B, _, H, W = x.shape
+    e = torch.empty_like(x) if denoise else x.new_empty(0)
+    return x.new_empty(3, B, 3, H, W), x.new_empty(3, B, 3, H, W), e, torch.empty_like(e)
 
 
 # ----------------------------------------------------------------------------- frame format

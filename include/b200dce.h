@@ -143,6 +143,31 @@ int b200_sci_forward(const float* x, const float* packed_host, float* illu_or_nu
                      void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * RUAS ("next" row SURVEY §8f-4): upstream Network.forward,
+ * src/mon_extra/vision/enhance/llie/ruas/model.py:202-206 = EnhanceNetwork
+ * (:117-125, three IEM iterations :84-95) then DenoiseNetwork (:142-149); cells =
+ * SearchBlock (:46-66) with the IEM / NRM genotypes of genotypes.py:15-16.
+ *
+ * `packed_host` (HOST memory, B200_RUAS_PACKED_FLOATS floats) is the plain
+ * concatenation, conv weights OIHW then bias, of
+ *   for i in 0..2  enhance_net.iems.i.cell.{c1_r.op, c2_d.op, c2_r.op, c3_d.op, c4.op, c5}     (387 floats each)
+ *   denoise_net.stem                                                                           (168)
+ *   for i in 0..2  denoise_net.nrms.i.{c1_d.op, c1_r.op, c2_d.op, c3_d.op, c3_r.op, c5}        (648 each)
+ *   denoise_net.activate.0                                                                     (165)
+ * (skip_connect slots own no parameters).
+ * ------------------------------------------------------------------------- */
+#define B200_RUAS_PACKED_FLOATS 3438
+
+/* Two 6-channel feature maps when the denoise net runs, else 0. */
+size_t b200_ruas_workspace_bytes(int B, int H, int W, int with_denoise);
+
+/* x [B,3,H,W] -> u [3][B,3,H,W] (u_list[0..2]), t [3][B,3,H,W] (t_list, may be
+ * NULL); with `denoised_or_null` != NULL also denoised [B,3,H,W] (u_list[3]) and
+ * optionally the noise map n [B,3,H,W]. */
+int b200_ruas_forward(const float* x, const float* packed_host, float* u, float* t_or_null, float* denoised_or_null,
+                      float* noise_or_null, int B, int H, int W, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * "next" rows: u8 HWC <-> fp32 NCHW frame conversion.
  * Replaces src/mon/core/image/utils.py:801-848 (to_image_tensor, /255) and
  * :766-800 (to_image_nparray denormalize: *255 then astype(uint8), i.e.

@@ -17,6 +17,9 @@ arithmetic.  Citations are relative to /root/reference/:
   src/mon_extra/vision/enhance/llie/zero_dce++/model.py:39,64-82.
 * `sci_forward`        follows src/mon_extra/vision/enhance/llie/sci/model.py:36-45,155-159
   (BatchNorm2d in eval mode).
+* `ruas_forward`       follows src/mon_extra/vision/enhance/llie/ruas/model.py:46-66 (SearchBlock),
+  :77-96 (IEM), :117-125 (EnhanceNetwork), :142-149 (DenoiseNetwork), :202-206 (Network.forward) with the
+  cells of genotypes.py:15-16 and the ops of operations.py:25-54.
 
 Parity pin: the reference holds no tests / golden vectors for this path
 ("parity unpinned" by the reference's own tests).  The pin we
@@ -113,6 +116,42 @@ def make_sci_state_dict(seed: int, regime: str = "init") -> dict:
         sd["conv.1.running_mean"] = torch.randn(3, generator=g) * 0.1
         sd["conv.1.running_var"] = 0.5 + torch.rand(3, generator=g)
     sd["conv.1.num_batches_tracked"] = torch.tensor(0, dtype=torch.long)
+    return sd
+
+
+# RUAS cells (ruas/genotypes.py:15-16): op of c1_d, c1_r, c2_d, c2_r, c3_d, c3_r, c4
+RUAS_IEM = ("skip_connect", "resconv_1x1", "resdilconv_3x3", "conv_3x3", "conv_3x3", "skip_connect", "conv_3x3")
+RUAS_NRM = ("resconv_1x1", "resconv_1x1", "resdilconv_3x3", "skip_connect", "resconv_1x1", "resconv_1x1",
+            "skip_connect")
+RUAS_SLOTS = ("c1_d", "c1_r", "c2_d", "c2_r", "c3_d", "c3_r", "c4")
+
+
+def make_ruas_state_dict(seed: int, regime: str = "init") -> dict:
+    """Seeded weights with the key names of upstream `Network` (ruas/model.py:152-206): `enhance_net.iems.{i}.cell.*`
+    (3 cells, 3 channels) and `denoise_net.{stem,nrms.{i}.*,activate.0}` (3 cells, 6 channels).  skip_connect slots
+    own no parameters.  regime="stress" scales the weights up so that t leaves the sigmoid's flat middle."""
+    g = torch.Generator().manual_seed(seed)
+    scale = [1.0 if regime == "init" else 3.0]
+    sd = {}
+
+    def conv(key, co, ci, k):
+        bound = 1.0 / math.sqrt(ci * k * k)
+        sd[key + ".weight"] = (torch.rand(co, ci, k, k, generator=g) * 2 - 1) * bound * scale[0]
+        sd[key + ".bias"] = (torch.rand(co, generator=g) * 2 - 1) * bound
+
+    def cell(prefix, ch, geno):
+        for slot, op in zip(RUAS_SLOTS, geno):
+            if op != "skip_connect":
+                conv(f"{prefix}.{slot}.op", ch, ch, 1 if op.endswith("1x1") else 3)
+        conv(f"{prefix}.c5", ch, 4 * ch, 1)
+
+    for i in range(3):
+        cell(f"enhance_net.iems.{i}.cell", 3, RUAS_IEM)
+    scale[0] = 1.0 if regime == "init" else 1.3  # three stacked 24 -> 6 cells amplify: keep the noise map O(1)
+    conv("denoise_net.stem", 6, 3, 3)
+    for i in range(3):
+        cell(f"denoise_net.nrms.{i}", 6, RUAS_NRM)
+    conv("denoise_net.activate.0", 3, 6, 3)
     return sd
 
 
@@ -242,6 +281,60 @@ def sci_forward(x: torch.Tensor, sd: dict, eps: float = 1e-5) -> tuple:
     illu = torch.clamp(fea + x, 0.0001, 1)
     r = torch.clamp(x / illu, 0, 1)
     return illu, r
+
+
+def _ruas_op(x, sd, key, op):
+    """operations.py:5-23 -> ConvBlock (:25-33) / ResBlock (:35-45) / Identity (:48-54)."""
+    if op == "skip_connect":
+        return x
+    w, b = sd[key + ".op.weight"], sd[key + ".op.bias"]
+    dil = 2 if "dil" in op else 1
+    pad = (w.shape[-1] - 1) // 2 * dil
+    y = F.conv2d(x, w, b, padding=pad, dilation=dil)
+    return y + x if op.startswith("res") else y
+
+
+def _ruas_cell(x, sd, prefix, geno):
+    """SearchBlock.forward (ruas/model.py:46-66)."""
+    act = lambda v: F.leaky_relu(v, 0.05)
+    d1 = act(_ruas_op(x, sd, prefix + ".c1_d", geno[0]))
+    r1 = act(_ruas_op(x, sd, prefix + ".c1_r", geno[1]) + x)
+    d2 = act(_ruas_op(r1, sd, prefix + ".c2_d", geno[2]))
+    r2 = act(_ruas_op(r1, sd, prefix + ".c2_r", geno[3]) + r1)
+    d3 = act(_ruas_op(r2, sd, prefix + ".c3_d", geno[4]))
+    r3 = act(_ruas_op(r2, sd, prefix + ".c3_r", geno[5]) + r2)
+    r4 = act(_ruas_op(r3, sd, prefix + ".c4", geno[6]))
+    return F.conv2d(torch.cat([d1, d2, d3, r4], dim=1), sd[prefix + ".c5.weight"], sd[prefix + ".c5.bias"])
+
+
+def ruas_max_operation(x):
+    """IEM.max_operation (ruas/model.py:77-82): 2x2 max over (r, r+1) x (c, c+1), zero beyond the last row/column."""
+    x = F.pad(x, (0, 1, 0, 1))
+    x = torch.max(x[:, :, :-1, :], x[:, :, 1:, :])
+    return torch.max(x[:, :, :, :-1], x[:, :, :, 1:])
+
+
+@torch.no_grad()
+def ruas_forward(x: torch.Tensor, sd: dict, denoise: bool = True) -> tuple:
+    """Network.forward (ruas/model.py:202-206): returns (u_list, t_list); with `denoise` the denoised u is appended to
+    u_list and the noise map returned as a third value."""
+    u_list, t_list = [], []
+    u = torch.ones_like(x)
+    for k in range(3):  # EnhanceNetwork.forward :117-125, IEM.forward :84-95
+        t_hat = ruas_max_operation(x) if k == 0 else ruas_max_operation(u) - 0.5 * (u - x)
+        t = torch.sigmoid(_ruas_cell(t_hat, sd, f"enhance_net.iems.{k}.cell", RUAS_IEM))
+        t = torch.clamp(t, 0.001, 1.0)
+        u = torch.clamp(x / t, 0.0, 1.0)
+        u_list.append(u)
+        t_list.append(t)
+    if not denoise:
+        return u_list, t_list, None
+    feat = F.conv2d(u, sd["denoise_net.stem.weight"], sd["denoise_net.stem.bias"], padding=1)  # :142-149
+    for i in range(3):
+        feat = _ruas_cell(feat, sd, f"denoise_net.nrms.{i}", RUAS_NRM)
+    n = F.conv2d(feat, sd["denoise_net.activate.0.weight"], sd["denoise_net.activate.0.bias"], padding=1)
+    u_list.append(u - n)
+    return u_list, t_list, n
 
 
 # --------------------------------------------------------------------------- #

@@ -10,6 +10,9 @@ What is executed from the reference, unmodified, read from where it lies:
   * src/mon_extra/vision/enhance/llie/zero_dce/model.py      (upstream Zero-DCE)
   * src/mon_extra/vision/enhance/llie/zero_dce++/model.py    (upstream Zero-DCE++, sf != 1)
   * src/mon_extra/vision/enhance/llie/sci/model.py           (upstream SCI EnhanceNetwork)
+  * src/mon_extra/vision/enhance/llie/ruas/model.py          (upstream RUAS EnhanceNetwork / DenoiseNetwork, with
+    operations.py and genotypes.py; `Network.__init__` itself loads a zoo checkpoint that is not in the tree, so the
+    two sub-networks are built the way Network.__init__ :168-177 builds them and chained as Network.forward :202-206)
 `import mon` itself is impossible here (plum/humps/lightning/fvcore/... are not
 installed, no network), so the three `mon` files are exec'd under a STUB `mon`
 package that provides only the base-class plumbing they subclass
@@ -18,7 +21,7 @@ src/mon/vision/enhance/base.py:32-47).  The arithmetic (`forward`) and the
 parameter names are the reference's own code.
 
 Assertions (all on CPU, fp32): oracle == reference bit-for-bit.
-Outputs: tests/golden/{dce,dcepp_sf1,dcepp_sf2,dcepp_sf12,sci}_{init,stress}.npz
+Outputs: tests/golden/{dce,dcepp_sf1,dcepp_sf2,dcepp_sf12,sci,ruas}_{init,stress}.npz
 holding input, weights and the REFERENCE outputs.
 """
 from __future__ import annotations
@@ -159,6 +162,13 @@ def load_upstream():
     return dce, dcepp, sci
 
 
+def load_upstream_ruas():
+    """ruas/model.py does `from operations import *` and `import genotypes`: its directory goes first on sys.path."""
+    d = REF / "src/mon_extra/vision/enhance/llie/ruas"
+    sys.path.insert(0, str(d))
+    return _load_file("up_ruas_model", d / "model.py")
+
+
 def to_upstream_keys(sd: dict) -> dict:
     return {k.replace("dw_conv", "depth_conv").replace("pw_conv", "point_conv"): v for k, v in sd.items()}
 
@@ -281,6 +291,30 @@ def main():
         eq(r, r_ref, f"sci/{regime}/r")
         save(f"sci_{regime}", x, sd, illu=illu_ref, r=r_ref)
         report.append(f"sci/{regime}: oracle == upstream EnhanceNetwork + divide")
+
+    # ---------------- RUAS ----------------
+    up_ruas = load_upstream_ruas()
+    import genotypes as up_geno  # noqa: E402  (ruas/genotypes.py, on sys.path since load_upstream_ruas)
+    assert tuple(n for n, _ in up_geno.IEM.normal) == O.RUAS_IEM and tuple(n for n, _ in up_geno.NRM.normal) == O.RUAS_NRM
+    for regime in ("init", "stress"):
+        x = O.synthetic_lowlight(2, 40, 52, seed=401)
+        sd = O.make_ruas_state_dict(17, regime)
+        enh = up_ruas.EnhanceNetwork(iteratioin=3, channel=3, genotype=up_geno.IEM).eval()
+        den = up_ruas.DenoiseNetwork(layers=3, channel=6, genotype=up_geno.NRM).eval()
+        enh.load_state_dict({k[len("enhance_net."):]: v for k, v in sd.items() if k.startswith("enhance_net.")})
+        den.load_state_dict({k[len("denoise_net."):]: v for k, v in sd.items() if k.startswith("denoise_net.")})
+        with torch.no_grad():
+            u_ref, t_ref = enh(x)
+            ud_ref, n_ref = den(u_ref[-1])
+        u_list, t_list, n = O.ruas_forward(x, sd)
+        for i in range(3):
+            eq(u_list[i], u_ref[i], f"ruas/{regime}/u{i}")
+            eq(t_list[i], t_ref[i], f"ruas/{regime}/t{i}")
+        eq(u_list[3], ud_ref, f"ruas/{regime}/denoised")
+        eq(n, n_ref, f"ruas/{regime}/noise")
+        save(f"ruas_{regime}", x, sd, u=torch.stack(u_ref), t=torch.stack(t_ref), denoised=ud_ref, noise=n_ref)
+        report.append(f"ruas/{regime}: oracle == upstream EnhanceNetwork -> DenoiseNetwork; "
+                      f"t in [{t_ref[-1].min():.3f}, {t_ref[-1].max():.3f}], |noise|max={n_ref.abs().max():.3f}")
 
     (GOLD / "PIN_REPORT.txt").write_text(
         f"generated by oracle/pin_against_reference.py with torch {torch.__version__} (CPU, fp32)\n" +

@@ -288,6 +288,59 @@ def test_sci_ragged_shapes_vs_oracle(cuda_dev, H, W, B):
     assert maxerr(illu, ri) <= TIGHT and maxerr(r, rr) <= TOL
 
 
+# ------------------------------------------------------------------ RUAS
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_ruas_golden(cuda_dev, golden, regime):
+    x, sd, outs = golden(f"ruas_{regime}")
+    m = P.MODELS.build(name="ruas_re")
+    m.load_state_dict(sd, strict=False)
+    m = m.to(cuda_dev)
+    u_list, t_list = m.forward_lists(x.to(cuda_dev))
+    assert len(u_list) == 4 and len(t_list) == 3
+    for i in range(3):
+        assert maxerr(t_list[i], outs["t"][i]) <= TIGHT, i
+        # u = clamp(y / t): the division amplifies t's rounding where t is small -> contract tolerance
+        assert maxerr(u_list[i], outs["u"][i]) <= TOL, i
+    assert maxerr(u_list[3], outs["denoised"]) <= TOL
+    out = m({"image": x.to(cuda_dev)})
+    assert list(out.keys()) == ["illumination", "enhanced_no_denoise", "noise", "enhanced"]
+    assert maxerr(out["noise"], outs["noise"]) <= TOL
+    assert torch.equal(out["enhanced"], u_list[3]) and torch.equal(out["enhanced_no_denoise"], u_list[2])
+    m.denoise = False
+    out = m({"image": x.to(cuda_dev)})
+    assert list(out.keys()) == ["illumination", "enhanced"]
+    assert torch.equal(out["enhanced"], u_list[2])
+
+
+@pytest.mark.parametrize("H,W,B", [(17, 33, 2), (1, 1, 1), (12, 32, 1), (13, 34, 1), (45, 100, 3), (2, 131, 1)])
+def test_ruas_ragged_shapes_vs_oracle(cuda_dev, H, W, B):
+    x = O.synthetic_lowlight(B, H, W, seed=71)
+    sd = O.make_ruas_state_dict(29, "stress")
+    u, t, den, noise = torch.ops.b200dce.ruas_forward(x.to(cuda_dev), P.ops.ruas_pack(sd), True)
+    ru, rt, rn = O.ruas_forward(x, sd)
+    for i in range(3):
+        assert maxerr(t[i], rt[i]) <= TIGHT and maxerr(u[i], ru[i]) <= TOL, i
+    assert maxerr(den, ru[3]) <= TOL and maxerr(noise, rn) <= TOL
+
+
+def test_ruas_1080p_tile_seams(cuda_dev):
+    """Full-size frame: every 12 x 32 tile seam and the frame borders against the oracle on crops whose receptive
+    field (3 IEM iterations x 3 px + stem/tail/3 NRM cells x 2..1 px = 17 px) lies inside the crop's margin."""
+    H, W = 1080, 1920
+    x = O.synthetic_lowlight(1, H, W, seed=72)
+    sd = O.make_ruas_state_dict(31, "stress")
+    u, t, den, noise = torch.ops.b200dce.ruas_forward(x.to(cuda_dev), P.ops.ruas_pack(sd), True)
+    for (ya, yb, xa, xb) in ((0, 96, 0, 128), (H - 96, H, W - 128, W), (500, 596, 900, 1028)):
+        ru, rt, _ = O.ruas_forward(x[:, :, ya:yb, xa:xb], sd)
+        m = 24  # margin dropped on crop sides that are not frame borders
+        ys = slice(0 if ya == 0 else m, (yb - ya) if yb == H else (yb - ya - m))
+        xs = slice(0 if xa == 0 else m, (xb - xa) if xb == W else (xb - xa - m))
+        got_u = u[2][:, :, ya:yb, xa:xb][:, :, ys, xs]
+        got_d = den[:, :, ya:yb, xa:xb][:, :, ys, xs]
+        assert maxerr(got_u, ru[2][:, :, ys, xs]) <= TOL
+        assert maxerr(got_d, ru[3][:, :, ys, xs]) <= TOL
+
+
 # ------------------------------------------------------------------ frame format + scheduler
 def test_u8_conversions_exact(cuda_dev):
     g = torch.Generator().manual_seed(5)

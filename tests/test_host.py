@@ -69,7 +69,7 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
 def test_registry_entries_and_name_spellings():
     assert P.MODELS["zero_dce"]["zero_dce_re"] is P.ZeroDCE_RE
     assert P.MODELS["zero_dce"]["zero_dce++_re"] is P.ZeroDCEpp_RE
-    assert set(P.MODELS.archs) >= {"zero_dce", "sci"}
+    assert set(P.MODELS.archs) >= {"zero_dce", "sci", "ruas"}
     m = P.MODELS.build(name="zero_dce++_re")
     assert isinstance(m, P.ZeroDCEpp_RE) and m.name == "zero_dce++_re"
     m = P.MODELS.build(config={"name": "zero_dce_re", "num_iters": 4})
@@ -137,6 +137,31 @@ def test_zero_dcepp_state_dict_layout_init_and_file_weights(tmp_path):
         P.ZeroDCEpp_RE(weights=str(tmp_path / "w.txt"))
     up = {k.replace("dw_conv", "depth_conv").replace("pw_conv", "point_conv"): v for k, v in m.state_dict().items()}
     assert set(P.remap_upstream_dcepp_keys(up)) == set(m.state_dict())
+
+
+def test_ruas_state_dict_and_pack_layout(lib_built):
+    """Key names = upstream Network (ruas/model.py:152-200; pinned by oracle/pin_against_reference.py loading the same
+    dict into the upstream modules); pack order = include/b200dce.h."""
+    sd = O.make_ruas_state_dict(17, "init")
+    m = P.RUAS_RE()
+    assert set(m.state_dict().keys()) == set(sd.keys())
+    m.load_state_dict(sd)
+    packed = m.packed_weights()
+    assert packed.shape == (3438,) and not packed.is_cuda
+    assert torch.equal(packed[:9], sd["enhance_net.iems.0.cell.c1_r.op.weight"].reshape(-1))
+    assert torch.equal(packed[9:12], sd["enhance_net.iems.0.cell.c1_r.op.bias"])
+    assert torch.equal(packed[3 * 387:3 * 387 + 162], sd["denoise_net.stem.weight"].reshape(-1))
+    assert torch.equal(packed[-3:], sd["denoise_net.activate.0.bias"])
+    with pytest.raises(RuntimeError):
+        m({"image": torch.rand(1, 3, 8, 8)})  # CPU tensor: no CPU fallback
+
+
+def test_ruas_oracle_matches_golden(golden):
+    for regime in ("init", "stress"):
+        x, sd, outs = golden(f"ruas_{regime}")
+        u, t, n = O.ruas_forward(x, sd)
+        assert torch.equal(torch.stack(u[:3]), outs["u"]) and torch.equal(torch.stack(t), outs["t"])
+        assert torch.equal(u[3], outs["denoised"]) and torch.equal(n, outs["noise"])
 
 
 def test_sci_state_dict_matches_upstream_finetunemodel_keys():
