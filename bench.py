@@ -167,7 +167,7 @@ def run_reference(args) -> None:
         "config": {"workload": WORKLOAD, "sample": sample},
         "cpu_baseline": {"value": value, "unit": "MP/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "MP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }), flush=True)
+    }), file=_RESULT_OUT, flush=True)
 
 
 # ----------------------------------------------------------------------------- GPU arm
@@ -440,13 +440,27 @@ def run_b200(args) -> None:
             threads = os.cpu_count() or 1
             v, sample = cpu_path_mp_s(2, 12.0, 40, threads)
             line["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": threads, "kind": "port", "sample": sample}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_RESULT_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_RESULT_OUT = sys.stdout
+
+
+def _reserve_stdout():
+    """stdout carries exactly ONE JSON line.  Libraries that write to file descriptor 1 on their own (NCCL prints
+    "NCCL version ..." there on some boxes, whatever NCCL_DEBUG_FILE says) are pointed at stderr: the real stdout is
+    kept on a private descriptor for the result line and fd 1 becomes a duplicate of fd 2."""
+    global _RESULT_OUT
+    sys.stdout.flush()
+    _RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
 def main():
+    _reserve_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
