@@ -360,9 +360,11 @@ def run_b200(args) -> None:
 
         # ---- end to end: pinned host frames -> FramePipeline -> pinned host results, every step
         pipe = P.FramePipeline(model, frames_per_chunk=2, H=H, W=W, wire="f32", slots=3)
-        host_in = torch.empty(FRAMES, 3, H, W, pin_memory=True)
-        host_in.copy_(x)
-        host_out = torch.empty(FRAMES, 3, H, W, pin_memory=True)
+        with P.sched.numa_local(local) as numa_cpus:  # pinned pages on this GPU's NUMA node
+            host_in = torch.empty(FRAMES, 3, H, W, pin_memory=True)
+            host_in.copy_(x)
+            host_out = torch.empty(FRAMES, 3, H, W, pin_memory=True)
+            host_out.zero_()
         e2e_steps = max(3, min(args.steps, 10))
         for _ in range(2):
             pipe.run(host_in, host_out)
@@ -381,9 +383,11 @@ def run_b200(args) -> None:
         u8 = None
         try:
             pipe8 = P.FramePipeline(model, frames_per_chunk=1, H=H, W=W, wire="u8", slots=3)
-            hin8 = torch.empty(FRAMES, H, W, 3, dtype=torch.uint8, pin_memory=True)
-            hin8.copy_(torch.ops.b200dce.f32nchw_to_u8hwc(x))
-            hout8 = torch.empty_like(hin8).pin_memory()
+            with P.sched.numa_local(local):
+                hin8 = torch.empty(FRAMES, H, W, 3, dtype=torch.uint8, pin_memory=True)
+                hin8.copy_(torch.ops.b200dce.f32nchw_to_u8hwc(x))
+                hout8 = torch.empty(FRAMES, H, W, 3, dtype=torch.uint8, pin_memory=True)
+                hout8.zero_()
             for _ in range(2):
                 pipe8.run(hin8, hout8)
             g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -421,6 +425,7 @@ def run_b200(args) -> None:
                        "parallelism": f"frame-sharded x{world}, no data-path collective"},
             "e2e": {"value": e2e_value, "unit": "MP/s", "h2d_bytes_per_step": host_in.numel() * 4,
                     "d2h_bytes_per_step": host_out.numel() * 4, "ms_per_step": e2e_ms / e2e_steps,
+                    "pinned_numa_local_cpus": len(numa_cpus) if numa_cpus else None,
                     "path": "FramePipeline(wire=f32): pinned host x -> H2D -> b200_dcepp_forward -> D2H enhanced, "
                             "2-frame chunks on 3 streams", "matches_device_result": e2e_ok, "u8_wire": u8},
             "gpu_launches": args.steps * 3,  # layer-1 kernel + persistent net kernel + full-resolution pass

@@ -7,6 +7,8 @@ H2D per frame, ~30-60 kernel launches, D2H + encode) with, per GPU, one process 
   * chunk i goes to slot i % slots:  H2D copy -> kernels (direct C-ABI launch on that stream, no
     allocation in the loop) -> D2H copy, so the copy engines (both directions) and the SMs overlap
     across slots;
+  * the pinned host buffers placed on the GPU's own NUMA node (`numa_local`): with one process per GPU on a
+    two-socket host the H2D / D2H DMA otherwise crosses the socket interconnect and all ranks share one node's DRAM;
   * optional u8 HWC frames on the wire (4x fewer PCIe bytes) with the conversion fused on device
     (to_image_tensor / to_image_nparray semantics, src/mon/core/image/utils.py:766-848).
 
@@ -15,6 +17,8 @@ NO collective on the data path (`shard_range`); only timings / checksums are gat
 """
 from __future__ import annotations
 
+import contextlib
+import os
 from dataclasses import dataclass
 from typing import Optional
 
@@ -22,7 +26,58 @@ import torch
 
 from ._lib import PRECISIONS, check, lib
 
-__all__ = ["shard_range", "FramePipeline", "DceppBatchStream", "gather_max_ms", "gather_objects"]
+__all__ = ["shard_range", "FramePipeline", "DceppBatchStream", "gather_max_ms", "gather_objects", "gpu_local_cpus",
+           "numa_local", "parse_cpulist"]
+
+
+def parse_cpulist(text: str) -> list:
+    """Linux cpulist syntax ("0-3,8,10-11") -> sorted list of CPU numbers."""
+    cpus = set()
+    for part in text.strip().split(","):
+        part = part.strip()
+        if not part:
+            continue
+        if "-" in part:
+            a, b = part.split("-", 1)
+            cpus.update(range(int(a), int(b) + 1))
+        else:
+            cpus.add(int(part))
+    return sorted(cpus)
+
+
+def gpu_local_cpus(device_index: int, sysfs: str = "/sys/bus/pci/devices") -> Optional[list]:
+    """CPUs of the NUMA node the GPU's PCIe root port hangs off (sysfs `local_cpulist`), or None if unknown."""
+    try:
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(os.path.join(sysfs, bdf, "local_cpulist")) as f:
+            cpus = parse_cpulist(f.read())
+    except Exception:
+        return None
+    allowed = os.sched_getaffinity(0)
+    cpus = [c for c in cpus if c in allowed]
+    return cpus or None
+
+
+@contextlib.contextmanager
+def numa_local(device_index: int):
+    """Run the calling thread on the GPU's local CPUs while host buffers are allocated inside the `with` block:
+    first touch places the pinned pages on the GPU's own NUMA node.  The previous affinity is restored on exit;
+    a no-op (yields None) where sysfs does not tell.  Yields the CPU list used."""
+    cpus = gpu_local_cpus(device_index)
+    if not cpus:
+        yield None
+        return
+    before = os.sched_getaffinity(0)
+    try:
+        os.sched_setaffinity(0, cpus)
+    except OSError:
+        yield None
+        return
+    try:
+        yield cpus
+    finally:
+        os.sched_setaffinity(0, before)
 
 
 def shard_range(n_frames: int, rank: int, world_size: int) -> range:

@@ -139,6 +139,16 @@ def test_zero_dcepp_state_dict_layout_init_and_file_weights(tmp_path):
     assert set(P.remap_upstream_dcepp_keys(up)) == set(m.state_dict())
 
 
+def test_numa_helpers(tmp_path):
+    from etss_07_imageenhance_b200 import sched
+    assert sched.parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    assert sched.parse_cpulist("") == []
+    before = os.sched_getaffinity(0)
+    with sched.numa_local(0) as cpus:  # no CUDA device here: unknown topology -> no-op
+        assert cpus is None or set(cpus) <= before
+    assert os.sched_getaffinity(0) == before
+
+
 def test_ruas_state_dict_and_pack_layout(lib_built):
     """Key names = upstream Network (ruas/model.py:152-200; pinned by oracle/pin_against_reference.py loading the same
     dict into the upstream modules); pack order = include/b200dce.h."""
