@@ -262,6 +262,7 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
         return {"workload": "C1 shape on GPU: zero_dce++ sf=1 1x3x512x512", "ms": ms,
                 "mp_s": 512 * 512 / 1e6 / (ms / 1e3)}
 
+    guarded("c2_dce_bf16_1080p_b16", c2("bf16", 16, 10))
     guarded("c3_dcepp_4k_b8", c3)
     guarded("c3_dcepp_4k_b8_no_adjust", c3_noadj)
     guarded("c4_sci_1080p_b16", c4)
@@ -269,7 +270,6 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
     guarded("c4_ruas_no_denoise_1080p_b16", c4_ruas(False))
     guarded("c2_dce_fp32_1080p_b2", c2("fp32", 2, 3))
     guarded("c2_dce_bf16x3_1080p_b16", c2("bf16x3", 16, 3))
-    guarded("c2_dce_bf16_1080p_b16", c2("bf16", 16, 5))
     guarded("c1_dcepp_sf1_512", sf1)
     return out
 

@@ -323,6 +323,33 @@ def test_ruas_ragged_shapes_vs_oracle(cuda_dev, H, W, B):
     assert maxerr(den, ru[3]) <= TOL and maxerr(noise, rn) <= TOL
 
 
+def test_ruas_and_sci_through_infer_shim(cuda_dev):
+    """`infer()` (resize up to a multiple of 32, forward, resize back; "time" first, "enhanced" last) for the two
+    upstream-only enhancers."""
+    x = O.synthetic_lowlight(1, 45, 70, seed=73)
+    sd = O.make_ruas_state_dict(33, "init")
+    m = P.RUAS_RE()
+    m.load_state_dict(sd)
+    out = m.to(cuda_dev).infer({"image": x})
+    assert list(out.keys()) == ["time", "illumination", "enhanced_no_denoise", "noise", "enhanced"]
+
+    def fwd(t):
+        u, tl, n = O.ruas_forward(t, sd)
+        return {"illumination": tl[2], "enhanced_no_denoise": u[2], "noise": n, "enhanced": u[3]}
+    ref = O.infer(fwd, x)
+    for k in ref:
+        assert out[k].shape == x.shape and maxerr(out[k], ref[k]) <= TOL, k
+
+    sd = O.make_sci_state_dict(35, "stress")
+    m = P.SCI_RE()
+    m.enhance.load_state_dict({**sd, **{"blocks.0." + k[5:]: v for k, v in sd.items() if k.startswith("conv.")}})
+    out = m.to(cuda_dev).infer({"image": x})
+    ref = O.infer(lambda t: dict(zip(("illumination", "enhanced"), O.sci_forward(t, sd))), x)
+    assert list(out.keys()) == ["time", "illumination", "enhanced"]
+    for k in ref:
+        assert maxerr(out[k], ref[k]) <= TOL, k
+
+
 def test_ruas_1080p_tile_seams(cuda_dev):
     """Full-size frame: every 12 x 32 tile seam and the frame borders against the oracle on crops whose receptive
     field (3 IEM iterations x 3 px + stem/tail/3 NRM cells x 2..1 px = 17 px) lies inside the crop's margin."""
