@@ -250,6 +250,19 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
             // output row j lives in the block opened by input row g_base + j; the two extra input rows of an item
             // open blocks that stay unused for this lap (phases are still completed so that every barrier's parity
             // is a function of g alone)
+            // layer 7: the curve input x of the row after this one is fetched while this row is processed (the load
+            // is independent of the accumulator; issued after the tensor-memory wait it sat on the row's critical path)
+            float xnext[3] = {0.f, 0.f, 0.f};
+            if constexpr (LAST) {
+                if (xx < W) {
+                    const int jf = EPG == 2 ? (int)((g_base ^ (uint32_t)par) & 1) : 0;
+                    if (jf < nout) {
+                        const float* xp = args.x + (size_t)b * 3 * plane + (size_t)(y0 + jf) * W + xx;
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) xnext[c] = __ldg(xp + (size_t)c * plane);
+                    }
+                }
+            }
             for (int j = EPG == 2 ? (int)((g_base ^ (uint32_t)par) & 1) : 0; j < nout + 2; j += EPG) {
                 const uint32_t g = g_base + j;
                 const int p = TC_NB - 1 - (int)(g & (TC_NB - 1));
@@ -306,7 +319,11 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                     float* ep = args.enhanced + (size_t)b * 3 * plane + pix;
                     float yv[3];
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) yv[c] = __ldg(xp + (size_t)c * plane);
+                    for (int c = 0; c < 3; ++c) yv[c] = xnext[c];
+                    if (j + EPG < nout) {
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) xnext[c] = __ldg(xp + (size_t)c * plane + (size_t)EPG * W);
+                    }
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         if (i < iters) {
