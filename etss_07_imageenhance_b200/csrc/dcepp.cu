@@ -310,6 +310,18 @@ dcepp_apply_vec4_kernel(const float* __restrict__ x, const float* __restrict__ a
         const int b = strip / strips_per_frame;
         const int Y0 = (strip - b * strips_per_frame) * R;
         const int rows = min(R, H - Y0);
+        const size_t plane = (size_t)H * W;
+        const int n_it = rows * W4;
+        // the x values of this thread's NEXT group are always in flight: the first group's loads are issued before
+        // the low-resolution rows of the strip are prepared, the following ones while the current group is computed
+        float4 vn[3];
+        if (t < n_it) {
+            const int rr = t / W4;
+            const size_t base = ((size_t)(b * 3) * H + (Y0 + rr)) * W + (t - rr * W4) * 4;
+            vn[0] = ld_stream4(x + base);
+            vn[1] = ld_stream4(x + base + plane);
+            vn[2] = ld_stream4(x + base + 2 * plane);
+        }
         __syncthreads();
         for (int idx = t; idx < rows * 3 * w; idx += 256) {
             const int rr = idx / (3 * w);
@@ -320,15 +332,18 @@ dcepp_apply_vec4_kernel(const float* __restrict__ x, const float* __restrict__ a
             vrow[idx] = ty.w0 * __ldg(ap + (size_t)ty.i0 * w) + ty.w1 * __ldg(ap + (size_t)ty.i1 * w);
         }
         __syncthreads();
-        for (int it = t; it < rows * W4; it += 256) {
+        for (int it = t; it < n_it; it += 256) {
             const int rr = it / W4;
             const int X = (it - rr * W4) * 4;
             const size_t base = ((size_t)(b * 3) * H + (Y0 + rr)) * W + X;
-            const size_t plane = (size_t)H * W;
-            float4 v[3];
-            v[0] = ld_stream4(x + base);
-            v[1] = ld_stream4(x + base + plane);
-            v[2] = ld_stream4(x + base + 2 * plane);
+            float4 v[3] = {vn[0], vn[1], vn[2]};
+            if (it + 256 < n_it) {
+                const int rn = (it + 256) / W4;
+                const size_t bn = ((size_t)(b * 3) * H + (Y0 + rn)) * W + (it + 256 - rn * W4) * 4;
+                vn[0] = ld_stream4(x + bn);
+                vn[1] = ld_stream4(x + bn + plane);
+                vn[2] = ld_stream4(x + bn + 2 * plane);
+            }
             Tap tx[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) tx[j] = tap_align_corners(X + j, sw, w);
