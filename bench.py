@@ -203,6 +203,11 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
     L = P._lib.lib()
 
     def guarded(name, fn):
+        # every extra is timed "alone": the part idles for two seconds first (a 10 % slowdown lingers after the
+        # tensor-core and fp32-pipe heavy extras, profiles/r01e_summary.md) and cached blocks of the previous extra go
+        torch.cuda.synchronize(dev)
+        torch.cuda.empty_cache()
+        time.sleep(2.0)
         try:
             out[name] = fn()
         except Exception as e:  # keep the headline line alive
@@ -262,10 +267,10 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
         return {"workload": "C1 shape on GPU: zero_dce++ sf=1 1x3x512x512", "ms": ms,
                 "mp_s": 512 * 512 / 1e6 / (ms / 1e3)}
 
-    guarded("c2_dce_bf16_1080p_b16", c2("bf16", 16, 10))
     guarded("c3_dcepp_4k_b8", c3)
     guarded("c3_dcepp_4k_b8_no_adjust", c3_noadj)
     guarded("c4_sci_1080p_b16", c4)
+    guarded("c2_dce_bf16_1080p_b16", c2("bf16", 16, 10))
     guarded("c4_ruas_1080p_b16", c4_ruas(True))
     guarded("c4_ruas_no_denoise_1080p_b16", c4_ruas(False))
     guarded("c2_dce_fp32_1080p_b2", c2("fp32", 2, 3))
