@@ -119,7 +119,7 @@ __device__ __forceinline__ void c5_part(const float* __restrict__ w, const float
 // ------------------------------------------------------------------------------------------------ IEM iteration
 // K0: first iteration (t_hat = max_operation(y));  else t_hat = max_operation(u) - 0.5 (u - y)   (model.py:84-89)
 template <bool K0>
-__global__ void __launch_bounds__(R_THREADS) ruas_iem_kernel(const float* __restrict__ y, const float* __restrict__ u,
+__global__ void __launch_bounds__(R_THREADS, 6) ruas_iem_kernel(const float* __restrict__ y, const float* __restrict__ u,
                                                              float* __restrict__ u_out, float* __restrict__ t_out,
                                                              const RuasIemCell c, int H, int W) {
     constexpr int TH = IEM_TH, R1_H = TH + 4, R2_H = TH + 2, P1 = R1_H * R1_W, P2 = R2_H * R2_W;
