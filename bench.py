@@ -377,8 +377,9 @@ def run_b200(args) -> None:
             dist.barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record(stream)
-        for _ in range(e2e_steps):
-            pipe.run(host_in, host_out)
+        for _ in range(e2e_steps):  # streaming form: no drain / refill of the copy pipeline between steps
+            pipe.run(host_in, host_out, wait=False)
+        pipe.drain()
         f1.record(stream)
         torch.cuda.synchronize(dev)
         e2e_ms = f0.elapsed_time(f1)
@@ -398,7 +399,8 @@ def run_b200(args) -> None:
             g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             g0.record(stream)
             for _ in range(e2e_steps):
-                pipe8.run(hin8, hout8)
+                pipe8.run(hin8, hout8, wait=False)
+            pipe8.drain()
             g1.record(stream)
             torch.cuda.synchronize(dev)
             u8 = {"ms_per_step": g0.elapsed_time(g1) / e2e_steps, "bytes_each_way": hin8.numel()}
@@ -431,8 +433,8 @@ def run_b200(args) -> None:
             "e2e": {"value": e2e_value, "unit": "MP/s", "h2d_bytes_per_step": host_in.numel() * 4,
                     "d2h_bytes_per_step": host_out.numel() * 4, "ms_per_step": e2e_ms / e2e_steps,
                     "pinned_numa_local_cpus": len(numa_cpus) if numa_cpus else None,
-                    "path": "FramePipeline(wire=f32): pinned host x -> H2D -> b200_dcepp_forward -> D2H enhanced, "
-                            "2-frame chunks on 3 streams", "matches_device_result": e2e_ok, "u8_wire": u8},
+                    "path": "FramePipeline(wire=f32).run(wait=False): pinned host x -> H2D -> b200_dcepp_forward -> D2H "
+                            "enhanced, 2-frame chunks on 3 streams, slot ring turning across steps, drain() at the end", "matches_device_result": e2e_ok, "u8_wire": u8},
             "gpu_launches": args.steps * 3,  # layer-1 kernel + persistent net kernel + full-resolution pass
             "roofline": {"bound": "hbm", "kernel": "dcepp_apply_vec4_kernel<true>", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,

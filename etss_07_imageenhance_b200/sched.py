@@ -167,6 +167,8 @@ class FramePipeline:
                 u8_in=torch.empty(F, H, W, 3, dtype=torch.uint8, device=dev) if wire == "u8" else None,
                 u8_out=torch.empty(F, H, W, 3, dtype=torch.uint8, device=dev) if wire == "u8" else None))
         self.launches = 0  # kernels launched by the last run()
+        self._chunk = 0         # running chunk counter: the slot ring keeps turning across run() calls
+        self._streaming = False
 
     # kernels per chunk, for the bench's gpu_launches claim
     def _launches_per_chunk(self, n: int) -> int:
@@ -188,9 +190,15 @@ class FramePipeline:
             check(L.b200_sci_forward(s.x.data_ptr(), self.packed.data_ptr(), adj, s.enhanced.data_ptr(), n, H, W, st),
                   "b200_sci_forward")
 
-    def run(self, host_in: torch.Tensor, host_out: torch.Tensor, host_adjust: Optional[torch.Tensor] = None) -> None:
+    def run(self, host_in: torch.Tensor, host_out: torch.Tensor, host_adjust: Optional[torch.Tensor] = None,
+            wait: bool = True) -> None:
         """Enqueue all chunks of `host_in` (pinned; [N,3,H,W] f32 or [N,H,W,3] u8) and wait for the
-        results in `host_out` (pinned, same format).  `host_adjust` (f32 wire only) receives the curve maps."""
+        results in `host_out` (pinned, same format).  `host_adjust` (f32 wire only) receives the curve maps.
+
+        `wait=False` is the streaming form: the call returns once everything is enqueued, the slot ring keeps turning
+        across calls (the first H2D copy of the next batch overlaps the last D2H copies of this one instead of a
+        drain / refill of the pipeline at every batch boundary), and the caller owns the hazard on the host buffers:
+        `host_in` must stay untouched and `host_out` unread until `drain()` returns."""
         N = host_in.shape[0]
         if not (host_in.is_pinned() and host_out.is_pinned()):
             raise ValueError("FramePipeline.run needs pinned host tensors")
@@ -199,11 +207,14 @@ class FramePipeline:
         L = lib()
         self.launches = 0
         cur = torch.cuda.current_stream(self.device)
-        for s in self.slots:
-            s.stream.wait_stream(cur)
-        for ci, i0 in enumerate(range(0, N, self.F)):
+        if not self._streaming:  # work queued on the caller's stream (e.g. the producer of host_in) comes first
+            for s in self.slots:
+                s.stream.wait_stream(cur)
+        self._streaming = not wait
+        for i0 in range(0, N, self.F):
             n = min(self.F, N - i0)
-            s = self.slots[ci % len(self.slots)]
+            s = self.slots[self._chunk % len(self.slots)]
+            self._chunk += 1
             with torch.cuda.stream(s.stream):
                 if self.wire == "u8":
                     s.u8_in[:n].copy_(host_in[i0:i0 + n], non_blocking=True)
@@ -221,9 +232,16 @@ class FramePipeline:
                     if host_adjust is not None:
                         host_adjust[i0:i0 + n].copy_(s.adjust[:n], non_blocking=True)
             self.launches += self._launches_per_chunk(n)
+        if wait:
+            self.drain()
+
+    def drain(self) -> None:
+        """Join the slot streams into the current stream and wait on the host for everything enqueued so far."""
+        cur = torch.cuda.current_stream(self.device)
         for s in self.slots:
             cur.wait_stream(s.stream)
         cur.synchronize()
+        self._streaming = False
 
 
 

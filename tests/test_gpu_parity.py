@@ -288,6 +288,23 @@ def test_sci_ragged_shapes_vs_oracle(cuda_dev, H, W, B):
     assert maxerr(illu, ri) <= TIGHT and maxerr(r, rr) <= TOL
 
 
+def test_frame_pipeline_streaming_calls_match_direct_forward(cuda_dev):
+    """run(wait=False) x3 + drain(): the slot ring keeps turning across calls, results as from the model."""
+    H, W, N = 48, 72, 5
+    sd = O.make_dcepp_state_dict(5, "stress")
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=12), sd).to(cuda_dev)
+    pipe = P.FramePipeline(m, frames_per_chunk=2, H=H, W=W, wire="f32", slots=3)
+    ins = [O.synthetic_lowlight(N, H, W, seed=10 + i).pin_memory() for i in range(3)]
+    outs = [torch.zeros_like(t).pin_memory() for t in ins]
+    for a, b in zip(ins, outs):
+        pipe.run(a, b, wait=False)
+    pipe.drain()
+    for a, b in zip(ins, outs):
+        assert torch.equal(b, m({"image": a.to(cuda_dev)})["enhanced"].cpu())
+    pipe.run(ins[0], outs[1])  # and the blocking form still works afterwards
+    assert torch.equal(outs[1], outs[0])
+
+
 # ------------------------------------------------------------------ RUAS
 @pytest.mark.parametrize("regime", ["init", "stress"])
 def test_ruas_golden(cuda_dev, golden, regime):
