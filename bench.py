@@ -364,7 +364,7 @@ def run_b200(args) -> None:
         stream_ms = b0.elapsed_time(b1) / args.steps
 
         # ---- end to end: pinned host frames -> FramePipeline -> pinned host results, every step
-        pipe = P.FramePipeline(model, frames_per_chunk=2, H=H, W=W, wire="f32", slots=3)
+        pipe = P.FramePipeline(model, frames_per_chunk=4, H=H, W=W, wire="f32", slots=4)  # sweep: tools/time_e2e.py
         with P.sched.numa_local(local) as numa_cpus:  # pinned pages on this GPU's NUMA node
             host_in = torch.empty(FRAMES, 3, H, W, pin_memory=True)
             host_in.copy_(x)
@@ -388,7 +388,7 @@ def run_b200(args) -> None:
         # u8 wire variant: same frames as HWC uint8 both ways
         u8 = None
         try:
-            pipe8 = P.FramePipeline(model, frames_per_chunk=1, H=H, W=W, wire="u8", slots=3)
+            pipe8 = P.FramePipeline(model, frames_per_chunk=1, H=H, W=W, wire="u8", slots=4)
             with P.sched.numa_local(local):
                 hin8 = torch.empty(FRAMES, H, W, 3, dtype=torch.uint8, pin_memory=True)
                 hin8.copy_(torch.ops.b200dce.f32nchw_to_u8hwc(x))
@@ -434,7 +434,7 @@ def run_b200(args) -> None:
                     "d2h_bytes_per_step": host_out.numel() * 4, "ms_per_step": e2e_ms / e2e_steps,
                     "pinned_numa_local_cpus": len(numa_cpus) if numa_cpus else None,
                     "path": "FramePipeline(wire=f32).run(wait=False): pinned host x -> H2D -> b200_dcepp_forward -> D2H "
-                            "enhanced, 2-frame chunks on 3 streams, slot ring turning across steps, drain() at the end", "matches_device_result": e2e_ok, "u8_wire": u8},
+                            "enhanced, 4-frame chunks on 4 streams, slot ring turning across steps, drain() at the end", "matches_device_result": e2e_ok, "u8_wire": u8},
             "gpu_launches": args.steps * 3,  # layer-1 kernel + persistent net kernel + full-resolution pass
             "roofline": {"bound": "hbm", "kernel": "dcepp_apply_vec4_kernel<true>", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,

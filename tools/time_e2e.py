@@ -15,15 +15,16 @@ for wire in ("f32", "u8"):
     if wire == "u8":
         hin8 = (hin.permute(0, 2, 3, 1) * 255).to(torch.uint8).contiguous().pin_memory()
         hout8 = torch.empty_like(hin8).pin_memory()
-    for chunk, slots in ((1, 3), (2, 3), (2, 4), (4, 2), (4, 3), (4, 4), (8, 2), (16, 1)):
+    for chunk, slots in ((1, 2), (1, 3), (1, 4), (1, 6), (2, 2), (2, 3), (2, 4), (2, 6), (4, 2), (4, 3), (4, 4), (8, 2)):
         pipe = P.FramePipeline(m, frames_per_chunk=chunk, H=H, W=W, wire=wire, slots=slots)
         a, b = (hin, hout) if wire == "f32" else (hin8, hout8)
         for _ in range(2):
             pipe.run(a, b)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(8):
-            pipe.run(a, b)
+        for _ in range(8):  # streaming form (the bench's e2e leg): the slot ring turns across steps
+            pipe.run(a, b, wait=False)
+        pipe.drain()
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 8
