@@ -118,12 +118,13 @@ class _Slot:
     workspace: torch.Tensor            # bytes
     u8_in: Optional[torch.Tensor]      # [F,H,W,3] u8
     u8_out: Optional[torch.Tensor]
+    aux: Optional[torch.Tensor] = None  # RUAS: u_list[0..2] as [3,F,3,H,W]
 
 
 class FramePipeline:
     """Streams frames host -> B200 -> host through one of the drop-in models.
 
-    model: ZeroDCEpp_RE | ZeroDCE_RE | SCI_RE (on a CUDA device).  `wire`: "f32" (NCHW float32, the
+    model: ZeroDCEpp_RE | ZeroDCE_RE | SCI_RE | RUAS_RE (on a CUDA device).  `wire`: "f32" (NCHW float32, the
     reference's tensor format) or "u8" (HWC uint8 frames, the reference's on-disk/video format)."""
 
     def __init__(self, model, frames_per_chunk: int, H: int, W: int, wire: str = "f32", slots: int = 3,
@@ -152,6 +153,11 @@ class FramePipeline:
         elif isinstance(model, M.SCI_RE):
             self.kind, self.adj_ch = "sci", 3
             ws_bytes = 0
+        elif isinstance(model, M.RUAS_RE):
+            if return_adjust:
+                raise ValueError("RUAS has no curve map; return_adjust is for the Zero-DCE family / SCI's illumination")
+            self.kind, self.adj_ch = "ruas", 3
+            ws_bytes = L.b200_ruas_workspace_bytes(F, H, W, int(model.denoise))
         else:
             raise TypeError(f"unsupported model {type(model)}")
         self.packed = model.packed_weights()
@@ -165,14 +171,16 @@ class FramePipeline:
                 adjust=torch.empty(F, self.adj_ch, H, W, device=dev) if return_adjust else None,
                 workspace=torch.empty(max(ws_bytes, 256), dtype=torch.uint8, device=dev),
                 u8_in=torch.empty(F, H, W, 3, dtype=torch.uint8, device=dev) if wire == "u8" else None,
-                u8_out=torch.empty(F, H, W, 3, dtype=torch.uint8, device=dev) if wire == "u8" else None))
+                u8_out=torch.empty(F, H, W, 3, dtype=torch.uint8, device=dev) if wire == "u8" else None,
+                aux=torch.empty(3, F, 3, H, W, device=dev) if self.kind == "ruas" else None))
         self.launches = 0  # kernels launched by the last run()
         self._chunk = 0         # running chunk counter: the slot ring keeps turning across run() calls
         self._streaming = False
 
     # kernels per chunk, for the bench's gpu_launches claim
     def _launches_per_chunk(self, n: int) -> int:
-        k = {"dcepp": 3, "dce": 8 * ((n + 1) // 2) if self.prec == 0 else 8, "sci": 1}[self.kind]
+        k = {"dcepp": 3, "dce": 8 * ((n + 1) // 2) if self.prec == 0 else 8, "sci": 1,
+             "ruas": 8 if getattr(self.model, "denoise", False) else 3}[self.kind]
         return k + (2 if self.wire == "u8" else 0)
 
     def _launch(self, s: _Slot, n: int) -> None:
@@ -186,6 +194,16 @@ class FramePipeline:
             check(L.b200_dce_forward(s.x.data_ptr(), self.packed.data_ptr(), adj, s.enhanced.data_ptr(), n, H, W,
                                      self.model.num_iters, self.prec, s.workspace.data_ptr(), s.workspace.numel(), st),
                   "b200_dce_forward")
+        elif self.kind == "ruas":
+            # `aux` is sized for a full chunk: with n < F the three u maps are still [3][F,...] apart, so the kernel is
+            # pointed at a compact [3][n,3,H,W] view of the same storage
+            u = s.aux.view(-1)[:3 * n * 3 * H * W]
+            den = self.model.denoise
+            check(L.b200_ruas_forward(s.x.data_ptr(), self.packed.data_ptr(), u.data_ptr(), None,
+                                      s.enhanced.data_ptr() if den else None, None, n, H, W, s.workspace.data_ptr(),
+                                      s.workspace.numel(), st), "b200_ruas_forward")
+            if not den:  # u_list[2] is the result
+                s.enhanced[:n].copy_(u.view(3, n, 3, H, W)[2], non_blocking=True)
         else:
             check(L.b200_sci_forward(s.x.data_ptr(), self.packed.data_ptr(), adj, s.enhanced.data_ptr(), n, H, W, st),
                   "b200_sci_forward")

@@ -305,6 +305,22 @@ def test_frame_pipeline_streaming_calls_match_direct_forward(cuda_dev):
     assert torch.equal(outs[1], outs[0])
 
 
+@pytest.mark.parametrize("denoise", [True, False])
+def test_frame_pipeline_ruas(cuda_dev, denoise):
+    H, W, N = 40, 56, 5
+    sd = O.make_ruas_state_dict(41, "stress")
+    m = P.RUAS_RE(denoise=denoise)
+    m.load_state_dict(sd)
+    m = m.to(cuda_dev)
+    pipe = P.FramePipeline(m, frames_per_chunk=2, H=H, W=W, wire="f32", slots=2)
+    hin = O.synthetic_lowlight(N, H, W, seed=12).pin_memory()
+    hout = torch.zeros_like(hin).pin_memory()
+    pipe.run(hin, hout)
+    assert torch.equal(hout, m({"image": hin.to(cuda_dev)})["enhanced"].cpu())
+    u, _, _ = O.ruas_forward(hin, sd, denoise=denoise)
+    assert maxerr(hout, u[3] if denoise else u[2]) <= TOL
+
+
 # ------------------------------------------------------------------ RUAS
 @pytest.mark.parametrize("regime", ["init", "stress"])
 def test_ruas_golden(cuda_dev, golden, regime):
