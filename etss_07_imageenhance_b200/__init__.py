@@ -18,7 +18,11 @@ from .models import (DSConv2d, DepthwiseSeparableConv2d, SCI_RE, RUAS_RE, ZeroDC
 from .registry import MODELS, ModelFactory, register_into_mon
 from .sched import DceppBatchStream, FramePipeline, gather_max_ms, gather_objects, shard_range
 
-__version__ = "0.1.0"
+# Drop-in step: when `mon` imports in this interpreter, the B200 classes replace the reference's entries in
+# mon.MODELS (register(..., replace=True), src/mon/core/factory.py:300-328); without `mon` this is a no-op.
+MON_REGISTERED = register_into_mon()
+
+__version__ = "0.2.0"
 __all__ = ["ops", "MODELS", "ModelFactory", "register_into_mon", "ZeroDCE_RE", "ZeroDCEpp_RE", "SCI_RE", "RUAS_RE", "DSConv2d",
            "DepthwiseSeparableConv2d", "ZeroDCELoss", "remap_upstream_dcepp_keys", "FramePipeline", "DceppBatchStream", "shard_range",
            "gather_max_ms", "gather_objects"]

@@ -23,10 +23,12 @@ extern "C" int b200_check_device(void) {
         (void)cudaGetLastError();
         return B200_ERR_NO_DEVICE;
     }
-    int major = 0;
-    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) {
+    // the library carries sm_100a SASS only (arch-specific target: it does not load on sm_103 or any other 10.x part)
+    int major = 0, minor = -1;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev) != cudaSuccess) {
         (void)cudaGetLastError();
         return B200_ERR_NO_DEVICE;
     }
-    return major == 10 ? B200_OK : B200_ERR_NO_DEVICE;
+    return major == 10 && minor == 0 ? B200_OK : B200_ERR_NO_DEVICE;
 }

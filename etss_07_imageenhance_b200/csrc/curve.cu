@@ -108,6 +108,11 @@ static int launch_curve(const float* x, const float* a, float* y, int B, int C, 
 }
 
 // ---- u8 HWC <-> fp32 NCHW (C = 3) ------------------------------------------------
+// to_image_tensor(normalize=True) -> normalize_image_by_range (core/image/photometry.py:262-263):
+//   image = (image - 0.0) * ratio + 0.0   with ratio = 1/255 (a Python double) applied to an fp32 tensor,
+// i.e. ONE fp32 multiply by fl32(1/255) -- not a division (the two differ in the last bit for 126 byte values).
+__device__ __forceinline__ float from_u8(uint32_t byte) { return __fmul_rn((float)byte, 1.f / 255.f); }
+
 // One thread handles 4 consecutive pixels = 12 interleaved bytes (3 x 32-bit words).
 __global__ void __launch_bounds__(256) u8hwc_to_f32nchw_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst,
                                                                long long frames, long long hw) {
@@ -120,20 +125,19 @@ __global__ void __launch_bounds__(256) u8hwc_to_f32nchw_kernel(const uint8_t* __
         const uint32_t* s = reinterpret_cast<const uint32_t*>(src + (f * hw + p4 * 4) * 3);
         const uint32_t w0 = __ldg(s), w1 = __ldg(s + 1), w2 = __ldg(s + 2);
         // bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
-        const float k = 255.f;
         float4 r, g, b;
-        r.x = __fdiv_rn((float)(w0 & 0xff), k);
-        g.x = __fdiv_rn((float)((w0 >> 8) & 0xff), k);
-        b.x = __fdiv_rn((float)((w0 >> 16) & 0xff), k);
-        r.y = __fdiv_rn((float)(w0 >> 24), k);
-        g.y = __fdiv_rn((float)(w1 & 0xff), k);
-        b.y = __fdiv_rn((float)((w1 >> 8) & 0xff), k);
-        r.z = __fdiv_rn((float)((w1 >> 16) & 0xff), k);
-        g.z = __fdiv_rn((float)(w1 >> 24), k);
-        b.z = __fdiv_rn((float)(w2 & 0xff), k);
-        r.w = __fdiv_rn((float)((w2 >> 8) & 0xff), k);
-        g.w = __fdiv_rn((float)((w2 >> 16) & 0xff), k);
-        b.w = __fdiv_rn((float)(w2 >> 24), k);
+        r.x = from_u8(w0 & 0xff);
+        g.x = from_u8((w0 >> 8) & 0xff);
+        b.x = from_u8((w0 >> 16) & 0xff);
+        r.y = from_u8(w0 >> 24);
+        g.y = from_u8(w1 & 0xff);
+        b.y = from_u8((w1 >> 8) & 0xff);
+        r.z = from_u8((w1 >> 16) & 0xff);
+        g.z = from_u8(w1 >> 24);
+        b.z = from_u8(w2 & 0xff);
+        r.w = from_u8((w2 >> 8) & 0xff);
+        g.w = from_u8((w2 >> 16) & 0xff);
+        b.w = from_u8(w2 >> 24);
         float* d = dst + f * 3 * hw + p4 * 4;
         st_stream4(d, r);
         st_stream4(d + hw, g);
@@ -141,8 +145,25 @@ __global__ void __launch_bounds__(256) u8hwc_to_f32nchw_kernel(const uint8_t* __
     }
 }
 
+// H*W not a multiple of 4 (frames are then not word aligned): one pixel per thread
+__global__ void __launch_bounds__(256) u8hwc_to_f32nchw_scalar_kernel(const uint8_t* __restrict__ src,
+                                                                      float* __restrict__ dst, long long frames,
+                                                                      long long hw) {
+    const long long total = frames * hw;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long f = i / hw, p = i - f * hw;
+        const uint8_t* s = src + i * 3;
+        float* d = dst + f * 3 * hw + p;
+        d[0] = from_u8(s[0]);
+        d[hw] = from_u8(s[1]);
+        d[2 * hw] = from_u8(s[2]);
+    }
+}
+
 __device__ __forceinline__ uint32_t to_u8(float v) {
-    // to_image_nparray(denormalize=True): v*255 then astype(uint8) (truncation toward zero)
+    // to_image_nparray(denormalize=True): v*255 then astype(uint8) (truncation toward zero).  Values outside [0, 1]
+    // are implementation-defined in the reference (C float -> uint8 cast); they are clamped here.
     float t = __fmul_rn(fminf(fmaxf(v, 0.f), 1.f), 255.f);
     return (uint32_t)(int)t;
 }
@@ -164,6 +185,21 @@ __global__ void __launch_bounds__(256) f32nchw_to_u8hwc_kernel(const float* __re
         d[0] = w0;
         d[1] = w1;
         d[2] = w2;
+    }
+}
+
+__global__ void __launch_bounds__(256) f32nchw_to_u8hwc_scalar_kernel(const float* __restrict__ src,
+                                                                      uint8_t* __restrict__ dst, long long frames,
+                                                                      long long hw) {
+    const long long total = frames * hw;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long f = i / hw, p = i - f * hw;
+        const float* s = src + f * 3 * hw + p;
+        uint8_t* d = dst + i * 3;
+        d[0] = (uint8_t)to_u8(s[0]);
+        d[1] = (uint8_t)to_u8(s[hw]);
+        d[2] = (uint8_t)to_u8(s[2 * hw]);
     }
 }
 
@@ -214,8 +250,12 @@ extern "C" int b200_u8hwc_to_f32nchw(const uint8_t* src, float* dst, int B, int 
     if (!src || !dst) return B200_ERR_NULL;
     if (B <= 0 || H <= 0 || W <= 0) return B200_ERR_BAD_SHAPE;
     const long long hw = (long long)H * W;
-    if (hw % 4 != 0) return B200_ERR_UNSUPPORTED;
-    if (!b200::aligned16(dst) || (reinterpret_cast<uintptr_t>(src) & 3u)) return B200_ERR_MISALIGNED;
+    if (hw % 4 != 0 || !b200::aligned16(dst) || (reinterpret_cast<uintptr_t>(src) & 3u)) {
+        long long blocks = ((long long)B * hw + 255) / 256;
+        if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
+        b200::u8hwc_to_f32nchw_scalar_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, B, hw);
+        return b200::launch_status();
+    }
     long long blocks = ((long long)B * (hw / 4) + 255) / 256;
     if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
     b200::u8hwc_to_f32nchw_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, B, hw);
@@ -226,8 +266,12 @@ extern "C" int b200_f32nchw_to_u8hwc(const float* src, uint8_t* dst, int B, int 
     if (!src || !dst) return B200_ERR_NULL;
     if (B <= 0 || H <= 0 || W <= 0) return B200_ERR_BAD_SHAPE;
     const long long hw = (long long)H * W;
-    if (hw % 4 != 0) return B200_ERR_UNSUPPORTED;
-    if (!b200::aligned16(src) || (reinterpret_cast<uintptr_t>(dst) & 3u)) return B200_ERR_MISALIGNED;
+    if (hw % 4 != 0 || !b200::aligned16(src) || (reinterpret_cast<uintptr_t>(dst) & 3u)) {
+        long long blocks = ((long long)B * hw + 255) / 256;
+        if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
+        b200::f32nchw_to_u8hwc_scalar_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, B, hw);
+        return b200::launch_status();
+    }
     long long blocks = ((long long)B * (hw / 4) + 255) / 256;
     if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
     b200::f32nchw_to_u8hwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, dst, B, hw);

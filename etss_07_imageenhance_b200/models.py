@@ -137,6 +137,10 @@ class _EnhancementModel(nn.Module):
         if path is not None:
             if not _is_weights_file(path):
                 raise ValueError(f"Cannot load weights from: {path}")
+            if path.suffix.lower() == ".onnx":
+                # globals.py:709 lists the suffix, but the reference's loader is `torch.load` too (nn/model.py:99-131)
+                # and cannot read an ONNX graph either: fail with a clear message instead of an unpickling error
+                raise ValueError(f"Cannot load weights from an ONNX file ({path}): export a .pt / .pth state_dict")
             dev = next(self.parameters()).device
             sd = torch.load(str(path), weights_only=True, map_location=dev)
         if sd is not None and "state_dict" in sd:
@@ -166,39 +170,39 @@ class _EnhancementModel(nn.Module):
         return next(self.parameters()).device
 
     def infer(self, datapoint: dict, image_size: Any = 512, resize: bool = False, *args, **kwargs) -> dict:
-        """`VisionModel.infer` (vision/model.py:76-127): every image tensor of the datapoint is resized to
-        `image_size` (`resize=True`) or up to the next multiple of 32 (`core.resize(v, divisible_by=32)`,
-        core/image/utils.py:381-382 rounds with ceil), moved to the model's device, run through `forward`, and every
-        image in the outputs whose size differs from the input's is resized back to (h0, w0).  The resize is
+        """`VisionModel.infer` (vision/model.py:76-127), statement by statement: every image tensor of the caller's
+        `datapoint` is replaced IN PLACE by its resized version -- to `image_size` (`resize=True`) or up to the next
+        multiple of 32 (`core.resize(v, divisible_by=32)`, core/image/utils.py:381-382 rounds with ceil) -- and moved
+        to the model's device (:101-109), `forward` runs between `Timer.tick()` / `tock()` (:112-115), every image in
+        the outputs whose size differs from the input's is resized back to (h0, w0) (:119-123) and `"time"` is
+        appended LAST (:126; predict.py:91 pops it by name, then `popitem()` yields "enhanced").  The resize is
         `torch.ops.b200dce.resize_bilinear` (F.interpolate bilinear, align_corners=False -- what kornia's resize
-        calls).  "time" is the forward's wall time (the reference uses an unsynchronised `Timer`; this one
-        synchronises so the number means something) and is inserted FIRST so that `outputs.popitem()` still
-        yields "enhanced" (predict.py:91-98)."""
+        calls); the tensor goes to the device first because the kernel lives there (the reference resizes on the
+        host, same arithmetic).  "time" is the forward's wall time; the reference's `Timer` does not synchronise the
+        device, this one does so that the number means something."""
         self.assert_datapoint(datapoint)
         h0, w0 = datapoint["image"].shape[-2:]
         if resize:
             th, tw = (image_size, image_size) if isinstance(image_size, int) else tuple(image_size)[-2:]
         else:
             th, tw = -(-h0 // 32) * 32, -(-w0 // 32) * 32
-        dp = {}
         for k, v in datapoint.items():
             if isinstance(v, torch.Tensor):
                 v = v.to(self.device)
                 if v.dim() == 4 and v.is_floating_point() and tuple(v.shape[-2:]) != (th, tw):
                     v = torch.ops.b200dce.resize_bilinear(v.float(), th, tw)
-            dp[k] = v
+                datapoint[k] = v
         torch.cuda.synchronize(self.device)
-        t0 = time.perf_counter()
-        outputs = self.forward(datapoint=dp, *args, **kwargs)
+        t0 = time.time()
+        outputs = self.forward(datapoint, *args, **kwargs)
         torch.cuda.synchronize(self.device)
-        elapsed = time.perf_counter() - t0
+        elapsed = time.time() - t0
         self.assert_outputs(outputs)
-        out = {"time": elapsed}
         for k, v in outputs.items():
             if isinstance(v, torch.Tensor) and v.dim() == 4 and tuple(v.shape[-2:]) != (h0, w0):
-                v = torch.ops.b200dce.resize_bilinear(v.contiguous(), h0, w0)
-            out[k] = v
-        return out
+                outputs[k] = torch.ops.b200dce.resize_bilinear(v.contiguous(), h0, w0)
+        outputs["time"] = elapsed
+        return outputs
 
     # ---- packed-weight cache: rebuilt when any parameter's storage / version / device changes
     def _params_key(self, tensors) -> tuple:

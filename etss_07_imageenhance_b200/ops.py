@@ -131,7 +131,7 @@ def dcepp_pack(dw_w: List[Tensor], dw_b: List[Tensor], pw_w: List[Tensor], pw_b:
 
 @dcepp_pack.register_fake
 def _(dw_w, dw_b, pw_w, pw_b):
-    return dw_w[0].new_empty(14000)
+    return dw_w[0].new_empty(lib().b200_dcepp_packed_floats(), dtype=torch.float32)  # host-only query
 
 
 def _check_sf(H: int, W: int, sf: int) -> None:
@@ -241,7 +241,7 @@ def dce_pack(weights: List[Tensor], biases: List[Tensor], iters: int, precision:
 
 @dce_pack.register_fake
 def _(weights, biases, iters, precision):
-    return weights[0].new_empty(400000, dtype=torch.uint8)
+    return weights[0].new_empty(lib().b200_dce_packed_bytes(precision, iters), dtype=torch.uint8)  # host-only query
 
 
 @torch.library.custom_op("b200dce::dce_forward", mutates_args=(), device_types="cuda")

@@ -169,10 +169,16 @@ int b200_ruas_forward(const float* x, const float* packed_host, float* u, float*
 
 /* ------------------------------------------------------------------------- *
  * "next" rows: u8 HWC <-> fp32 NCHW frame conversion.
- * Replaces src/mon/core/image/utils.py:801-848 (to_image_tensor, /255) and
- * :766-800 (to_image_nparray denormalize: *255 then astype(uint8), i.e.
- * truncation; values are clamped to [0,255] first, which is identical for the
- * enhancers' [0,1] outputs).
+ * Replaces src/mon/core/image/utils.py:801-848 (to_image_tensor(normalize=True)
+ * -> normalize_image_by_range, src/mon/core/image/photometry.py:262-263:
+ * (image - 0.0) * ratio + 0.0 with ratio = 1/255, i.e. ONE fp32 multiply by
+ * fl32(1/255) -- bit-exact against the reference, pinned by
+ * oracle/pin_against_reference.py / tests/golden/u8_wire.npz) and :766-800
+ * (to_image_nparray(denormalize=True): *255 in fp32 then astype(uint8), i.e.
+ * truncation; values are clamped to [0,1] first, where the reference's cast is
+ * implementation-defined -- identical for the enhancers' [0,1] outputs).
+ * Any H, W (a scalar kernel takes over when H*W % 4 != 0 or a pointer is not
+ * word / 16-byte aligned).
  * ------------------------------------------------------------------------- */
 int b200_u8hwc_to_f32nchw(const uint8_t* src, float* dst, int B, int H, int W, void* stream);
 int b200_f32nchw_to_u8hwc(const float* src, uint8_t* dst, int B, int H, int W, void* stream);

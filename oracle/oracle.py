@@ -410,6 +410,32 @@ def infer(forward, x: torch.Tensor) -> dict:
                 tuple(v.shape[-2:]) != (h0, w0) else v) for k, v in out.items()}
 
 
+# --------------------------------------------------------------------------- #
+# frame format: u8 HWC <-> fp32 NCHW
+# --------------------------------------------------------------------------- #
+def u8hwc_to_f32nchw(frames: torch.Tensor) -> torch.Tensor:
+    """`to_image_tensor(image, normalize=True)` (src/mon/core/image/utils.py:801-848) for a batch of HWC uint8 frames:
+    channel-first, then `normalize_image` = `normalize_image_by_range(min=0, max=255, new_min=0, new_max=1)`
+    (src/mon/core/image/photometry.py:232-288): cast to the default dtype (fp32), `ratio = (1 - 0) / (255 - 0)` as a
+    Python double, `image = (image - 0.0) * ratio + 0.0` -- i.e. ONE fp32 multiply by fl32(1/255), not a division
+    (the two differ in the last bit for 126 of the 256 byte values).  [B,H,W,3] uint8 -> [B,3,H,W] fp32."""
+    image = frames.permute(0, 3, 1, 2)
+    image = image.to(dtype=torch.float32)
+    ratio = (1.0 - 0.0) / (255.0 - 0.0)
+    return ((image - 0.0) * ratio + 0.0).contiguous()
+
+
+def f32nchw_to_u8hwc(image: torch.Tensor) -> torch.Tensor:
+    """`to_image_nparray(image, denormalize=True)` (src/mon/core/image/utils.py:766-800): numpy fp32,
+    `denormalize_image` = `(image - 0.0) * 255.0 + 0.0` in fp32 (photometry.py:266-270,277-283), `.astype(np.uint8)`
+    (truncation toward zero; no rounding, no clamp), channel-last.  Values outside [0, 1] are implementation-defined
+    in the reference (C float -> uint8 cast); the curve's outputs never leave [0, 1].  [B,3,H,W] fp32 -> [B,H,W,3] u8."""
+    a = image.detach().cpu().numpy().astype(np.float32)
+    ratio = (255.0 - 0.0) / (1.0 - 0.0)
+    a = ((a - 0.0) * ratio + 0.0).astype(np.uint8)
+    return torch.from_numpy(np.ascontiguousarray(a.transpose(0, 2, 3, 1)))
+
+
 def psnr(a: torch.Tensor, b: torch.Tensor) -> float:
     mse = torch.mean((a.double() - b.double()) ** 2).item()
     if mse == 0:

@@ -21,8 +21,10 @@ src/mon/vision/enhance/base.py:32-47).  The arithmetic (`forward`) and the
 parameter names are the reference's own code.
 
 Assertions (all on CPU, fp32): oracle == reference bit-for-bit.
+  * src/mon/core/image/photometry.py, src/mon/core/image/utils.py  (to_image_tensor(normalize=True) /
+    to_image_nparray(denormalize=True): the u8 HWC <-> fp32 NCHW frame format)
 Outputs: tests/golden/{dce,dcepp_sf1,dcepp_sf2,dcepp_sf12,sci,ruas}_{init,stress}.npz
-holding input, weights and the REFERENCE outputs.
+holding input, weights and the REFERENCE outputs; tests/golden/u8_wire.npz.
 """
 from __future__ import annotations
 
@@ -167,6 +169,25 @@ def load_upstream_ruas():
     d = REF / "src/mon_extra/vision/enhance/llie/ruas"
     sys.path.insert(0, str(d))
     return _load_file("up_ruas_model", d / "model.py")
+
+
+def load_reference_image_utils():
+    """src/mon/core/image/{photometry,utils}.py, unmodified, under the stub `mon` (they need only `mon.core.pathlib`
+    for an isinstance check and `mon.core.image.color` for an unrelated function; cv2 / torchvision are installed)."""
+    import pathlib as _pl
+    core = sys.modules["mon.core"]
+    cpath = types.ModuleType("mon.core.pathlib")
+    cpath.Path = _pl.Path
+    image = types.ModuleType("mon.core.image")
+    color = types.ModuleType("mon.core.image.color")
+    core.pathlib, core.image, image.color = cpath, image, color
+    for n, m in [("mon.core.pathlib", cpath), ("mon.core.image", image), ("mon.core.image.color", color)]:
+        sys.modules[n] = m
+    d = REF / "src/mon/core/image"
+    phot = _load_file("mon.core.image.photometry", d / "photometry.py")
+    utils = _load_file("mon.core.image.utils", d / "utils.py")
+    image.photometry, image.utils = phot, utils
+    return phot, utils
 
 
 def to_upstream_keys(sd: dict) -> dict:
@@ -315,6 +336,30 @@ def main():
         save(f"ruas_{regime}", x, sd, u=torch.stack(u_ref), t=torch.stack(t_ref), denoised=ud_ref, noise=n_ref)
         report.append(f"ruas/{regime}: oracle == upstream EnhanceNetwork -> DenoiseNetwork; "
                       f"t in [{t_ref[-1].min():.3f}, {t_ref[-1].max():.3f}], |noise|max={n_ref.abs().max():.3f}")
+
+    # ---------------- u8 HWC <-> fp32 NCHW frame format ----------------
+    phot, iutils = load_reference_image_utils()
+    g = torch.Generator().manual_seed(501)
+    frames = torch.randint(0, 256, (2, 36, 52, 3), dtype=torch.uint8, generator=g)
+    frames[0, 0, :, 0] = torch.arange(52, dtype=torch.uint8)          # every byte value appears
+    frames[0, :32, :8, 1] = torch.arange(256, dtype=torch.uint8).view(32, 8)
+    ref_f = torch.cat([iutils.to_image_tensor(f.numpy(), keepdim=False, normalize=True) for f in frames])
+    got_f = O.u8hwc_to_f32nchw(frames)
+    eq(got_f, ref_f, "u8hwc_to_f32nchw")
+    n_div = int((got_f != frames.permute(0, 3, 1, 2).float() / 255.0).sum())
+    all_bytes = torch.arange(256, dtype=torch.uint8).view(1, 16, 16, 1).expand(1, 16, 16, 3).contiguous()
+    nb = int((O.u8hwc_to_f32nchw(all_bytes)[0, 0] != all_bytes[0, :, :, 0].float() / 255.0).sum())
+    e_img = torch.rand(2, 3, 36, 52, generator=g)
+    e_img[0, :, 0, :4] = torch.tensor([0.0, 1.0, 0.5, 254.999 / 255.0])
+    ref_u = torch.stack([torch.from_numpy(iutils.to_image_nparray(e_img[i:i + 1], keepdim=False, denormalize=True))
+                         for i in range(2)])
+    got_u = O.f32nchw_to_u8hwc(e_img)
+    eq(got_u, ref_u, "f32nchw_to_u8hwc")
+    GOLD.mkdir(parents=True, exist_ok=True)
+    np.savez_compressed(GOLD / "u8_wire.npz", frames=frames.numpy(), f32=ref_f.numpy(), image=e_img.numpy(),
+                        u8=ref_u.numpy())
+    report.append(f"u8 wire: oracle == reference to_image_tensor(normalize=True) / to_image_nparray(denormalize=True); "
+                  f"multiply by fl32(1/255) differs from /255.0 for {nb} of the 256 byte values ({n_div} elements of the fixture)")
 
     (GOLD / "PIN_REPORT.txt").write_text(
         f"generated by oracle/pin_against_reference.py with torch {torch.__version__} (CPU, fp32)\n" +

@@ -7,10 +7,13 @@ import numpy as np
 import pytest
 import torch
 
+from pathlib import Path
+
 import etss_07_imageenhance_b200 as P
 from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
+GOLDEN_DIR = Path(__file__).resolve().parent / "golden"
 TOL = 1e-3      # contract (BASELINE.json north_star, fp32 mode)
 TIGHT = 1e-4    # what the fp32 kernels actually have to meet here
 TIGHT_PP = 2.5e-4  # Zero-DCE++ end to end: the pointwise convs run as 3-term split-bf16 tensor-core MMAs (~2^-16 per product)
@@ -244,7 +247,7 @@ def test_dce_bf16_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
     assert out["adjust"].shape == (B, 3 * iters, H, W)
     assert maxerr(out["adjust"], emu["adjust"]) <= BF16_EMU_TOL
     assert maxerr(out["enhanced"], emu["enhanced"]) <= BF16_EMU_TOL
-    assert O.psnr(out["enhanced"].cpu(), ref["enhanced"]) >= 45.0
+    assert O.psnr(out["enhanced"].cpu(), ref["enhanced"]) >= 50.0   # the contract (BASELINE.json north_star)
 
 
 def test_dce_bf16_zero_weights_identity_1080p(cuda_dev):
@@ -357,14 +360,14 @@ def test_ruas_ragged_shapes_vs_oracle(cuda_dev, H, W, B):
 
 
 def test_ruas_and_sci_through_infer_shim(cuda_dev):
-    """`infer()` (resize up to a multiple of 32, forward, resize back; "time" first, "enhanced" last) for the two
-    upstream-only enhancers."""
+    """`infer()` (resize up to a multiple of 32, forward, resize back; "time" appended last as vision/model.py:126
+    does) for the two upstream-only enhancers."""
     x = O.synthetic_lowlight(1, 45, 70, seed=73)
     sd = O.make_ruas_state_dict(33, "init")
     m = P.RUAS_RE()
     m.load_state_dict(sd)
-    out = m.to(cuda_dev).infer({"image": x})
-    assert list(out.keys()) == ["time", "illumination", "enhanced_no_denoise", "noise", "enhanced"]
+    out = m.to(cuda_dev).infer({"image": x.clone()})
+    assert list(out.keys()) == ["illumination", "enhanced_no_denoise", "noise", "enhanced", "time"]
 
     def fwd(t):
         u, tl, n = O.ruas_forward(t, sd)
@@ -376,9 +379,9 @@ def test_ruas_and_sci_through_infer_shim(cuda_dev):
     sd = O.make_sci_state_dict(35, "stress")
     m = P.SCI_RE()
     m.enhance.load_state_dict({**sd, **{"blocks.0." + k[5:]: v for k, v in sd.items() if k.startswith("conv.")}})
-    out = m.to(cuda_dev).infer({"image": x})
+    out = m.to(cuda_dev).infer({"image": x.clone()})
     ref = O.infer(lambda t: dict(zip(("illumination", "enhanced"), O.sci_forward(t, sd))), x)
-    assert list(out.keys()) == ["time", "illumination", "enhanced"]
+    assert list(out.keys()) == ["illumination", "enhanced", "time"]
     for k in ref:
         assert maxerr(out[k], ref[k]) <= TOL, k
 
@@ -402,15 +405,33 @@ def test_ruas_1080p_tile_seams(cuda_dev):
 
 
 # ------------------------------------------------------------------ frame format + scheduler
-def test_u8_conversions_exact(cuda_dev):
-    g = torch.Generator().manual_seed(5)
-    frames = torch.randint(0, 256, (2, 36, 52, 3), dtype=torch.uint8, generator=g)
+def test_u8_conversions_bit_exact_vs_reference_golden(cuda_dev):
+    """tests/golden/u8_wire.npz holds outputs of the reference's own to_image_tensor(normalize=True) /
+    to_image_nparray(denormalize=True) (oracle/pin_against_reference.py); every byte value appears in `frames`."""
+    z = np.load(GOLDEN_DIR / "u8_wire.npz")
+    frames, image = torch.from_numpy(z["frames"]), torch.from_numpy(z["image"])
+    assert len(torch.unique(frames)) == 256
     f = torch.ops.b200dce.u8hwc_to_f32nchw(frames.to(cuda_dev)).cpu()
-    ref = frames.permute(0, 3, 1, 2).float() / 255.0          # to_image_tensor(normalize=True)
+    assert torch.equal(f, torch.from_numpy(z["f32"])) and torch.equal(f, O.u8hwc_to_f32nchw(frames))
+    back = torch.ops.b200dce.f32nchw_to_u8hwc(image.to(cuda_dev)).cpu()
+    assert torch.equal(back, torch.from_numpy(z["u8"])) and torch.equal(back, O.f32nchw_to_u8hwc(image))
+
+
+@pytest.mark.parametrize("B,H,W", [(2, 36, 52), (1, 5, 7), (3, 1, 1), (2, 33, 31), (1, 1080, 1920)])
+def test_u8_conversions_vs_oracle_any_shape(cuda_dev, B, H, W):
+    # H*W % 4 != 0 takes the scalar kernels (frames are then not word aligned)
+    g = torch.Generator().manual_seed(5)
+    frames = torch.randint(0, 256, (B, H, W, 3), dtype=torch.uint8, generator=g)
+    f = torch.ops.b200dce.u8hwc_to_f32nchw(frames.to(cuda_dev)).cpu()
+    ref = O.u8hwc_to_f32nchw(frames)
     assert torch.equal(f, ref)
-    back = torch.ops.b200dce.f32nchw_to_u8hwc(f.to(cuda_dev)).cpu()
-    ref_back = (ref * 255).to(torch.uint8).permute(0, 2, 3, 1)  # to_image_nparray(denormalize=True): truncation
-    assert torch.equal(back, ref_back)
+    img = torch.rand(B, 3, H, W, generator=g)
+    img.view(-1)[:2] = torch.tensor([0.0, 1.0])
+    back = torch.ops.b200dce.f32nchw_to_u8hwc(img.to(cuda_dev)).cpu()
+    assert torch.equal(back, O.f32nchw_to_u8hwc(img))
+    # round trip of a frame: u8 -> fp32 -> u8 is NOT the identity under the reference's truncation (n/255*255 can land
+    # just below n); the kernel reproduces exactly what the reference does
+    assert torch.equal(torch.ops.b200dce.f32nchw_to_u8hwc(f.to(cuda_dev)).cpu(), O.f32nchw_to_u8hwc(ref))
 
 
 @pytest.mark.parametrize("wire", ["f32", "u8"])
@@ -452,16 +473,23 @@ def test_infer_resizes_to_multiple_of_32_and_back(cuda_dev, H, W):
     x = O.synthetic_lowlight(2, H, W, seed=78)
     sd = O.make_dcepp_state_dict(23, "stress")
     m = load_into(P.ZeroDCEpp_RE(scale_factor=1), sd).to(cuda_dev)
-    out = m.infer({"image": x})                      # CPU tensor in: infer moves it to the model's device
+    dp = {"image": x.clone(), "meta": {"stem": "f"}}
+    out = m.infer(dp)                                # CPU tensor in: infer moves it to the model's device
     ref = O.infer(lambda t: O.zero_dcepp_forward(t, sd, scale_factor=1), x)
-    assert list(out.keys()) == ["time", "adjust", "enhanced"] and out["time"] > 0
-    out.pop("time")
-    k, v = out.popitem()                             # predict.py:91-98 takes the last item as the image to save
+    # vision/model.py:101-109 writes the resized, device-resident tensors back into the CALLER's datapoint
+    assert dp["image"].is_cuda and tuple(dp["image"].shape[-2:]) == (-(-H // 32) * 32, -(-W // 32) * 32)
+    assert maxerr(dp["image"], O.infer_resize(x)) <= 1e-6 and dp["meta"] == {"stem": "f"}
+    # :126 appends "time" LAST; predict.py:91-98 pops it by name, then popitem() is the image to save
+    assert list(out.keys()) == ["adjust", "enhanced", "time"] and out["time"] > 0
+    t = out.pop("time", None)
+    assert t
+    k, v = out.popitem()
     assert k == "enhanced" and v.shape == x.shape
     assert maxerr(v, ref["enhanced"]) <= TIGHT_PP
     assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT_PP
     # resize=True: fixed square model input (image_size), outputs back at the input size
-    out2 = m.infer({"image": x}, image_size=64, resize=True)
+    out2 = m.infer({"image": x.clone()}, image_size=64, resize=True)
+    assert list(out2.keys())[-1] == "time"
     ref2 = O.infer_resize(O.zero_dcepp_forward(O.infer_resize(x, (64, 64)), sd, scale_factor=1)["enhanced"], (H, W))
     assert maxerr(out2["enhanced"], ref2) <= TIGHT_PP
 
@@ -525,3 +553,71 @@ def test_dce_bf16x3_1080p_matches_fp32_mode_and_identity(cuda_dev):
     z = load_into(P.ZeroDCE_RE(precision="bf16x3"), {k: torch.zeros_like(v) for k, v in sd.items()}).to(cuda_dev)
     o = z({"image": x})
     assert torch.equal(o["enhanced"], x) and not o["adjust"].any()
+
+
+# ------------------------------------------------------------------ full-size parity at the BASELINE configs (C2, C3, C4)
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3", "bf16"])
+def test_dce_1080p_frame_vs_oracle(cuda_dev, precision):
+    """C2 frame size against the CPU oracle itself (not mode against mode): fp32 / bf16x3 under the <= 1e-3 contract,
+    bf16 under the PSNR >= 50 dB contract; stress weights so the curve maps are not ~0."""
+    x = O.synthetic_lowlight(1, 1080, 1920, seed=111)
+    sd = O.make_dce_state_dict(43, "stress")
+    ref = O.zero_dce_forward(x, sd)
+    out = load_into(P.ZeroDCE_RE(precision=precision), sd).to(cuda_dev)({"image": x.to(cuda_dev)})
+    if precision == "bf16":
+        p = O.psnr(out["enhanced"].cpu(), ref["enhanced"])
+        emu = O.zero_dce_forward_bf16_operands(x, sd)
+        print(f"bf16 1080p: PSNR vs fp32 oracle = {p:.1f} dB")
+        assert p >= 50.0, p
+        assert maxerr(out["adjust"], emu["adjust"]) <= BF16_EMU_TOL and maxerr(out["enhanced"], emu["enhanced"]) <= BF16_EMU_TOL
+    else:
+        ea, ee = maxerr(out["adjust"], ref["adjust"]), maxerr(out["enhanced"], ref["enhanced"])
+        print(f"{precision} 1080p: max|adjust err| = {ea:.2e}, max|enhanced err| = {ee:.2e}")
+        assert ea <= TOL and ee <= TOL
+        assert ea <= X3_TIGHT and ee <= X3_TIGHT, (ea, ee)
+
+
+@pytest.mark.parametrize("precision", ["bf16", "bf16x3"])
+def test_dce_batch16_1080p_frames_equal_single_frame_runs(cuda_dev, precision):
+    """C2 batch: strip / segment / batch seams of the persistent layer kernels -- frames 0, 7, 15 of a 16-frame batch
+    are bit-identical to the same frame run alone (different work-item numbering, same arithmetic), and a second
+    forward of the batch reproduces the first."""
+    x = O.synthetic_lowlight(16, 1080, 1920, seed=112).to(cuda_dev)
+    sd = O.make_dce_state_dict(47, "stress")
+    m = load_into(P.ZeroDCE_RE(precision=precision), sd).to(cuda_dev)
+    enh = m({"image": x})["enhanced"].clone()
+    assert torch.equal(m({"image": x})["enhanced"], enh)
+    for b in (0, 7, 15):
+        o = m({"image": x[b:b + 1]})
+        assert torch.equal(o["enhanced"], enh[b:b + 1]), b
+    torch.cuda.empty_cache()
+
+
+def test_dcepp_4k_frame_and_batch8_vs_oracle(cuda_dev):
+    """C3: 8 x 3 x 2160 x 3840, scale_factor = 12, against the CPU oracle (all eight frames)."""
+    x = O.synthetic_lowlight(8, 2160, 3840, seed=113)
+    sd = O.make_dcepp_state_dict(53, "stress")
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=12), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    one = m({"image": x[3:4].to(cuda_dev)})
+    assert torch.equal(one["enhanced"], out["enhanced"][3:4]) and torch.equal(one["adjust"], out["adjust"][3:4])
+    for b in range(8):
+        ref = O.zero_dcepp_forward(x[b:b + 1], sd, scale_factor=12)
+        ea, ee = maxerr(out["adjust"][b:b + 1], ref["adjust"]), maxerr(out["enhanced"][b:b + 1], ref["enhanced"])
+        assert ea <= TIGHT_PP and ee <= TIGHT_PP, (b, ea, ee)
+    del out, one
+    torch.cuda.empty_cache()
+
+
+def test_sci_1080p_batch_vs_oracle(cuda_dev):
+    """C4 frame size: every 24 x 32 tile seam and the frame borders of two full 1080p frames against the oracle."""
+    x = O.synthetic_lowlight(2, 1080, 1920, seed=114)
+    sd = O.make_sci_state_dict(59, "stress")
+    illu, r = torch.ops.b200dce.sci_forward(x.to(cuda_dev), P.ops.sci_pack(sd), True)
+    ri, rr = O.sci_forward(x, sd)
+    assert maxerr(illu, ri) <= TIGHT and maxerr(r, rr) <= TOL
+    # 16-frame batch: frames are independent
+    xb = O.synthetic_lowlight(16, 1080, 1920, seed=115).to(cuda_dev)
+    ib, rb = torch.ops.b200dce.sci_forward(xb, P.ops.sci_pack(sd), True)
+    i1, r1 = torch.ops.b200dce.sci_forward(xb[9:10].contiguous(), P.ops.sci_pack(sd), True)
+    assert torch.equal(ib[9:10], i1) and torch.equal(rb[9:10], r1)

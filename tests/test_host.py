@@ -100,6 +100,67 @@ def test_second_registration_is_ignored_unless_replace():
     assert f["a"]["d"] is C and f.models == ["m", "d"]
 
 
+_MON_DROPIN_SCRIPT = r"""
+import importlib.util, sys, types
+from pathlib import Path
+sys.path.insert(0, {root!r})
+_s = importlib.util.spec_from_file_location("_r", {root!r} + "/etss_07_imageenhance_b200/registry.py")
+R = importlib.util.module_from_spec(_s); _s.loader.exec_module(R)   # by path: the package itself is imported below
+ref_factory = Path({ref!r}) / "src/mon/core/factory.py"
+if ref_factory.exists():
+    # the REFERENCE's own ModelFactory (src/mon/core/factory.py:233-436), unmodified; `humps` is not installed, so a
+    # stub with the three spellings it calls stands in for it
+    humps = types.ModuleType("humps")
+    humps.kebabize, humps.pascalize = R.kebabize, R.pascalize
+    humps.depascalize = R.snakeize
+    sys.modules["humps"] = humps
+    spec = importlib.util.spec_from_file_location("ref_factory", str(ref_factory))
+    fac = importlib.util.module_from_spec(spec); spec.loader.exec_module(fac)
+    Factory, kind = fac.ModelFactory, "reference"
+else:
+    Factory, kind = R.ModelFactory, "local"
+mon = types.ModuleType("mon")
+mon.MODELS = Factory("Models")
+sys.modules["mon"] = mon
+
+@mon.MODELS.register(name="zero_dce_re", arch="zero_dce")        # what zero_dce.py:86 / zero_dcepp.py:87 do at import
+class RefZeroDCE: pass
+@mon.MODELS.register(name="zero_dce++_re", arch="zero_dce")
+class RefZeroDCEpp: pass
+class Other: pass
+mon.MODELS.register(name="zero_dce++_re", arch="zero_dce", module=Other)          # no replace: ignored
+assert mon.MODELS["zero_dce"]["zero_dce++_re"] is RefZeroDCEpp
+
+import etss_07_imageenhance_b200 as P                                            # the documented one-liner
+assert P.MON_REGISTERED is True
+assert mon.MODELS["zero_dce"]["zero_dce++_re"] is P.ZeroDCEpp_RE
+assert mon.MODELS["zero_dce"]["zero_dce_re"] is P.ZeroDCE_RE
+m = mon.MODELS.build(config={{"name": "zero_dce++_re", "scale_factor": 12}})       # predict.py:46
+assert type(m) is P.ZeroDCEpp_RE and m.scale_factor == 12 and m.name == "zero_dce++_re"
+assert type(mon.MODELS.build(name="zero_dce_re")) is P.ZeroDCE_RE
+print("ok", kind)
+"""
+
+
+def test_import_registers_the_dropins_into_mon_with_replace():
+    """with `mon` importable, `import etss_07_imageenhance_b200` re-registers the two classes
+    over the reference's entries (factory.py:300-328 ignores a second registration unless replace=True).  Runs in a
+    fresh interpreter with a stub `mon` whose MODELS is the reference's own ModelFactory when /root/reference is
+    there (this container), else the local clone of it."""
+    import subprocess
+    ref = os.environ.get("B200DCE_REFERENCE", "/root/reference")
+    r = subprocess.run([sys.executable, "-c", _MON_DROPIN_SCRIPT.format(root=str(ROOT), ref=ref)],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert r.stdout.strip().startswith("ok")
+    if Path(ref).exists():
+        assert r.stdout.strip() == "ok reference"
+
+
+def test_without_mon_the_import_is_a_no_op():
+    assert P.MON_REGISTERED is False or "mon" in sys.modules
+
+
 # ------------------------------------------------------------------ state_dict contract (SURVEY F6)
 SPA = [f"loss.loss_spa.weight_{d}" for d in ("left", "right", "up", "down")]
 
@@ -135,6 +196,9 @@ def test_zero_dcepp_state_dict_layout_init_and_file_weights(tmp_path):
         assert torch.equal(v, m2.state_dict()[k])
     with pytest.raises(ValueError):
         P.ZeroDCEpp_RE(weights=str(tmp_path / "w.txt"))
+    (tmp_path / "w.onnx").write_bytes(b"\x08\x07")   # accepted suffix (globals.py:709), but not a torch.load-able file
+    with pytest.raises(ValueError, match="ONNX"):
+        P.ZeroDCEpp_RE(weights=str(tmp_path / "w.onnx"))
     up = {k.replace("dw_conv", "depth_conv").replace("pw_conv", "point_conv"): v for k, v in m.state_dict().items()}
     assert set(P.remap_upstream_dcepp_keys(up)) == set(m.state_dict())
 
@@ -211,6 +275,11 @@ def test_fake_impls_give_shapes_without_a_gpu():
         assert adj.shape == (2, 24, 24, 36)
         a = torch.ops.b200dce.dcepp_lowres(x, packed, 12)
         assert a.shape == (2, 3, 2, 3)
+        # the pack ops' fake sizes are the library's own (host-only queries), not literals
+        ws = [torch.empty(1, device="cuda")] * 7
+        assert torch.ops.b200dce.dcepp_pack(ws, ws, ws, ws).shape == (_lib.lib().b200_dcepp_packed_floats(),)
+        for prec in (_lib.PREC_FP32, _lib.PREC_BF16, _lib.PREC_BF16X3):
+            assert torch.ops.b200dce.dce_pack(ws, ws, 8, prec).shape == (_lib.lib().b200_dce_packed_bytes(prec, 8),)
 
 
 # ------------------------------------------------------------------ frame sharding (multi-GPU host logic)

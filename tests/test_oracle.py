@@ -102,3 +102,15 @@ def test_infer_resize_rounds_up_to_multiple_of_32():
     assert torch.equal(O.infer_resize(x[..., :32, :64]), x[..., :32, :64])
     out = O.infer(lambda t: {"adjust": t * 0.5, "enhanced": t.clamp(0, 1)}, x)
     assert out["enhanced"].shape == x.shape and list(out.keys()) == ["adjust", "enhanced"]
+
+
+def test_oracle_u8_wire_matches_reference_golden():
+    """tests/golden/u8_wire.npz = outputs of the reference's own to_image_tensor(normalize=True) /
+    to_image_nparray(denormalize=True); normalisation is a multiply by fl32(1/255), not a division."""
+    from pathlib import Path
+    z = np.load(Path(__file__).resolve().parent / "golden" / "u8_wire.npz")
+    frames, image = torch.from_numpy(z["frames"]), torch.from_numpy(z["image"])
+    f = O.u8hwc_to_f32nchw(frames)
+    assert torch.equal(f, torch.from_numpy(z["f32"]))
+    assert torch.equal(O.f32nchw_to_u8hwc(image), torch.from_numpy(z["u8"]))
+    assert (f != frames.permute(0, 3, 1, 2).float() / 255.0).any()   # the division is a different function
