@@ -224,7 +224,11 @@ class FramePipeline:
             raise ValueError("construct the pipeline with return_adjust=True to receive the curve maps")
         L = lib()
         self.launches = 0
+        # a cached-key compare when nothing changed; picks up load_state_dict() / in-place edits made since the last call
+        packed = self.model.packed_weights()
         cur = torch.cuda.current_stream(self.device)
+        if packed is not self.packed:  # re-packed on the current stream just now: the slot streams come after it
+            self.packed, self._streaming = packed, False
         if not self._streaming:  # work queued on the caller's stream (e.g. the producer of host_in) comes first
             for s in self.slots:
                 s.stream.wait_stream(cur)
@@ -312,6 +316,10 @@ class DceppBatchStream:
         `apply_events` = (start, end) CUDA events recorded around the full-resolution kernel on its stream."""
         L, k = lib(), self._i & 1
         B, H, W = self.B, self.H, self.W
+        packed = self.model.packed_weights()  # cached-key compare; follows load_state_dict() between batches
+        if packed is not self.packed:         # re-packed on the current stream just now
+            self.packed = packed
+            self.s_net.wait_stream(torch.cuda.current_stream(self.device))
         if tuple(x.shape) != (B, 3, H, W) or tuple(enhanced.shape) != (B, 3, H, W):
             raise ValueError(f"expected [{B},3,{H},{W}] tensors")
         with torch.cuda.stream(self.s_net):

@@ -621,3 +621,20 @@ def test_sci_1080p_batch_vs_oracle(cuda_dev):
     ib, rb = torch.ops.b200dce.sci_forward(xb, P.ops.sci_pack(sd), True)
     i1, r1 = torch.ops.b200dce.sci_forward(xb[9:10].contiguous(), P.ops.sci_pack(sd), True)
     assert torch.equal(ib[9:10], i1) and torch.equal(rb[9:10], r1)
+
+
+def test_frame_pipeline_follows_load_state_dict(cuda_dev):
+    """The pipeline re-reads the model's packed weights at every run(): a load_state_dict() between two runs must
+    change the result (it used to keep the weights it was constructed with)."""
+    H, W, N = 48, 72, 4
+    m = load_into(P.ZeroDCEpp_RE(scale_factor=12), O.make_dcepp_state_dict(5, "stress")).to(cuda_dev)
+    pipe = P.FramePipeline(m, frames_per_chunk=2, H=H, W=W, wire="f32", slots=2)
+    hin = O.synthetic_lowlight(N, H, W, seed=13).pin_memory()
+    a, b = torch.zeros_like(hin).pin_memory(), torch.zeros_like(hin).pin_memory()
+    pipe.run(hin, a)
+    sd2 = O.make_dcepp_state_dict(6, "stress")
+    load_into(m, sd2)
+    pipe.run(hin, b)
+    assert not torch.equal(a, b)
+    assert torch.equal(b, m({"image": hin.to(cuda_dev)})["enhanced"].cpu())
+    assert maxerr(b, O.zero_dcepp_forward(hin, sd2, 12)["enhanced"]) <= TIGHT_PP
