@@ -9,6 +9,8 @@
 //   K2  full-resolution pass (the HBM-bound one): reads x once (128-bit), bilinear-upsamples the low-res map
 //       (align_corners=True) from shared memory, applies the 8-iteration curve, writes `enhanced` and
 //       `adjust` once each.  Persistent CTAs, grid = multiple of the SM count.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "dcepp_mma.cuh"
 
@@ -94,8 +96,10 @@ dcepp_layer_kernel(const float* __restrict__ srcA, const float* __restrict__ src
     if (FIRST && sync != nullptr) {
         static_assert(K1_TH == MM_TH && K1_TW == MM_TW, "layer 1 and the net kernel tile the map identically");
         const int tpf = gridDim.x * gridDim.y, tile = (b * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        if (t < 5) sync[MM_FLAG0 + t * (gridDim.z * tpf) + tile] = 0;
-        if (tile == 0 && t == 5) sync[0] = 0;
+        const int flag0 = mm_flag0(gridDim.z);
+        if (t < 5) sync[flag0 + t * (gridDim.z * tpf) + tile] = 0;
+        if (tile == 0)  // counters, abort word, per-SM CTA counts, per-frame "layer 7 done" counts
+            for (int i = t; i < flag0; i += 256) sync[i] = 0;
     }
 
     // weights -> smem  (layout in global == layout in smem, except the 16B alignment gap for CIN=3)
@@ -329,7 +333,7 @@ dcepp_apply_vec4_kernel(const float* __restrict__ x, const float* __restrict__ a
             const int c = rem / w, xx = rem - c * w;
             const Tap ty = tap_align_corners(Y0 + rr, sh, h);
             const float* ap = a_lr + ((size_t)(b * 3 + c) * h) * w + xx;
-            vrow[idx] = ty.w0 * __ldg(ap + (size_t)ty.i0 * w) + ty.w1 * __ldg(ap + (size_t)ty.i1 * w);
+            vrow[idx] = mm_lerp(ty.w0, __ldg(ap + (size_t)ty.i0 * w), ty.w1, __ldg(ap + (size_t)ty.i1 * w));
         }
         __syncthreads();
         for (int it = t; it < n_it; it += 256) {
@@ -351,10 +355,10 @@ dcepp_apply_vec4_kernel(const float* __restrict__ x, const float* __restrict__ a
             for (int c = 0; c < 3; ++c) {
                 const float* vr = vrow + (rr * 3 + c) * w;
                 float4 a;
-                a.x = tx[0].w0 * vr[tx[0].i0] + tx[0].w1 * vr[tx[0].i1];
-                a.y = tx[1].w0 * vr[tx[1].i0] + tx[1].w1 * vr[tx[1].i1];
-                a.z = tx[2].w0 * vr[tx[2].i0] + tx[2].w1 * vr[tx[2].i1];
-                a.w = tx[3].w0 * vr[tx[3].i0] + tx[3].w1 * vr[tx[3].i1];
+                a.x = mm_lerp(tx[0].w0, vr[tx[0].i0], tx[0].w1, vr[tx[0].i1]);
+                a.y = mm_lerp(tx[1].w0, vr[tx[1].i0], tx[1].w1, vr[tx[1].i1]);
+                a.z = mm_lerp(tx[2].w0, vr[tx[2].i0], tx[2].w1, vr[tx[2].i1]);
+                a.w = mm_lerp(tx[3].w0, vr[tx[3].i0], tx[3].w1, vr[tx[3].i1]);
                 float2 y0 = make_float2(v[c].x, v[c].y), y1 = make_float2(v[c].z, v[c].w);
                 const float2 na0 = make_float2(-a.x, -a.y), na1 = make_float2(-a.z, -a.w);
                 for (int i = 0; i < iters; ++i) {
@@ -380,8 +384,8 @@ dcepp_apply_scalar_kernel(const float* __restrict__ x, const float* __restrict__
         const long long bc = r1 / H;
         const Tap ty = tap_align_corners(Y, sh, h), tx = tap_align_corners(X, sw, w);
         const float* ap = a_lr + (size_t)bc * h * w;
-        const float a = tx.w0 * (ty.w0 * ap[(size_t)ty.i0 * w + tx.i0] + ty.w1 * ap[(size_t)ty.i1 * w + tx.i0]) +
-                        tx.w1 * (ty.w0 * ap[(size_t)ty.i0 * w + tx.i1] + ty.w1 * ap[(size_t)ty.i1 * w + tx.i1]);
+        const float a = mm_lerp(tx.w0, mm_lerp(ty.w0, ap[(size_t)ty.i0 * w + tx.i0], ty.w1, ap[(size_t)ty.i1 * w + tx.i0]),
+                                tx.w1, mm_lerp(ty.w0, ap[(size_t)ty.i0 * w + tx.i1], ty.w1, ap[(size_t)ty.i1 * w + tx.i1]));
         float y = x[i];
         for (int k = 0; k < iters; ++k) y = curve_step(y, a);
         enh[i] = y;
@@ -392,6 +396,8 @@ dcepp_apply_scalar_kernel(const float* __restrict__ x, const float* __restrict__
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 // one feature map: [B][16 channel pairs][h][mm_pitch(w)] float2
 static size_t fmap_bytes(int B, int h, int w) { return align_up((size_t)B * 16 * h * mm_pitch(w) * sizeof(float2), 256); }
+// the low-res curve map [B][3][h][pitch], pitch = w rounded up to a multiple of 4 (a tensor map reads it in the fused launch)
+static size_t amap_bytes(int B, int h, int w) { return align_up((size_t)B * 3 * h * ((w + 3) & ~3) * sizeof(float), 256); }
 
 }  // namespace b200
 
@@ -419,22 +425,18 @@ extern "C" size_t b200_dcepp_workspace_bytes(int B, int H, int W, int sf) {
     if (B <= 0 || H <= 0 || W <= 0 || sf <= 0) return 0;
     const size_t h = H / sf, w = W / sf;
     const size_t fmap = fmap_bytes(B, (int)h, (int)w);
-    const size_t amap = align_up((size_t)B * 3 * h * w * sizeof(float), 256);
+    const size_t amap = amap_bytes(B, (int)h, (int)w);
     return 5 * fmap + amap + align_up(mm_sync_words(B, (int)h, (int)w) * sizeof(int), 256);
 }
 
-extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_lr, int B, int H, int W, int sf,
-                                 void* workspace, size_t workspace_bytes, void* stream) {
-    if (!x || !packed || !a_lr || !workspace) return B200_ERR_NULL;
-    if (B <= 0 || H <= 0 || W <= 0 || sf <= 0) return B200_ERR_BAD_SHAPE;
-    if (H % sf != 0 || W % sf != 0) return B200_ERR_BAD_SHAPE;
-    if (B > 65535) return B200_ERR_UNSUPPORTED;
-    if (!aligned16(x) || !aligned16(packed) || !aligned16(a_lr) || !aligned16(workspace)) return B200_ERR_MISALIGNED;
+// Layer 1 launch + the persistent launch for layers 2..7.  With `fuse` != nullptr the full-resolution pass rides in the
+// second launch (blocks of `x` in the tile queue) and writes fuse->enh / fuse->adj.
+static int dcepp_net(const float* x, const float* packed, float* a_lr, int B, int H, int W, int sf, void* workspace,
+                     size_t workspace_bytes, const MmApplyArgs* fuse, cudaStream_t s) {
     const int h = H / sf, w = W / sf;
     const size_t fmap = fmap_bytes(B, h, w);
-    const size_t amap = align_up((size_t)B * 3 * h * w * sizeof(float), 256);
+    const size_t amap = amap_bytes(B, h, w);
     if (workspace_bytes < b200_dcepp_workspace_bytes(B, H, W, sf)) return B200_ERR_WORKSPACE;
-    cudaStream_t s = (cudaStream_t)stream;
     char* ws = (char*)workspace;
     float* x1 = (float*)(ws + 0 * fmap);
     float* x2 = (float*)(ws + 1 * fmap);
@@ -444,6 +446,15 @@ extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_l
     float* x6 = x4;  // x4 is dead once layer 5 has run
     const float sfs = (float)sf;
     int* sync = (int*)(ws + 5 * fmap + amap);
+    MmApplyArgs ap{};
+    if (fuse) ap = *fuse;
+    // debug aid (not part of the ABI): with B200DCE_TRACE=1 and >= 1 MiB of workspace beyond what the call needs, the
+    // fused launch records a per-item timeline there (tools/trace_dcepp.py reads it)
+    if (fuse && getenv("B200DCE_TRACE") && workspace_bytes >= b200_dcepp_workspace_bytes(B, H, W, sf) + (1u << 20)) {
+        ap.trace = (uint32_t*)(ws + b200_dcepp_workspace_bytes(B, H, W, sf));
+        ap.trace_cap = (int)((workspace_bytes - b200_dcepp_workspace_bytes(B, H, W, sf)) / 16);
+        cudaMemsetAsync(ap.trace, 0, 16, s);
+    }
     int rc;
     if ((rc = launch_k1<3, 1, 8, true, false>(x, nullptr, x1, packed + pp_layer_offset(0), B, h, w, H, W, sfs, sync, s)))
         return rc;
@@ -455,8 +466,17 @@ extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_l
         a.wl[l] = mm + mm_offset(l + 1);
     }
     float* maps[5] = {x1, x2, x3, x4, x5};
-    if ((rc = launch_mm_net(a, maps, B, h, w, sync, s))) return rc;
-    return B200_OK;
+    return launch_mm_net(a, ap, x, maps, B, h, w, sync, s);
+}
+
+extern "C" int b200_dcepp_lowres(const float* x, const float* packed, float* a_lr, int B, int H, int W, int sf,
+                                 void* workspace, size_t workspace_bytes, void* stream) {
+    if (!x || !packed || !a_lr || !workspace) return B200_ERR_NULL;
+    if (B <= 0 || H <= 0 || W <= 0 || sf <= 0) return B200_ERR_BAD_SHAPE;
+    if (H % sf != 0 || W % sf != 0) return B200_ERR_BAD_SHAPE;
+    if (B > 65535) return B200_ERR_UNSUPPORTED;
+    if (!aligned16(x) || !aligned16(packed) || !aligned16(a_lr) || !aligned16(workspace)) return B200_ERR_MISALIGNED;
+    return dcepp_net(x, packed, a_lr, B, H, W, sf, workspace, workspace_bytes, nullptr, (cudaStream_t)stream);
 }
 
 extern "C" int b200_dcepp_apply(const float* x, const float* a_lr, float* enhanced, float* adjust, int B, int H, int W,
@@ -507,6 +527,16 @@ extern "C" int b200_dcepp_apply(const float* x, const float* a_lr, float* enhanc
     return launch_status();
 }
 
+// B200DCE_DCEPP_FUSE (read per call; tuning / A-B aid, not part of the ABI): 0 = three launches (layer 1, net, full-
+// resolution pass), 1 / 2 = the full-resolution pass rides in the net launch and 1 / 2 of an SM's two CTAs prefer its
+// blocks over net tiles.  Default 1.
+static int dcepp_fuse_mode() {
+    const char* e = getenv("B200DCE_DCEPP_FUSE");
+    if (!e || !*e) return 1;
+    const int v = atoi(e);
+    return v < 0 ? 0 : (v > 2 ? 2 : v);
+}
+
 extern "C" int b200_dcepp_forward(const float* x, const float* packed, float* enhanced, float* adjust, int B, int H,
                                   int W, int sf, int iters, void* workspace, size_t workspace_bytes, void* stream) {
     if (!x || !packed || !enhanced || !workspace) return B200_ERR_NULL;
@@ -522,6 +552,19 @@ extern "C" int b200_dcepp_forward(const float* x, const float* packed, float* en
         float* a = adjust ? adjust : a_ws;
         if ((rc = b200_dcepp_lowres(x, packed, a, B, H, W, 1, workspace, workspace_bytes, stream))) return rc;
         return b200_curve_shared(x, a, enhanced, B, 3, H, W, iters, stream);
+    }
+    const int mode = dcepp_fuse_mode();
+    if (mode > 0 && B <= 65535 && aligned16(x) && aligned16(packed) && aligned16(enhanced) && aligned16(workspace) &&
+        (!adjust || aligned16(adjust))) {
+        MmApplyArgs ap{};
+        ap.enh = enhanced;
+        ap.adj = adjust;
+        ap.H = H, ap.W = W, ap.iters = iters;
+        ap.sh = H > 1 ? (float)(h - 1) / (float)(H - 1) : 0.f;  // as b200_dcepp_apply
+        ap.sw = W > 1 ? (float)(w - 1) / (float)(W - 1) : 0.f;
+        ap.prefer = mode;
+        if (mm_plan_blocks(ap, B, w))
+            return dcepp_net(x, packed, a_ws, B, H, W, sf, workspace, workspace_bytes, &ap, (cudaStream_t)stream);
     }
     if ((rc = b200_dcepp_lowres(x, packed, a_ws, B, H, W, sf, workspace, workspace_bytes, stream))) return rc;
     return b200_dcepp_apply(x, a_ws, enhanced, adjust, B, H, W, h, w, iters, stream);

@@ -29,9 +29,23 @@
 // critical path.  There is no launch boundary or wave tail between layers.  Deadlock-free: a producer only waits on
 // tiles with smaller numbers, drawn earlier by CTAs that are resident (grid <= one resident wave) and whose consumers
 // never wait on anything but their own producer.
+//
+// Whole forward in one launch (b200_dcepp_forward, scale_factor >= 4).  The full-resolution pass (bilinear upsample,
+// align_corners=True, + the 8-iteration curve; zero_dcepp.py:198-203) is cut into blocks of `br` rows x `bw` pixels
+// x 3 planes of x that fit one ring stage and joins the same queue: a block of frame f becomes runnable when all
+// layer-7 tiles of f have published (per-frame counter, release / acquire), the producer fetches its x values with one
+// cp.async.bulk.tensor (up to four blocks = 92 KB in flight per CTA, so the HBM read stream never depends on
+// registers or occupancy), the consumer warps lerp the low-resolution map straight from L2 (18 scalar loads per
+// 4 pixels x 3 channels), run the curve and store `enhanced` / `adjust` with 128-bit streaming stores.  The net tiles
+// are ordered frame group by frame group (a group = enough frames to give every CTA a tile per layer), so the
+// HBM-bound blocks of early frames run on the same SMs, at the same time, as the FMA / shared-memory-bound tiles of
+// later frames: per SM one CTA prefers blocks (falls back to tiles while no frame is ready), the other prefers tiles
+// (falls back to blocks when the tiles are exhausted).  Nobody ever waits for a block: blocks are claimed by
+// compare-and-swap only once their frame is complete, so the deadlock argument above is unchanged.
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -50,23 +64,37 @@ constexpr int MM_PS = MM_HR * MM_HC;                 // float2 per pair plane of
 constexpr int MM_STAGE_PAIRS = 8;                    // one k16 block
 constexpr int MM_STAGE_BYTES = MM_STAGE_PAIRS * MM_PS * 8;
 constexpr int MM_NS = 4;          // ring slots
-constexpr int MM_THREADS = 288;   // 8 consumer warps + the producer warp
+constexpr int MM_HALF = 288;      // one half of a CTA: 8 consumer warps + the producer warp, own ring and barriers
+constexpr int MM_THREADS = 2 * MM_HALF;  // two independent halves per CTA, one CTA per SM (18 warps are allocated as
+                                         // 20: 96 registers per thread, as with two 9-warp CTAs)
 static_assert(MM_STAGE_BYTES % 128 == 0, "TMA destinations stay 128-byte aligned");
 static_assert(MM_PS % 16 == 4 || MM_PS % 16 == 12, "pair-plane stride keeps the (g, c) 64-bit loads conflict free");
 
-// per-layer packed block (32-bit words): dw [Cin/2][20] | pw bias [32] | frags [KT][NT][32 lanes][4]
+// per-layer packed block (32-bit words): one blob per k16 block (= per stage), shipped into the ring slot behind the
+// stage's feature-map box by a bulk copy, so a CTA holds no resident weights and changes layers for free:
+//   blob kt: dw [8 pairs][20] | frags [NT][32 lanes][4] | pw bias [32]
 //   dw row of pair p: 9 x (tap of channel 2p, tap of channel 2p+1), then (bias 2p, bias 2p+1)
 __host__ __device__ constexpr int mm_cin(int l) { return l <= 3 ? 32 : 64; }  // l = 1..6 (e_conv2..7)
 __host__ __device__ constexpr int mm_nt(int l) { return l == 6 ? 1 : 4; }
-__host__ __device__ constexpr int mm_words(int l) { return mm_cin(l) * 10 + 32 + (mm_cin(l) / 16) * mm_nt(l) * 128; }
+__host__ __device__ constexpr int mm_blob_words(int l) { return 160 + mm_nt(l) * 128 + 32; }
+__host__ __device__ constexpr int mm_words(int l) { return (mm_cin(l) / 16) * mm_blob_words(l); }
 __host__ __device__ constexpr int mm_offset(int l) {
     int o = 0;
     for (int i = 1; i < l; ++i) o += mm_words(i);
     return o;
 }
 constexpr int MM_TOTAL_WORDS = mm_offset(7);
-constexpr int MM_W_WORDS_MAX = mm_words(4);
-constexpr int MM_NET_SMEM = MM_NS * MM_STAGE_BYTES + MM_W_WORDS_MAX * 4 + 2 * MM_NS * 8 + 4 * 16 + 16;
+constexpr int MM_BLOB_BYTES_MAX = mm_blob_words(1) * 4;
+constexpr int MM_SLOT_BYTES = MM_STAGE_BYTES + MM_BLOB_BYTES_MAX;  // feature-map box | weight blob
+static_assert(MM_SLOT_BYTES % 128 == 0 && (mm_blob_words(1) * 4) % 16 == 0 && (mm_blob_words(6) * 4) % 16 == 0,
+              "bulk-copy sizes / TMA destinations");
+constexpr int MM_VCOLS = 64;                      // low-res columns under one block of the full-resolution pass
+constexpr int MM_VROW_FLOATS = 8 * 3 * MM_VCOLS;  // per CTA: [consumer warp][channel][column]
+// ring | full / empty barriers | 4 item descriptors | per-warp strips of the full-resolution pass
+constexpr int MM_HALF_SMEM = MM_NS * MM_SLOT_BYTES + 2 * MM_NS * 8 + 4 * 16 + MM_VROW_FLOATS * 4;
+constexpr int MM_NET_SMEM = 2 * MM_HALF_SMEM;
+static_assert(MM_HALF_SMEM % 128 == 0, "the second half's ring stays 128-byte aligned");
+static_assert(MM_NET_SMEM <= 227 * 1024, "one CTA per SM");
 
 __device__ __forceinline__ uint32_t mm_pack_bf16x2(float lo_elem, float hi_elem) {
     __nv_bfloat162 h = __floats2bfloat162_rn(lo_elem, hi_elem);  // .x (low 16 bits) = lo_elem
@@ -83,29 +111,32 @@ __device__ __forceinline__ void mm_split2(float v0, float v1, uint32_t& hi, uint
 __device__ void mm_pack_layer(int l, const float* dw_w, const float* dw_b, const float* pw_w, const float* pw_b,
                               uint32_t* out) {
     const int cin = mm_cin(l), nt_n = mm_nt(l), cout = l == 6 ? 3 : 32;
-    float* f = reinterpret_cast<float*>(out);
-    for (int i = threadIdx.x; i < cin * 10; i += blockDim.x) {
-        const int p = i / 20, j = i - p * 20;
-        const int tap = j >> 1, ch = 2 * p + (j & 1);
-        f[i] = tap < 9 ? dw_w[ch * 9 + tap] : dw_b[ch];
-    }
-    for (int i = threadIdx.x; i < 32; i += blockDim.x) f[cin * 10 + i] = i < cout ? pw_b[i] : 0.f;
-    uint32_t* fr = out + cin * 10 + 32;
-    const int n_fr = (cin / 16) * nt_n * 128;
-    for (int i = threadIdx.x; i < n_fr; i += blockDim.x) {
-        const int j = i & 3, lane = (i >> 2) & 31, tile = i >> 7;
-        const int kt = tile / nt_n, nt = tile - kt * nt_n;
-        const int g = lane >> 2, c = lane & 3;
-        const int n = nt * 8 + g;
-        const int k0 = kt * 16 + 2 * c + ((j & 1) ? 8 : 0);
-        float w0 = 0.f, w1 = 0.f;
-        if (n < cout) {
-            w0 = pw_w[n * cin + k0];
-            w1 = pw_w[n * cin + k0 + 1];
+    const int bw = mm_blob_words(l), kt_n = cin / 16;
+    for (int i = threadIdx.x; i < kt_n * bw; i += blockDim.x) {
+        const int kt = i / bw, e = i - kt * bw;
+        float* f = reinterpret_cast<float*>(out);
+        if (e < 160) {  // depthwise taps + bias of pairs kt*8 .. kt*8+7
+            const int p = kt * 8 + e / 20, j = e % 20;
+            const int tap = j >> 1, ch = 2 * p + (j & 1);
+            f[i] = tap < 9 ? dw_w[ch * 9 + tap] : dw_b[ch];
+        } else if (e < 160 + nt_n * 128) {  // pointwise B fragments of this k16 block, split {hi, lo}
+            const int fi = e - 160;
+            const int j = fi & 3, lane = (fi >> 2) & 31, nt = fi >> 7;
+            const int g = lane >> 2, c = lane & 3;
+            const int n = nt * 8 + g;
+            const int k0 = kt * 16 + 2 * c + ((j & 1) ? 8 : 0);
+            float w0 = 0.f, w1 = 0.f;
+            if (n < cout) {
+                w0 = pw_w[n * cin + k0];
+                w1 = pw_w[n * cin + k0 + 1];
+            }
+            uint32_t hi, lo;
+            mm_split2(w0, w1, hi, lo);
+            out[i] = j < 2 ? hi : lo;
+        } else {  // pointwise bias (every blob carries it; the tile's first stage is the one that is read)
+            const int o = e - 160 - nt_n * 128;
+            f[i] = o < cout ? pw_b[o] : 0.f;
         }
-        uint32_t hi, lo;
-        mm_split2(w0, w1, hi, lo);
-        fr[i] = j < 2 ? hi : lo;
     }
 }
 
@@ -124,13 +155,19 @@ __device__ __forceinline__ int mm_ld_acquire(const int* p) {
 __device__ __forceinline__ void mm_st_release(int* p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void mm_red_release_add(int* p, int v) {
+    asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
-// sync words (caller's workspace, zeroed by layer 1's launch): [0] = work counter, [MM_FLAG0 + q] = tile q of
-// layers 2..6 published (layer 7 has no consumer in this launch)
-constexpr int MM_FLAG0 = 32;  // flags start one 128-byte line after the counter
+// sync words (caller's workspace, zeroed by layer 1's launch):
+//   [0] tile counter | [1] block counter (full-resolution pass) | [2] abort flag (a spin guard tripped) |
+//   [MM_SMCNT0 + smid % MM_NSMCNT] CTAs that have started on that SM (decides which of the two prefers blocks) |
+//   [MM_FDONE0 + b] layer-7 tiles of frame b published | [mm_flag0(B) + q] tile q of layers 2..6 published
+constexpr int MM_SMCNT0 = 32, MM_NSMCNT = 192, MM_FDONE0 = MM_SMCNT0 + MM_NSMCNT;
+__host__ __device__ inline int mm_flag0(int B) { return (MM_FDONE0 + B + 31) & ~31; }
 __host__ __device__ inline size_t mm_sync_words(int B, int h, int w) {
     const size_t tiles = (size_t)B * ((h + MM_TH - 1) / MM_TH) * ((w + MM_TW - 1) / MM_TW);
-    return MM_FLAG0 + 5 * tiles;
+    return mm_flag0(B) + 5 * tiles;
 }
 __host__ __device__ inline int mm_pitch(int w) { return (w + 1) & ~1; }  // float2 per feature-map row
 
@@ -139,40 +176,99 @@ struct MmNetArgs {
     const uint32_t* wl[6];  // packed blocks of e_conv2..7
 };
 
+// the full-resolution pass as queue items (total == 0: this launch runs the net only)
+struct MmApplyArgs {
+    float* enh;     // [B,3,H,W]
+    float* adj;     // [B,3,H,W] or nullptr
+    int H, W, iters;
+    float sh, sw;   // ATen area_pixel_compute_scale(align_corners=True): (h-1)/(H-1), (w-1)/(W-1)
+    int bw, br;     // block: bw pixels (multiple of 4) x br rows x 3 planes of x ...
+    int ac, ar;     // ... + the ac columns x ar rows x 3 channels of the low-res map under it <= one ring stage
+    int aoff;       // float offset of the low-res tile inside the stage
+    int wq;         // row pitch of the low-res map (floats, multiple of 4: a tensor map reads it)
+    int nbx, nby;   // blocks per row band, bands per frame
+    int total;      // B * nbx * nby
+    int prefer;     // CTAs per SM that prefer blocks over tiles (0..2)
+    int group;      // frames per tile-ordering group
+    uint32_t* trace;  // debug: per-item timeline records {cta << 16 | smid << 4 | kind, t_wait, t_start, t_end} (ns), or nullptr
+    int trace_cap;    // records that fit (record 0 holds the running count)
+};
+__device__ __forceinline__ uint32_t mm_now_ns() {
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return (uint32_t)t;
+}
+
+// Spin guard: every wait of the launch gives up after ~2 s and raises the abort word; once it is up, every wait of
+// every CTA returns at once (checked every 256 spins of a slow path only) and the control flow runs to its normal end
+// on garbage -- a scheduling bug must show up as wrong numbers in a test, never as a hung device.
+constexpr long long MM_SPIN_CLOCKS = 4000000000LL;
+__device__ __forceinline__ bool mm_spin_expired(long long t0, int& n, int* sync) {
+    if ((++n & 255) != 0) return false;
+    if (*reinterpret_cast<volatile int*>(sync + 2)) return true;
+    if (clock64() - t0 < MM_SPIN_CLOCKS) return false;
+    atomicExch(sync + 2, 1);
+    return true;
+}
+__device__ __forceinline__ void mm_mbar_wait(uint64_t* bar, uint32_t parity, int* sync) {
+    if (tc::mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    int n = 0;
+    while (!tc::mbar_try_wait(bar, parity))
+        if (mm_spin_expired(t0, n, sync)) return;
+}
+__device__ __forceinline__ float mm_ld_cg(const float* p) {  // L2 (coherent): data written earlier in this launch
+    float v;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+// w0*v0 + w1*v1 with the contraction spelled out (the unfused full-resolution kernel uses the same helper, so both
+// paths round identically)
+__device__ __forceinline__ float mm_lerp(float w0, float v0, float w1, float v1) {
+    return __fmaf_rn(w0, v0, __fmul_rn(w1, v1));
+}
+
 // One 8 x 32 output tile, executed by the 8 consumer warps.  `ck` = this CTA's running stage counter.
 template <int NSRC, int NT, bool TANH>
-__device__ __forceinline__ void mm_tile(const uint8_t* ring, uint64_t* full, uint64_t* empty, int& ck,
-                                        const float* s_w, float* __restrict__ dst, int h, int w, int wp, int b, int y0,
-                                        int x0) {
+__device__ __forceinline__ void mm_tile(int t, const uint8_t* ring, uint64_t* full, uint64_t* empty, int& ck,
+                                        float* __restrict__ dst, int h, int w, int wp, int b, int y0, int x0,
+                                        int wq = 0) {
     constexpr int CIN = 32 * NSRC, KT = CIN / 16;
-    const float* s_dw = s_w;                                        // [CIN/2][20]
-    const float* s_pb = s_w + CIN * 10;                             // [32]
-    const uint4* s_fr = reinterpret_cast<const uint4*>(s_pb + 32);  // [KT][NT][32]
 
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int lane = t & 31, warp = t >> 5;
     const int g = lane >> 2, c = lane & 3;
     const int wy = (warp >> 2) * 4, wx = (warp & 3) * 8;
 
-    // accumulators start at the pointwise bias: acc[mt][nt] = {(row g, n 2c), (g, 2c+1), (g+8, 2c), (g+8, 2c+1)}
+    // acc[mt][nt] = {(row g, n 2c), (g, 2c+1), (g+8, 2c), (g+8, 2c+1)}; starts at the pointwise bias, read from the
+    // blob of the tile's first stage (which the caller has already waited for)
     float acc[2][NT][4];
+    {
+        const float* s_pb = reinterpret_cast<const float*>(ring + (ck % MM_NS) * MM_SLOT_BYTES + MM_STAGE_BYTES) + 160 +
+                            NT * 128;  // [32]
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt) {
-        const float2 pb = *reinterpret_cast<const float2*>(s_pb + nt * 8 + 2 * c);
+        for (int nt = 0; nt < NT; ++nt) {
+            const float2 pb = *reinterpret_cast<const float2*>(s_pb + nt * 8 + 2 * c);
 #pragma unroll
-        for (int mt = 0; mt < 2; ++mt) acc[mt][nt][0] = acc[mt][nt][2] = pb.x, acc[mt][nt][1] = acc[mt][nt][3] = pb.y;
+            for (int mt = 0; mt < 2; ++mt) acc[mt][nt][0] = acc[mt][nt][2] = pb.x, acc[mt][nt][1] = acc[mt][nt][3] = pb.y;
+        }
     }
 
 #pragma unroll 1
     for (int kt = 0; kt < KT; ++kt) {
         const int slot = ck % MM_NS;
+        // not guarded: once a tile's first stage has landed, the producer issues the others without waiting for
+        // anything but ring slots, i.e. for these consumers
         tc::mbar_wait(&full[slot], (ck / MM_NS) & 1);
-        const float2* st = reinterpret_cast<const float2*>(ring + slot * MM_STAGE_BYTES);
+        const float2* st = reinterpret_cast<const float2*>(ring + slot * MM_SLOT_BYTES);
+        const float* s_dw = reinterpret_cast<const float*>(ring + slot * MM_SLOT_BYTES + MM_STAGE_BYTES);  // [8][20]
+        const uint4* s_fr = reinterpret_cast<const uint4*>(s_dw + 160);                                    // [NT][32]
+
         // ---- depthwise 3x3 for this lane's fragment entries: 2 channel pairs x 4 vertically adjacent pixels ----
         float2 val[2][4];  // [pair c / c+4][output row]
 #pragma unroll
         for (int j2 = 0; j2 < 2; ++j2) {
             const int p = j2 * 4 + c;
-            const float4* wq = reinterpret_cast<const float4*>(s_dw + (kt * 8 + p) * 20);
+            const float4* wq = reinterpret_cast<const float4*>(s_dw + p * 20);
             const float4 q0 = wq[0], q1 = wq[1], q2 = wq[2], q3 = wq[3], q4 = wq[4];
             const float2 wk[9] = {make_float2(q0.x, q0.y), make_float2(q0.z, q0.w), make_float2(q1.x, q1.y),
                                   make_float2(q1.z, q1.w), make_float2(q2.x, q2.y), make_float2(q2.z, q2.w),
@@ -202,10 +298,7 @@ __device__ __forceinline__ void mm_tile(const uint8_t* ring, uint64_t* full, uin
 #pragma unroll
             for (int oo = 0; oo < 4; ++oo) val[j2][oo] = __fadd2_rn(__fadd2_rn(o[oo][0], o[oo][1]), o[oo][2]);
         }
-        __syncwarp();  // every lane's shared loads of this stage have returned
-        if (lane == 0) tc::mbar_arrive(&empty[slot]);
-        ++ck;
-        // ---- A fragments (hi / lo) of the two m-tiles, then 3 MMAs per n-tile ----
+        // ---- A fragments (hi / lo) of the two m-tiles, then 3 MMAs per n-tile (B fragments from the stage's blob) ----
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt) {
             uint32_t ah[4], al[4];
@@ -215,12 +308,15 @@ __device__ __forceinline__ void mm_tile(const uint8_t* ring, uint64_t* full, uin
             mm_split2(val[1][2 * mt + 1].x, val[1][2 * mt + 1].y, ah[3], al[3]);  // row g + 8, k = 2c+8, 2c+9
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
-                const uint4 bf = s_fr[(kt * NT + nt) * 32 + lane];  // {hi b0, hi b1, lo b0, lo b1}
+                const uint4 bf = s_fr[nt * 32 + lane];  // {hi b0, hi b1, lo b0, lo b1}
                 mm_mma_bf16(acc[mt][nt], al, bf.x, bf.y);
                 mm_mma_bf16(acc[mt][nt], ah, bf.z, bf.w);
                 mm_mma_bf16(acc[mt][nt], ah, bf.x, bf.y);
             }
         }
+        __syncwarp();  // every lane's shared loads of this stage (halo box and blob) have returned
+        if (lane == 0) tc::mbar_arrive(&empty[slot]);
+        ++ck;
     }
 
     // ---- epilogue: activation + stores; image row y0 + wy + r = m-tile r / 2, half r % 2 ----
@@ -240,37 +336,154 @@ __device__ __forceinline__ void mm_tile(const uint8_t* ring, uint64_t* full, uin
                     if (r < rows) q[(size_t)r * wp] = u;
                 }
             }
-        } else {  // x_r: planar [B,3,h,w], channels 2c and 2c+1
-            const size_t plane = (size_t)h * w;
-            float* dp = dst + ((size_t)b * 3 + 2 * c) * plane + (size_t)(y0 + wy) * w + xx;
+        } else {  // x_r: planar [B,3,h,wq] (row pitch wq = w for the caller's dense map), channels 2c and 2c+1
+            const size_t plane = (size_t)h * wq;
+            float* dp = dst + ((size_t)b * 3 + 2 * c) * plane + (size_t)(y0 + wy) * wq + xx;
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 if (2 * c + e >= 3) continue;
 #pragma unroll
                 for (int r = 0; r < 4; ++r)
-                    if (r < rows) dp[(size_t)e * plane + (size_t)r * w] = tanhf(acc[r >> 1][0][(r & 1) * 2 + e]);
+                    if (r < rows) dp[(size_t)e * plane + (size_t)r * wq] = tanhf(acc[r >> 1][0][(r & 1) * 2 + e]);
             }
         }
     }
 }
 
-__global__ void __launch_bounds__(MM_THREADS, 2)
-dcepp_net_kernel(const MmNetArgs a, const __grid_constant__ CUtensorMap tm1, const __grid_constant__ CUtensorMap tm2,
-                 const __grid_constant__ CUtensorMap tm3, const __grid_constant__ CUtensorMap tm4,
-                 const __grid_constant__ CUtensorMap tm5, int B, int h, int w, int* __restrict__ sync) {
-    extern __shared__ __align__(128) uint8_t mm_smem[];
-    uint8_t* ring = mm_smem;
-    float* s_w = reinterpret_cast<float*>(mm_smem + MM_NS * MM_STAGE_BYTES);
-    uint64_t* full = reinterpret_cast<uint64_t*>(s_w + MM_W_WORDS_MAX);
-    uint64_t* empty = full + MM_NS;
-    // tile descriptors, producer -> consumers: {tile number q (-1 = end), layer + 8 * frame, y0, x0}
-    volatile int4* s_tq = reinterpret_cast<volatile int4*>(empty + MM_NS);
+// One block of the full-resolution pass, executed by the 8 consumer warps.  The ring slot ck % MM_NS holds, both put
+// there by the producer's bulk tensor copies, br rows x bw pixels x 3 planes of x and the ar x ac x 3 tile of the
+// low-resolution map under them -- the consumers touch shared memory only (no global load, so no L2 round trip on a
+// warp's critical path; with 16 consumer warps per SM there is nothing to hide one behind).  Warp i owns rows i,
+// i + 8, ... of the block, a lane the 4-pixel groups lane, lane + 32 of a row.
+// Upsample = ATen upsample_bilinear2d(align_corners=True), vertical lerp of the two low-res rows first, horizontal
+// second (the order of the unfused kernel): per row, the lanes lerp the <= MM_VCOLS low-res columns under the block
+// vertically into the warp's strip of shared memory (column index clamped at w - 1, so the "+1" neighbour of the last
+// column is itself, as in ATen); a group then needs 2 shared loads per pixel and channel.  The slot goes back to the
+// producer as soon as a warp holds its last x values in registers and has built its last strip.
+template <bool ITERS8>
+__device__ __forceinline__ void mm_curve4(float4& xv, const float4& av, int iters) {
+    // y <- y + a * (y*y - y) (zero_dcepp.py:203), ATen's rounding sequence, two pixels per instruction:
+    // rn(p - y) with p = rn(y*y) is the FFMA2 by -1 (one rounding), then FMUL2, FADD2
+    float2 y0 = make_float2(xv.x, xv.y), y1 = make_float2(xv.z, xv.w);
+    const float2 a0 = make_float2(av.x, av.y), a1 = make_float2(av.z, av.w);
+    const float2 m1 = make_float2(-1.f, -1.f);
+    if (ITERS8) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            y0 = __fadd2_rn(y0, __fmul2_rn(a0, __ffma2_rn(y0, m1, __fmul2_rn(y0, y0))));
+            y1 = __fadd2_rn(y1, __fmul2_rn(a1, __ffma2_rn(y1, m1, __fmul2_rn(y1, y1))));
+        }
+    } else {
+        for (int i = 0; i < iters; ++i) {
+            y0 = __fadd2_rn(y0, __fmul2_rn(a0, __ffma2_rn(y0, m1, __fmul2_rn(y0, y0))));
+            y1 = __fadd2_rn(y1, __fmul2_rn(a1, __ffma2_rn(y1, m1, __fmul2_rn(y1, y1))));
+        }
+    }
+    xv = make_float4(y0.x, y0.y, y1.x, y1.y);
+}
 
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+template <bool ITERS8>
+__device__ __forceinline__ void mm_apply_block(int t, const uint8_t* ring, uint64_t* empty, int& ck,
+                                               const MmApplyArgs& ap, float* s_vrow, int h, int w, int b, int Y0, int X0) {
+    const int lane = t & 31, warp = t >> 5;
+    const int slot = ck % MM_NS;
+    const float* st = reinterpret_cast<const float*>(ring + slot * MM_SLOT_BYTES);
+    const float* sa = st + ap.aoff;  // [3][ar][ac]
+    const int gw = ap.bw >> 2, ps = ap.br * ap.bw, pa = ap.ar * ap.ac;
+    const size_t plane = (size_t)ap.H * ap.W;
+    float* vr = s_vrow + warp * (3 * MM_VCOLS);
+    // low-res columns under this block: cb .. cb + ncol - 1 (the last one is the "+1" neighbour of the last pixel);
+    // the tile in shared memory starts at column cb & ~3 and row yb
+    const int xlast = min(X0 + ap.bw, ap.W) - 1;
+    const int cb = tap_align_corners(X0, ap.sw, w).i0;
+    const int ncol = tap_align_corners(xlast, ap.sw, w).i0 - cb + 2;
+    const int xb = cb & ~3;
+    const int yb = tap_align_corners(Y0, ap.sh, h).i0;
+    const int nrows = min(ap.br, ap.H - Y0);
+    const int rlast = warp + ((nrows - 1 - warp) & ~7);  // this warp's last row (< warp when it has none)
+    const int npass = (gw + 31) >> 5;                    // 1 or 2
+    for (int r = warp; r < nrows; r += 8) {
+        const int Y = Y0 + r;
+        // ---- vertical lerp of the low-res rows under image row Y into the warp's strip ----
+        const Tap ty = tap_align_corners(Y, ap.sh, h);
+        const float* a0 = sa + (ty.i0 - yb) * ap.ac;
+        const float* a1 = sa + (ty.i1 - yb) * ap.ac;
+        __syncwarp();  // the previous row's strip has been read by every lane
+        for (int col = lane; col < ncol; col += 32) {
+            const int cc = min(cb + col, w - 1) - xb;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) vr[c * MM_VCOLS + col] = mm_lerp(ty.w0, a0[c * pa + cc], ty.w1, a1[c * pa + cc]);
+        }
+        __syncwarp();
+        float* erow = ap.enh + (size_t)b * 3 * plane + (size_t)Y * ap.W + X0;
+        float* arow = ap.adj ? ap.adj + (size_t)b * 3 * plane + (size_t)Y * ap.W + X0 : nullptr;
+#pragma unroll 1
+        for (int pss = 0; pss < npass; ++pss) {
+            // ---- x values -> registers; the warp's last pass over the stage releases the slot ----
+            const int c4 = lane + 32 * pss;
+            const int X = X0 + 4 * c4;
+            const bool ok = c4 < gw && X < ap.W;
+            if (!ok) continue;
+            // ---- horizontal lerp + curve + stores ----
+            // tap_align_corners without its clamps: src = rn(sw * X) <= (w - 1)(1 + 2^-23)^2 < w, so the index never
+            // exceeds w - 1 and the weight stays in [0, 1) -- the same bits with 6 instead of 12 instructions a pixel
+            Tap t0, t1, t2, t3;
+            auto tap = [&](Tap& tp, int xo) {
+                const float src = __fmul_rn(ap.sw, (float)(X + xo));
+                tp.i0 = (int)src;
+                tp.w1 = __fsub_rn(src, (float)tp.i0);
+                tp.w0 = __fsub_rn(1.f, tp.w1);
+            };
+            tap(t0, 0), tap(t1, 1), tap(t2, 2), tap(t3, 3);
+            const int d0 = t0.i0 - cb, d1 = t1.i0 - cb, d2 = t2.i0 - cb, d3 = t3.i0 - cb;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float* v = vr + c * MM_VCOLS;
+                float4 xvc = *reinterpret_cast<const float4*>(st + c * ps + r * ap.bw + 4 * c4);
+                float4 av;
+                av.x = mm_lerp(t0.w0, v[d0], t0.w1, v[d0 + 1]);
+                av.y = mm_lerp(t1.w0, v[d1], t1.w1, v[d1 + 1]);
+                av.z = mm_lerp(t2.w0, v[d2], t2.w1, v[d2 + 1]);
+                av.w = mm_lerp(t3.w0, v[d3], t3.w1, v[d3 + 1]);
+                mm_curve4<ITERS8>(xvc, av, ap.iters);
+                st_stream4(erow + c * plane + 4 * c4, xvc);
+                if (arow) st_stream4(arow + c * plane + 4 * c4, av);
+            }
+        }
+    }
+    __syncwarp();  // every lane's shared loads of this stage have returned
+    if (lane == 0) tc::mbar_arrive(&empty[slot]);
+    ++ck;
+}
+
+constexpr int MM_CLAIM = 4;  // blocks of the full-resolution pass claimed per atomic (= ring depth)
+
+// FUSED = false: the net only (b200_dcepp_lowres); without the block path in the consumer loop the tile code keeps
+// all its values in the 96 registers.
+template <bool FUSED, bool TRACE>
+__global__ void __launch_bounds__(MM_THREADS, 1)
+dcepp_net_kernel(const MmNetArgs a, const MmApplyArgs ap, const __grid_constant__ CUtensorMap tm1,
+                 const __grid_constant__ CUtensorMap tm2, const __grid_constant__ CUtensorMap tm3,
+                 const __grid_constant__ CUtensorMap tm4, const __grid_constant__ CUtensorMap tm5,
+                 const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tma, int B, int h, int w,
+                 int* __restrict__ sync) {
+    extern __shared__ __align__(128) uint8_t mm_smem_all[];
+    const int half = threadIdx.x >= MM_HALF ? 1 : 0;  // two independent halves: own ring, barriers, producer
+    uint8_t* mm_smem = mm_smem_all + half * MM_HALF_SMEM;
+    uint8_t* ring = mm_smem;
+    uint64_t* full = reinterpret_cast<uint64_t*>(mm_smem + MM_NS * MM_SLOT_BYTES);
+    uint64_t* empty = full + MM_NS;
+    // item descriptors, producer -> consumers: {item number q (-1 = end), kind + 8 * frame, y0, x0};
+    // kind 0..5 = tile of e_conv2..7, 6 = block of the full-resolution pass
+    volatile int4* s_tq = reinterpret_cast<volatile int4*>(empty + MM_NS);
+    float* s_vrow = reinterpret_cast<float*>(mm_smem + MM_NS * MM_SLOT_BYTES + 2 * MM_NS * 8 + 64);
+
+    const int t = threadIdx.x - half * MM_HALF, lane = t & 31, warp = t >> 5;
     const int ntx = (w + MM_TW - 1) / MM_TW, nty = (h + MM_TH - 1) / MM_TH;
-    const int tpf = ntx * nty, tpl = B * tpf, total = 6 * tpl;
+    const int tpf = ntx * nty, total = 6 * B * tpf;
     const int wp = mm_pitch(w);
-    int* flags = sync + MM_FLAG0;
+    int* flags = sync + mm_flag0(B);
+    const int tpl = B * tpf;  // flags of one layer
 
     if (t == 0) {
         for (int i = 0; i < MM_NS; ++i) {
@@ -289,30 +502,105 @@ dcepp_net_kernel(const MmNetArgs a, const __grid_constant__ CUtensorMap tm1, con
             tc::tma_prefetch_desc(&tm3);
             tc::tma_prefetch_desc(&tm4);
             tc::tma_prefetch_desc(&tm5);
+            if (ap.total > 0) {
+                tc::tma_prefetch_desc(&tmx);
+                tc::tma_prefetch_desc(&tma);
+            }
         }
+        // which of this SM's two halves prefer blocks of the full-resolution pass
+        const bool prefer_blocks = ap.total > 0 && (1 - half) < ap.prefer;
+        const int bpf = ap.nbx * ap.nby;        // blocks per frame
+        const int G = ap.total > 0 ? ap.group : B;  // frames per tile-ordering group (the last group may be short)
+        // Blocks are claimed MM_CLAIM at a time with one atomicAdd, whether or not their frame is complete yet; a claimed
+        // block whose frame is not ready stays pending while this producer goes on with tiles, so nobody ever waits for
+        // a block while tiles are left (and once they are all claimed, their claimers finish them without help).
+        bool tiles_left = true, blocks_left = ap.total > 0;
+        int pend_i = 0, pend_n = 0, ready_frame = -1;
         int pk = 0, tk = 0;
         for (;;) {
-            int q = 0;
-            if (lane == 0) q = atomicAdd(sync, 1);
-            q = __shfl_sync(0xffffffffu, q, 0);
-            if (q >= total) {  // end marker: an empty stage whose tile number is -1
-                const int slot = pk % MM_NS;
-                if (pk >= MM_NS) tc::mbar_wait(&empty[slot], ((pk / MM_NS) - 1) & 1);
-                if (lane == 0) {
-                    s_tq[tk & 3].x = -1;
-                    tc::mbar_arrive(&full[slot]);
+            int q = -1, kind = -1;
+            if ((blocks_left || pend_n > 0) && (prefer_blocks || !tiles_left)) {
+                if (pend_n == 0) {
+                    if (lane == 0) q = atomicAdd(sync + 1, MM_CLAIM);
+                    q = __shfl_sync(0xffffffffu, q, 0);
+                    if (q >= ap.total)
+                        blocks_left = false;
+                    else
+                        pend_i = q, pend_n = min(MM_CLAIM, ap.total - q);
                 }
-                break;
+                if (pend_n > 0) {
+                    const int fb = pend_i / bpf;
+                    if (fb != ready_frame) {
+                        int done = 0;
+                        if (lane == 0) done = mm_ld_acquire(sync + MM_FDONE0 + fb);
+                        done = __shfl_sync(0xffffffffu, done, 0);
+                        if (done >= tpf) ready_frame = fb;
+                    }
+                    if (fb == ready_frame) {
+                        q = pend_i++;
+                        --pend_n;
+                        kind = 6;
+                    }
+                }
             }
-            const int l = q / tpl, r = q - l * tpl;
-            const int b = r / tpf, r2 = r - b * tpf;
+            if (kind < 0 && tiles_left) {
+                if (lane == 0) q = atomicAdd(sync, 1);
+                q = __shfl_sync(0xffffffffu, q, 0);
+                if (q < total)
+                    kind = 0;
+                else
+                    tiles_left = false;
+            }
+            if (kind < 0) {
+                if (!tiles_left && !blocks_left && pend_n == 0) break;
+                if (!tiles_left) {  // the pending blocks belong to a frame whose last tiles are still in flight elsewhere
+                    __nanosleep(256);
+                    if (*reinterpret_cast<volatile int*>(sync + 2)) break;
+                }
+                continue;
+            }
+            if (kind == 6) {
+                // ---- one block of the full-resolution pass: a single stage ----
+                const int b = q / bpf, r = q - b * bpf;
+                const int by = r / ap.nbx, bx = r - by * ap.nbx;
+                const int slot = pk % MM_NS;
+                if (pk >= MM_NS) mm_mbar_wait(&empty[slot], ((pk / MM_NS) - 1) & 1, sync);
+                if (lane == 0) {
+                    volatile int4* d = &s_tq[tk & 3];
+                    d->x = q, d->y = 6 + 8 * b, d->z = by * ap.br, d->w = bx * ap.bw;
+                    // the low-res map of frame b was written through the generic proxy (acquired above)
+                    tc::fence_proxy_async_all();
+                    tc::mbar_arrive_expect_tx(&full[slot], (uint32_t)(12 * (ap.br * ap.bw + ap.ar * ap.ac)));
+                    const uint32_t dst = tc::smem_u32(ring + slot * MM_SLOT_BYTES);
+                    tc::tma_load_3d(dst, &tmx, bx * ap.bw, by * ap.br, 3 * b, &full[slot]);
+                    tc::tma_load_3d(dst + 4 * ap.aoff, &tma, tap_align_corners(bx * ap.bw, ap.sw, w).i0 & ~3,
+                                    tap_align_corners(by * ap.br, ap.sh, h).i0, 3 * b, &full[slot]);
+                }
+                __syncwarp();
+                ++pk;
+                ++tk;
+                continue;
+            }
+            // ---- one tile of the net.  Order: frame group (G frames), layer, frame, tile row, tile column ----
+            const int gsz = 6 * G * tpf;              // tiles of a full group
+            const int grp = q / gsz, rg = q - grp * gsz;
+            const int gfr = min(G, B - grp * G);      // frames of this group
+            const int l = rg / (gfr * tpf), r = rg - l * (gfr * tpf);
+            const int b = grp * G + r / tpf, r2 = r % tpf;
             const int tyi = r2 / ntx, txi = r2 - tyi * ntx;
             if (l > 0) {
                 if (lane < 9) {  // the nine layer l-1 tiles under this tile's halo
                     const int ny = tyi + lane / 3 - 1, nx = txi + lane % 3 - 1;
                     if (ny >= 0 && ny < nty && nx >= 0 && nx < ntx) {
                         const int* f = flags + (size_t)(l - 1) * tpl + b * tpf + ny * ntx + nx;
-                        while (mm_ld_acquire(f) == 0) __nanosleep(32);
+                        if (mm_ld_acquire(f) == 0) {
+                            const long long t0 = clock64();
+                            int n = 0;
+                            while (mm_ld_acquire(f) == 0) {
+                                __nanosleep(32);
+                                if (mm_spin_expired(t0, n, sync)) break;
+                            }
+                        }
                     }
                 }
                 __syncwarp();
@@ -321,55 +609,92 @@ dcepp_net_kernel(const MmNetArgs a, const __grid_constant__ CUtensorMap tm1, con
             const CUtensorMap* mA = l == 0 || l == 5 ? &tm1 : (l == 1 || l == 4 ? &tm2 : &tm3);
             const CUtensorMap* mB = l == 4 ? &tm5 : &tm4;
             const int nst = l < 3 ? 2 : 4;
+            const uint32_t* wl = nullptr;  // selected with constant indices: the kernel parameters stay in the constant
+#pragma unroll                             // bank (a dynamic index would copy them to the stack)
+            for (int i = 0; i < 6; ++i)
+                if (i == l) wl = a.wl[i];
+            const uint32_t blob = (l == 5 ? mm_blob_words(6) : mm_blob_words(1)) * 4;
             for (int i = 0; i < nst; ++i, ++pk) {
                 const int slot = pk % MM_NS;
-                if (pk >= MM_NS) tc::mbar_wait(&empty[slot], ((pk / MM_NS) - 1) & 1);
+                if (pk >= MM_NS) mm_mbar_wait(&empty[slot], ((pk / MM_NS) - 1) & 1, sync);
                 if (lane == 0) {
                     if (i == 0) {
                         volatile int4* d = &s_tq[tk & 3];
-                        d->x = q, d->y = l + 8 * b, d->z = tyi * MM_TH, d->w = txi * MM_TW;
+                        d->x = l * tpl + b * tpf + r2, d->y = l + 8 * b, d->z = tyi * MM_TH, d->w = txi * MM_TW;
                         tc::fence_proxy_async_all();  // the acquired tiles were written through the generic proxy
                     }
-                    tc::mbar_arrive_expect_tx(&full[slot], MM_STAGE_BYTES);
-                    tc::tma_load_3d(tc::smem_u32(ring + slot * MM_STAGE_BYTES), i < 2 ? mA : mB, txi * MM_TW - MM_XOFF,
-                                    tyi * MM_TH - 1, b * 16 + (i & 1) * 8, &full[slot]);
+                    tc::mbar_arrive_expect_tx(&full[slot], MM_STAGE_BYTES + blob);
+                    const uint32_t dst = tc::smem_u32(ring + slot * MM_SLOT_BYTES);
+                    tc::tma_load_3d(dst, i < 2 ? mA : mB, txi * MM_TW - MM_XOFF, tyi * MM_TH - 1, b * 16 + (i & 1) * 8,
+                                    &full[slot]);
+                    tc::bulk_load(dst + MM_STAGE_BYTES, reinterpret_cast<const uint8_t*>(wl) + i * blob, blob, &full[slot]);
                 }
                 __syncwarp();
             }
             ++tk;
         }
+        // end marker: an empty stage whose item number is -1
+        {
+            const int slot = pk % MM_NS;
+            if (pk >= MM_NS) mm_mbar_wait(&empty[slot], ((pk / MM_NS) - 1) & 1, sync);
+            if (lane == 0) {
+                s_tq[tk & 3].x = -1;
+                tc::mbar_arrive(&full[slot]);
+            }
+        }
         return;
     }
 
     // ================= consumer warps =================
-    int ck = 0, tk = 0, cur_l = -1;
+    int ck = 0, tk = 0;
+    uint32_t tr_wait = 0, tr_start = 0, tr_id = 0;
+    const bool tracing = TRACE && t == 0;
+    if (tracing) {
+        uint32_t smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        tr_id = ((2 * blockIdx.x + half) << 16) | ((smid & 0xfff) << 4);
+    }
+    auto trace_item = [&](int kind) {
+        const uint32_t i = atomicAdd(ap.trace, 1u) + 1;
+        if ((int)i < ap.trace_cap)
+            reinterpret_cast<uint4*>(ap.trace)[i] = make_uint4(tr_id | (uint32_t)kind, tr_wait, tr_start, mm_now_ns());
+    };
     for (;;) {
-        tc::mbar_wait(&full[ck % MM_NS], (ck / MM_NS) & 1);  // the tile's first stage (or the end marker)
+        if (tracing) tr_wait = mm_now_ns();
+        mm_mbar_wait(&full[ck % MM_NS], (ck / MM_NS) & 1, sync);  // the item's first stage (or the end marker)
+        if (tracing) tr_start = mm_now_ns();
         const int q = s_tq[tk & 3].x;
         if (q < 0) break;
         const int lb = s_tq[tk & 3].y, y0 = s_tq[tk & 3].z, x0 = s_tq[tk & 3].w;
         const int l = lb & 7, b = lb >> 3;
-        const uint32_t* wl = nullptr;  // selected with constant indices: the kernel parameters stay in the constant
-        float* ds = nullptr;           // bank (a dynamic index would copy them to the stack)
+        if (FUSED && l == 6) {
+            if (ap.iters == 8)
+                mm_apply_block<true>(t, ring, empty, ck, ap, s_vrow, h, w, b, y0, x0);
+            else
+                mm_apply_block<false>(t, ring, empty, ck, ap, s_vrow, h, w, b, y0, x0);
+            ++tk;
+            if (tracing) trace_item(6);
+            continue;
+        }
+        float* ds = nullptr;  // selected with constant indices: the kernel parameters stay in the constant bank
 #pragma unroll
         for (int i = 0; i < 6; ++i)
-            if (i == l) wl = a.wl[i], ds = a.dst[i];
-        if (l != cur_l) {  // every consumer warp is past the previous tile's closing barrier: the old block is dead
-            const int nw4 = (l < 3 ? mm_words(1) : (l < 5 ? mm_words(4) : mm_words(6))) / 4;
-            for (int i = t; i < nw4; i += 256)
-                reinterpret_cast<uint4*>(s_w)[i] = __ldg(reinterpret_cast<const uint4*>(wl) + i);
-            tc::named_bar_sync(1, 256);
-            cur_l = l;
-        }
+            if (i == l) ds = a.dst[i];
         if (l < 3)
-            mm_tile<1, 4, false>(ring, full, empty, ck, s_w, ds, h, w, wp, b, y0, x0);
+            mm_tile<1, 4, false>(t, ring, full, empty, ck, ds, h, w, wp, b, y0, x0);
         else if (l < 5)
-            mm_tile<2, 4, false>(ring, full, empty, ck, s_w, ds, h, w, wp, b, y0, x0);
+            mm_tile<2, 4, false>(t, ring, full, empty, ck, ds, h, w, wp, b, y0, x0);
         else
-            mm_tile<2, 1, true>(ring, full, empty, ck, s_w, ds, h, w, wp, b, y0, x0);
-        tc::named_bar_sync(1, 256);  // all of this tile's stores are issued
-        if (l < 5 && t == 0) mm_st_release(flags + q, 1);
+            mm_tile<2, 1, true>(t, ring, full, empty, ck, ds, h, w, wp, b, y0, x0, ap.total > 0 ? ap.wq : w);
+        tc::named_bar_sync(1 + half, 256);  // all of this tile's stores are issued
+        if (t == 0) {
+            if (l < 5)
+                mm_st_release(flags + q, 1);
+            else if (ap.total > 0)
+                mm_red_release_add(sync + MM_FDONE0 + b, 1);  // one more layer-7 tile of frame b
+        }
         ++tk;
+        if (tracing) trace_item(l);
     }
 }
 
@@ -388,9 +713,67 @@ static int mm_make_map(CUtensorMap* m, const void* base, int B, int h, int w) {
     return r == CUDA_SUCCESS ? B200_OK : B200_ERR_LAUNCH;
 }
 
-// x[0..4] = x1 x2 x3 x4 x5 (x6 reuses x4's buffer)
-static int launch_mm_net(const MmNetArgs& a, float* const* x, int B, int h, int w, int* sync, cudaStream_t s) {
-    auto kern = dcepp_net_kernel;
+// planar fp32 [planes][rows][pitch] as a 3-D tensor (x, y, plane); `cols` <= pitch are the valid columns
+static int mm_make_plane_map(CUtensorMap* m, const void* base, int planes, int rows, int cols, int pitch, int bx,
+                             int by) {
+    tma_encode_fn enc = tma_encoder();
+    if (!enc) return B200_ERR_LAUNCH;
+    const cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)planes};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch * 4, (cuuint64_t)rows * pitch * 4};
+    const cuuint32_t box[3] = {(cuuint32_t)bx, (cuuint32_t)by, 3};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? B200_OK : B200_ERR_LAUNCH;
+}
+
+// Can the full-resolution pass ride in the net launch?  Fills the block geometry of `ap` (H, W, sh, sw set by the
+// caller; w = width of the low-res map).  Needs 128-bit rows (W % 4 == 0), at most MM_VCOLS low-res columns under a
+// block, and a stage that holds the block of x plus the low-res tile under it.
+static bool mm_plan_blocks(MmApplyArgs& ap, int B, int w) {
+    const int H = ap.H, W = ap.W;
+    if ((W & 3) != 0 || W < 4) return false;
+    // widest block: 64 groups of 4 pixels (two passes of a warp) with <= MM_VCOLS low-res columns below
+    int bw_max = 252;
+    if (ap.sw > 0.f) {
+        const long long lim = (long long)((MM_VCOLS - 4) / ap.sw);
+        if (lim < bw_max) bw_max = (int)lim & ~3;
+    }
+    if (bw_max < 4) return false;
+    ap.nbx = (W + bw_max - 1) / bw_max;
+    ap.bw = (((W + ap.nbx - 1) / ap.nbx) + 3) & ~3;
+    if (ap.bw > bw_max) ap.bw = bw_max;
+    // low-res tile: columns cb & ~3 .. i0(last pixel) + 1, rows i0(first row) .. i0(last row) + 1 (safe upper bounds)
+    ap.ac = ((int)(ap.sw * (float)(ap.bw - 1)) + 3 + 3 + 3) & ~3;
+    if (ap.ac > 256) return false;
+    ap.wq = (w + 3) & ~3;
+    auto tile = [&](int br) {
+        ap.br = br;
+        ap.ar = (int)(ap.sh * (float)(br - 1)) + 3;
+        ap.aoff = (br * ap.bw * 3 + 31) & ~31;  // the tile starts 128-byte aligned
+        return ap.ar <= 256 && (ap.aoff + 3 * ap.ar * ap.ac) * 4 <= MM_STAGE_BYTES;
+    };
+    int br = MM_STAGE_BYTES / (12 * ap.bw);
+    if (br > 256) br = 256;
+    if (br > H) br = H;
+    while (br >= 1 && !tile(br)) --br;
+    if (br < 1) return false;
+    if (br > 8 && (br & 7) && tile(br & ~7)) br &= ~7;  // whole rounds of the 8 consumer warps
+    tile(br);
+    ap.nbx = (W + ap.bw - 1) / ap.bw;
+    ap.nby = (H + ap.br - 1) / ap.br;
+    const long long total = (long long)B * ap.nbx * ap.nby;
+    if (total > 0x3fffffffLL) return false;
+    ap.total = (int)total;
+    return true;
+}
+
+// x[0..4] = x1 x2 x3 x4 x5 (x6 reuses x4's buffer); `ap.total` > 0 adds the full-resolution pass over `xin`
+static int launch_mm_net(const MmNetArgs& a, MmApplyArgs ap, const float* xin, float* const* x, int B, int h, int w,
+                         int* sync, cudaStream_t s) {
+    auto kern = ap.total > 0 ? (ap.trace ? dcepp_net_kernel<true, true> : dcepp_net_kernel<true, false>)
+                             : dcepp_net_kernel<false, false>;
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MM_NET_SMEM) != cudaSuccess) {
         (void)cudaGetLastError();
         return B200_ERR_LAUNCH;
@@ -402,16 +785,29 @@ static int launch_mm_net(const MmNetArgs& a, float* const* x, int B, int h, int 
     }
     int dev = 0, sms = B200_NUM_SMS;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    CUtensorMap m[5];
+    CUtensorMap m[7];
     memset(m, 0, sizeof(m));
     for (int i = 0; i < 5; ++i) {
         const int rc = mm_make_map(&m[i], x[i], B, h, w);
         if (rc) return rc;
     }
-    const long long total = 6LL * B * ((h + MM_TH - 1) / MM_TH) * ((w + MM_TW - 1) / MM_TW);
-    long long grid = (long long)sms * occ;
-    if (grid > total) grid = total;
-    kern<<<(unsigned)grid, MM_THREADS, MM_NET_SMEM, s>>>(a, m[0], m[1], m[2], m[3], m[4], B, h, w, sync);
+    const long long tpf = (long long)((h + MM_TH - 1) / MM_TH) * ((w + MM_TW - 1) / MM_TW);
+    const long long total = 6LL * B * tpf + ap.total;
+    long long grid = (long long)sms * occ;  // x 2 halves = workers
+    if (2 * grid > total) grid = (total + 1) / 2;
+    if (ap.total > 0) {
+        int rc = mm_make_plane_map(&m[5], xin, 3 * B, ap.H, ap.W, ap.W, ap.bw, ap.br);
+        if (rc) return rc;
+        if ((rc = mm_make_plane_map(&m[6], a.dst[5], 3 * B, h, w, ap.wq, ap.ac, ap.ar))) return rc;
+        // frames per tile-ordering group: enough tiles per layer that a tile's nine predecessors (claimed one layer =
+        // group * tpf claims earlier) are finished rather than in flight when it is claimed
+        // (measured, 16 x 1080p / 8 x 2160p: ~3.25 tiles per worker and layer is the knee -- smaller groups start the
+        // full-resolution pass earlier but stall producers on predecessors and starve the tile phase of parallelism)
+        long long g = (13 * 2 * grid + 4 * tpf - 1) / (4 * tpf);
+        if (const char* e = getenv("B200DCE_DCEPP_GROUP")) g = atoi(e);  // tuning aid
+        ap.group = (int)(g < 1 ? 1 : (g > B ? B : g));
+    }
+    kern<<<(unsigned)grid, MM_THREADS, MM_NET_SMEM, s>>>(a, ap, m[0], m[1], m[2], m[3], m[4], m[5], m[6], B, h, w, sync);
     return launch_status();
 }
 

@@ -190,6 +190,12 @@ __device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const void* tmap,
         "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
         : "memory");
 }
+// 1-D bulk copy global -> shared (16-byte multiples), completion on an mbarrier (complete_tx::bytes)
+__device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 // 4-D tiled tensor store shared -> global (bulk async group); out-of-bounds parts of the box are clipped
 __device__ __forceinline__ void tma_store_4d(const void* tmap, uint32_t smem_src, int c0, int c1, int c2, int c3) {
     asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3, %4}], [%5];" ::"l"(tmap),
