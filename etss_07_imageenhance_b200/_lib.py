@@ -35,6 +35,8 @@ _SIGNATURES = {
     "b200_dcepp_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_dcepp_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                    c_void_p, c_size_t, c_void_p]),
+    "b200_dcepp_forward_marked": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                          c_void_p, c_size_t, c_void_p, c_void_p]),
     "b200_dcepp_lowres": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_size_t,
                                   c_void_p]),
     "b200_dcepp_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,

@@ -432,7 +432,7 @@ extern "C" size_t b200_dcepp_workspace_bytes(int B, int H, int W, int sf) {
 // Layer 1 launch + the persistent launch for layers 2..7.  With `fuse` != nullptr the full-resolution pass rides in the
 // second launch (blocks of `x` in the tile queue) and writes fuse->enh / fuse->adj.
 static int dcepp_net(const float* x, const float* packed, float* a_lr, int B, int H, int W, int sf, void* workspace,
-                     size_t workspace_bytes, const MmApplyArgs* fuse, cudaStream_t s) {
+                     size_t workspace_bytes, const MmApplyArgs* fuse, cudaStream_t s, cudaEvent_t mid = nullptr) {
     const int h = H / sf, w = W / sf;
     const size_t fmap = fmap_bytes(B, h, w);
     const size_t amap = amap_bytes(B, h, w);
@@ -458,6 +458,7 @@ static int dcepp_net(const float* x, const float* packed, float* a_lr, int B, in
     int rc;
     if ((rc = launch_k1<3, 1, 8, true, false>(x, nullptr, x1, packed + pp_layer_offset(0), B, h, w, H, W, sfs, sync, s)))
         return rc;
+    if (mid != nullptr && cudaEventRecord(mid, s) != cudaSuccess) return B200_ERR_LAUNCH;
     const uint32_t* mm = reinterpret_cast<const uint32_t*>(packed + PP_TOTAL_FLOATS);
     MmNetArgs a;  // e_conv2..7 (zero_dcepp.py:191-196): x2 x3 x4 | cat(x3,x4) -> x5 | cat(x2,x5) -> x6 | cat(x1,x6) -> x_r
     float* ds[6] = {x2, x3, x4, x5, x6, a_lr};
@@ -537,8 +538,8 @@ static int dcepp_fuse_mode() {
     return v < 0 ? 0 : (v > 2 ? 2 : v);
 }
 
-extern "C" int b200_dcepp_forward(const float* x, const float* packed, float* enhanced, float* adjust, int B, int H,
-                                  int W, int sf, int iters, void* workspace, size_t workspace_bytes, void* stream) {
+static int dcepp_forward(const float* x, const float* packed, float* enhanced, float* adjust, int B, int H, int W, int sf,
+                         int iters, void* workspace, size_t workspace_bytes, void* stream, cudaEvent_t mid) {
     if (!x || !packed || !enhanced || !workspace) return B200_ERR_NULL;
     if (B <= 0 || H <= 0 || W <= 0 || sf <= 0 || iters < 0) return B200_ERR_BAD_SHAPE;
     if (H % sf != 0 || W % sf != 0) return B200_ERR_BAD_SHAPE;
@@ -564,8 +565,21 @@ extern "C" int b200_dcepp_forward(const float* x, const float* packed, float* en
         ap.sw = W > 1 ? (float)(w - 1) / (float)(W - 1) : 0.f;
         ap.prefer = mode;
         if (mm_plan_blocks(ap, B, w))
-            return dcepp_net(x, packed, a_ws, B, H, W, sf, workspace, workspace_bytes, &ap, (cudaStream_t)stream);
+            return dcepp_net(x, packed, a_ws, B, H, W, sf, workspace, workspace_bytes, &ap, (cudaStream_t)stream, mid);
     }
     if ((rc = b200_dcepp_lowres(x, packed, a_ws, B, H, W, sf, workspace, workspace_bytes, stream))) return rc;
+    if (mid != nullptr && cudaEventRecord(mid, (cudaStream_t)stream) != cudaSuccess) return B200_ERR_LAUNCH;
     return b200_dcepp_apply(x, a_ws, enhanced, adjust, B, H, W, h, w, iters, stream);
+}
+
+extern "C" int b200_dcepp_forward(const float* x, const float* packed, float* enhanced, float* adjust, int B, int H,
+                                  int W, int sf, int iters, void* workspace, size_t workspace_bytes, void* stream) {
+    return dcepp_forward(x, packed, enhanced, adjust, B, H, W, sf, iters, workspace, workspace_bytes, stream, nullptr);
+}
+
+extern "C" int b200_dcepp_forward_marked(const float* x, const float* packed, float* enhanced, float* adjust, int B,
+                                         int H, int W, int sf, int iters, void* workspace, size_t workspace_bytes,
+                                         void* stream, void* mid_event) {
+    return dcepp_forward(x, packed, enhanced, adjust, B, H, W, sf, iters, workspace, workspace_bytes, stream,
+                         (cudaEvent_t)mid_event);
 }

@@ -179,7 +179,8 @@ class FramePipeline:
 
     # kernels per chunk, for the bench's gpu_launches claim
     def _launches_per_chunk(self, n: int) -> int:
-        k = {"dcepp": 3, "dce": 8 * ((n + 1) // 2) if self.prec == 0 else 8, "sci": 1,
+        fused = self.sf >= 4 and self.W % 4 == 0 and os.environ.get("B200DCE_DCEPP_FUSE", "1") != "0"
+        k = {"dcepp": 2 if fused else 3, "dce": 8 * ((n + 1) // 2) if self.prec == 0 else 8, "sci": 1,
              "ruas": 8 if getattr(self.model, "denoise", False) else 3}[self.kind]
         return k + (2 if self.wire == "u8" else 0)
 
@@ -209,14 +210,18 @@ class FramePipeline:
                   "b200_sci_forward")
 
     def run(self, host_in: torch.Tensor, host_out: torch.Tensor, host_adjust: Optional[torch.Tensor] = None,
-            wait: bool = True) -> None:
+            wait: bool = True, copy_only: bool = False) -> None:
         """Enqueue all chunks of `host_in` (pinned; [N,3,H,W] f32 or [N,H,W,3] u8) and wait for the
         results in `host_out` (pinned, same format).  `host_adjust` (f32 wire only) receives the curve maps.
 
         `wait=False` is the streaming form: the call returns once everything is enqueued, the slot ring keeps turning
         across calls (the first H2D copy of the next batch overlaps the last D2H copies of this one instead of a
         drain / refill of the pipeline at every batch boundary), and the caller owns the hazard on the host buffers:
-        `host_in` must stay untouched and `host_out` unread until `drain()` returns."""
+        `host_in` must stay untouched and `host_out` unread until `drain()` returns.
+
+        `copy_only=True` moves exactly the same bytes through the same slots, streams and chunking but launches no
+        kernel (the device-side result buffers are copied back as they are): the host / PCIe ceiling of this pipeline
+        on this machine, for the bench's "pipeline at x % of the copy-only rate" line."""
         N = host_in.shape[0]
         if not (host_in.is_pinned() and host_out.is_pinned()):
             raise ValueError("FramePipeline.run needs pinned host tensors")
@@ -240,20 +245,23 @@ class FramePipeline:
             with torch.cuda.stream(s.stream):
                 if self.wire == "u8":
                     s.u8_in[:n].copy_(host_in[i0:i0 + n], non_blocking=True)
-                    check(L.b200_u8hwc_to_f32nchw(s.u8_in.data_ptr(), s.x.data_ptr(), n, self.H, self.W,
-                                                  s.stream.cuda_stream), "b200_u8hwc_to_f32nchw")
+                    if not copy_only:
+                        check(L.b200_u8hwc_to_f32nchw(s.u8_in.data_ptr(), s.x.data_ptr(), n, self.H, self.W,
+                                                      s.stream.cuda_stream), "b200_u8hwc_to_f32nchw")
                 else:
                     s.x[:n].copy_(host_in[i0:i0 + n], non_blocking=True)
-                self._launch(s, n)
+                if not copy_only:
+                    self._launch(s, n)
                 if self.wire == "u8":
-                    check(L.b200_f32nchw_to_u8hwc(s.enhanced.data_ptr(), s.u8_out.data_ptr(), n, self.H, self.W,
-                                                  s.stream.cuda_stream), "b200_f32nchw_to_u8hwc")
+                    if not copy_only:
+                        check(L.b200_f32nchw_to_u8hwc(s.enhanced.data_ptr(), s.u8_out.data_ptr(), n, self.H, self.W,
+                                                      s.stream.cuda_stream), "b200_f32nchw_to_u8hwc")
                     host_out[i0:i0 + n].copy_(s.u8_out[:n], non_blocking=True)
                 else:
                     host_out[i0:i0 + n].copy_(s.enhanced[:n], non_blocking=True)
                     if host_adjust is not None:
                         host_adjust[i0:i0 + n].copy_(s.adjust[:n], non_blocking=True)
-            self.launches += self._launches_per_chunk(n)
+            self.launches += 0 if copy_only else self._launches_per_chunk(n)
         if wait:
             self.drain()
 

@@ -90,9 +90,20 @@ size_t b200_dcepp_workspace_bytes(int B, int H, int W, int scale_factor);
  *   a3  bilinear downsample, align_corners=False (zero_dcepp.py:186-188) — fused into layer 1's load
  *   a4  7x [depthwise 3x3 + pointwise 1x1] + ReLU/tanh (zero_dcepp.py:190-196)
  *   a5  bilinear upsample, align_corners=True (upstream model.py:39,80)   \  one fused full-resolution pass:
- *   a6  8-iteration curve (zero_dcepp.py:201-203)                         /  reads x once, writes each output once */
+ *   a6  8-iteration curve (zero_dcepp.py:201-203)                         /  reads x once, writes each output once
+ * Two launches for scale_factor >= 4 and W % 4 == 0 (layer 1; then ONE persistent launch whose work queue holds the
+ * tiles of layers 2..7 and the blocks of the full-resolution pass), three otherwise; both orders of launch give
+ * bit-identical results. */
 int b200_dcepp_forward(const float* x, const float* packed, float* enhanced, float* adjust_or_null, int B, int H, int W,
                        int scale_factor, int iters, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Measurement aid: b200_dcepp_forward, which additionally records the caller's cudaEvent_t `mid_event` (as void*)
+ * on `stream` in front of the forward's LAST launch -- the one that carries the HBM-bound full-resolution pass
+ * (scale_factor >= 4: the persistent launch with layers 2..7 + the full-resolution blocks; otherwise the separate
+ * full-resolution kernel) -- so that launch can be timed with CUDA events for the roofline (bench.py). */
+int b200_dcepp_forward_marked(const float* x, const float* packed, float* enhanced, float* adjust_or_null, int B, int H,
+                              int W, int scale_factor, int iters, void* workspace, size_t workspace_bytes, void* stream,
+                              void* mid_event);
 
 /* Only the low-resolution curve-estimation net (stages a3+a4): writes a_lr
  * [B,3,H/sf,W/sf].  Exposed for tests and for callers that cache the map. */
