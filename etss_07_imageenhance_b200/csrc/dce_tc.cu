@@ -30,6 +30,8 @@
 //                tiles into the smem ring (generic-proxy stores + fence.proxy.async).
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 #include "dce_tc.cuh"
@@ -563,6 +565,408 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Fused layer pair (north_star (1): consecutive layers fused on shared-memory tiles, the map between them never
+// touches HBM).  Layer A = conv3x3(x_a; 32 -> 32) + ReLU, layer B = conv3x3(cat(x_a, A(x_a)); 64 -> 32) + ReLU: with
+// x_a = x3 this is e_conv4 followed by e_conv5 (zero_dce.py:179-180) -- x4 stays on chip and x3 is read once for both.
+//
+// Both layers keep the input-row-stationary form of the per-layer kernel and run as two coupled row pipelines in ONE
+// CTA per SM (all 512 TMEM columns: 8 accumulator blocks per layer):
+//   TMA producer   rows of x_a (130 pixels: a strip yields 126 valid output pixels of layer B, so layer A must
+//                  produce 128 = MMA M pixels, from 130) -> x_a stage ring
+//   MMA issuer A   stage -> accumulator ring A (3 output rows per MMA, as in the per-layer kernel)
+//   epilogue A     TMEM -> bias + ReLU -> bf16 -> the row goes into a ring of shared-memory slots IN THE OPERAND LAYOUT
+//                  (SWIZZLE_64B, one 64-byte row per pixel); rows / pixels outside the image are written as zeros
+//                  (they are layer B's zero padding, not layer A's response to padded input)
+//   MMA issuer B   K = 64: chunks 0-1 from the x_a stage (the same tile layer A read, one pixel further in), chunks 2-3
+//                  from the slot epilogue A filled -> accumulator ring B
+//   epilogue B     TMEM -> bias + ReLU -> bf16 -> staging -> bulk tensor store (126 pixels)
+// A stage of x_a is released by two arrivals (both issuers); a slot of the A-output ring by issuer B's commit.
+// Rows stream down a segment; layer A recomputes 2 rows per segment (42 of 40 + 2 halo rows), nothing else.
+// ------------------------------------------------------------------------------------------------
+constexpr int TP_VALID = TC_M - 2;  // valid layer-B output pixels per strip
+constexpr int TP_NST = 12;          // x_a rows in flight: a stage is held until layer B (4-5 rows behind layer A) has read
+                                    // it too, what is left beyond that lag is the TMA prefetch distance
+constexpr int TP_NM = 4;            // layer-A output rows held on chip
+constexpr int TP_NB = 8;            // accumulator blocks per layer
+constexpr int TP_WA = 3 * 2 * 3072, TP_WB = 3 * 4 * 3072;
+constexpr int TP_EPG = 1;            // epilogue groups of 4 warps per layer (2 = alternating rows: measured slower)
+constexpr int TP_THREADS = (8 * TP_EPG + 3) * 32;  // epilogue A, epilogue B, two MMA issuers, TMA producer
+constexpr int TP_BAR_BYTES = 1024;
+constexpr int TP_HEAD = TP_WA + TP_WB + 256 + TP_BAR_BYTES + 16;
+constexpr int TP_SMEM = TP_HEAD + 1024 + TP_EPG * TC_NOUT * TC_OUT_BYTES + (TP_NM + TP_NST) * TC_SRC_STRIDE;
+static_assert(TP_SMEM <= 227 * 1024, "shared memory budget");
+
+struct TpArgs {
+    __nv_bfloat16* dst;     // layer B output, NHWC bf16 [B,H,W,32]
+    const uint8_t* wpackA;  // packed block of layer A (18 KB of tiles + 32 biases)
+    const uint8_t* wpackB;  // packed block of layer B (36 KB + 32 biases)
+    int B, H, W, R, nseg, nstrip;
+};
+
+__global__ void __launch_bounds__(TP_THREADS, 1)
+dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, const __grid_constant__ CUtensorMap tmo) {
+    constexpr int NB_SH = 3;
+    constexpr int TILE = 3072;
+    constexpr int W_EPB = 4 * TP_EPG, W_MMA_A = 8 * TP_EPG, W_MMA_B = W_MMA_A + 1, W_TMA = W_MMA_A + 2;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* s_wA = smem_raw;
+    uint8_t* s_wB = smem_raw + TP_WA;
+    float* s_biasA = reinterpret_cast<float*>(smem_raw + TP_WA + TP_WB);
+    float* s_biasB = s_biasA + 32;
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(smem_raw + TP_WA + TP_WB + 256);
+    uint64_t* stage_full = s_bar;                  // [NST] TMA complete_tx
+    uint64_t* stage_empty = stage_full + TP_NST;   // [NST] both issuers (2)
+    uint64_t* accA_full = stage_empty + TP_NST;    // [NB]  issuer A commit
+    uint64_t* accA_empty = accA_full + TP_NB;      // [NB]  epilogue A (128)
+    uint64_t* accB_full = accA_empty + TP_NB;      // [NB]  issuer B commit
+    uint64_t* accB_empty = accB_full + TP_NB;      // [NB]  epilogue B (128)
+    uint64_t* mid_full = accB_empty + TP_NB;       // [NM]  epilogue A (128)
+    uint64_t* mid_empty = mid_full + TP_NM;        // [NM]  issuer B commit
+    static_assert((2 * TP_NST + 4 * TP_NB + 2 * TP_NM) * 8 <= TP_BAR_BYTES, "mbarrier area");
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + TP_WA + TP_WB + 256 + TP_BAR_BYTES);
+    const uint32_t out_u32 = (smem_u32(smem_raw + TP_HEAD) + 1023u) & ~1023u;  // swizzle phase = address bits 7-8
+    uint8_t* s_out = smem_raw + (out_u32 - smem_u32(smem_raw));
+    const uint32_t mid_u32 = out_u32 + TP_EPG * TC_NOUT * TC_OUT_BYTES;
+    uint8_t* s_mid = smem_raw + (mid_u32 - smem_u32(smem_raw));
+    const uint32_t stage_u32 = mid_u32 + TP_NM * TC_SRC_STRIDE;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int H = args.H, W = args.W, R = args.R;
+    const int n_items = args.B * args.nseg * args.nstrip;
+
+    // ---- one-time setup ----
+    {
+        const uint4* gA = reinterpret_cast<const uint4*>(args.wpackA);
+        const uint4* gB = reinterpret_cast<const uint4*>(args.wpackB);
+        uint4* sA = reinterpret_cast<uint4*>(s_wA);
+        uint4* sB = reinterpret_cast<uint4*>(s_wB);
+        for (int i = tid; i < TP_WA / 16; i += TP_THREADS) sA[i] = __ldg(gA + i);
+        for (int i = tid; i < TP_WB / 16; i += TP_THREADS) sB[i] = __ldg(gB + i);
+        if (tid < 32) s_biasA[tid] = __ldg(reinterpret_cast<const float*>(args.wpackA + TP_WA) + tid);
+        if (tid >= 32 && tid < 64) s_biasB[tid - 32] = __ldg(reinterpret_cast<const float*>(args.wpackB + TP_WB) + tid - 32);
+        fence_proxy_async_smem();  // B tiles are read through the async proxy
+    }
+    if (warp == W_MMA_A) {
+        if (lane == 0) {
+            for (int i = 0; i < TP_NST; ++i) {
+                mbar_init(&stage_full[i], 1);
+                mbar_init(&stage_empty[i], 2);
+            }
+            for (int i = 0; i < TP_NB; ++i) {
+                mbar_init(&accA_full[i], 1);
+                mbar_init(&accA_empty[i], 128);
+                mbar_init(&accB_full[i], 1);
+                mbar_init(&accB_empty[i], 128);
+            }
+            for (int i = 0; i < TP_NM; ++i) {
+                mbar_init(&mid_full[i], 128);
+                mbar_init(&mid_empty[i], 1);
+            }
+            mbar_fence_init();
+        }
+        __syncwarp();
+        tmem_alloc(s_tmem, 512);
+    }
+    if (warp == W_TMA && lane == 0) {
+        tma_prefetch_desc(&tma);
+        tma_prefetch_desc(&tmo);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tbase = *s_tmem;
+    if (warp < 4) {  // every MMA accumulates: start from zeroed accumulator blocks
+        const uint32_t tl = tbase + ((uint32_t)(warp * 32) << 16);
+        for (int i = 0; i < 2 * TP_NB; ++i) tmem_zero32(tl + i * 32);
+        tc_wait_st();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+
+    // Per item: nB = layer-B output rows, layer A produces nB + 2 rows from nB + 4 rows of x_a.  Running row counters:
+    // ga = x_a rows (stage ring, accumulator ring A), gb = layer-A output rows = layer-B input rows (slot ring,
+    // accumulator ring B).  Accumulator block of a row counter g: NB-1 - g % NB, parity (g / NB) & 1.
+    auto item_geom = [&](int item, int& b, int& y0, int& x0, int& nB) {
+        const int strip = item % args.nstrip;
+        const int seg = (item / args.nstrip) % args.nseg;
+        b = item / (args.nstrip * args.nseg);
+        y0 = seg * R;
+        x0 = strip * TP_VALID;
+        nB = min(R, H - y0);
+    };
+
+    if (warp < W_EPB) {
+        // =========================== EPILOGUE A: accumulator ring A -> on-chip row slots ===========================
+        const int q = warp & 3, par = warp >> 2, m = q * 32 + lane;
+        const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+        float bias[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) bias[i] = s_biasA[i];
+        uint32_t ga = 0, gb = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            const int nA = nB + 2;
+            const int px = x0 - 1 + m;  // image column of this lane's pixel
+            const bool px_ok = px >= 0 && px < W;
+            for (int j = (int)((ga ^ (uint32_t)par) & 1); j < nA + 2; j += TP_EPG) {  // this group's rows: g % 2 == par
+                const uint32_t g = ga + j;
+                const int p = TP_NB - 1 - (int)(g & (TP_NB - 1));
+                mbar_wait_guard(&accA_full[p], (g >> NB_SH) & 1);
+                if (j >= nA) {
+                    mbar_arrive(&accA_empty[p]);
+                    continue;
+                }
+                tc_fence_after();
+                uint32_t v[32];
+                tmem_ld32(tlane + p * 32, v);
+                tc_wait_ld();
+                tmem_zero32(tlane + p * 32);
+                tc_wait_st();
+                tc_fence_before();
+                mbar_arrive(&accA_empty[p]);
+                const int y = y0 - 1 + j;  // image row of this layer-A output row
+                const bool ok = px_ok && y >= 0 && y < H;
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float a0 = ok ? fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f) : 0.f;
+                    const float a1 = ok ? fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f) : 0.f;
+                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
+                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                }
+                const uint32_t gm = gb + j;
+                const int ms = (int)(gm % TP_NM);
+                if (gm >= TP_NM) mbar_wait_guard(&mid_empty[ms], ((gm / TP_NM) - 1) & 1);
+                uint8_t* op = s_mid + ms * TC_SRC_STRIDE + m * 64;
+                const int sw = (m >> 1) & 3;
+                *reinterpret_cast<uint4*>(op + ((0 ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(op + ((1 ^ sw) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
+                *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+                fence_proxy_async_smem();  // read by issuer B's MMAs through the async proxy
+                mbar_arrive(&mid_full[ms]);
+            }
+            ga += nA + 2;
+            gb += nA;
+        }
+    } else if (warp < W_MMA_A) {
+        // =========================== EPILOGUE B: accumulator ring B -> global ===========================
+        const int q = warp & 3, par = (warp - W_EPB) >> 2, m = q * 32 + lane;
+        const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16) + TP_NB * 32;
+        float bias[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) bias[i] = s_biasB[i];
+        uint32_t gb = 0, obuf = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            for (int j = (int)((gb ^ (uint32_t)par) & 1); j < nB + 2; j += TP_EPG) {
+                const uint32_t g = gb + j;
+                const int p = TP_NB - 1 - (int)(g & (TP_NB - 1));
+                mbar_wait_guard(&accB_full[p], (g >> NB_SH) & 1);
+                if (j >= nB) {
+                    mbar_arrive(&accB_empty[p]);
+                    continue;
+                }
+                tc_fence_after();
+                uint32_t v[32];
+                tmem_ld32(tlane + p * 32, v);
+                tc_wait_ld();
+                tmem_zero32(tlane + p * 32);
+                tc_wait_st();
+                tc_fence_before();
+                mbar_arrive(&accB_empty[p]);
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float a0 = fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f);
+                    const float a1 = fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f);
+                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
+                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                }
+                const uint32_t ob = (uint32_t)(par * TC_NOUT + (int)obuf) * TC_OUT_BYTES;
+                uint8_t* op = s_out + ob + m * 64;
+                const int sw = (m >> 1) & 3;
+                *reinterpret_cast<uint4*>(op + ((0 ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(op + ((1 ^ sw) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
+                *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+                fence_proxy_async_smem();
+                named_bar_sync(1 + par, 128);
+                if (q == 0 && lane == 0) {  // the box is TP_VALID pixels: pixels 126 / 127 of the tile are not results
+                    tma_store_4d(&tmo, out_u32 + ob, 0, x0, y0 + j, b);
+                    tma_store_commit();
+                    tma_store_wait_read<0>();
+                }
+                if (++obuf == TC_NOUT) obuf = 0;
+            }
+            gb += nB + 2;
+        }
+    } else if (warp == W_MMA_A) {
+        // =========================== MMA ISSUER A (x_a -> layer A) ===========================
+        constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
+        constexpr uint32_t IDESC_FULL = IDESC0 | ((uint32_t)(96 >> 3) << 17);
+        const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_wA), 128, 256);
+        const uint64_t adesc0 = smem_desc_sw64(stage_u32);
+        const bool leader = elect_one();
+        uint32_t g = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int seg = (item / args.nstrip) % args.nseg;
+            const int nout = min(R, H - seg * R) + 2;  // layer-A output rows
+            const int nin = nout + 2;
+            for (int ri = 0; ri < nin; ++ri, ++g) {
+                const uint32_t st = g % TP_NST;
+                const int pn = TP_NB - 1 - (int)(g & (TP_NB - 1));
+                mbar_wait_guard(&stage_full[st], (g / TP_NST) & 1);
+                if (g >= TP_NB) mbar_wait_guard(&accA_empty[pn], ((g >> NB_SH) & 1) ^ 1);
+                tc_fence_after();
+                const uint64_t adesc = adesc0 + (uint64_t)((st * TC_SRC_STRIDE) >> 4);
+                if (ri >= 2 && ri < nout && pn + 3 <= TP_NB) {
+                    // interior row, no ring wrap: one N = 96 MMA per (dx, kc), offsets are compile-time constants
+                    if (leader) {
+                        const uint32_t d = tbase + pn * 32;
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx)
+#pragma unroll
+                            for (int kc = 0; kc < 2; ++kc)
+                                mma_ss(d, adesc + (uint64_t)((dx * 64 + kc * 32) >> 4),
+                                       bdesc0 + (uint64_t)(((dx * 2 + kc) * TILE) >> 4), IDESC_FULL, 1u);
+                    }
+                } else if (leader) {
+                    int dy = max(0, ri - (nout - 1));
+                    const int dy_hi = min(2, ri);
+                    while (dy <= dy_hi) {  // segment borders / ring wrap: split into groups of output rows
+                        const int p0 = (pn + dy) & (TP_NB - 1);
+                        const int cnt = min(dy_hi - dy + 1, TP_NB - p0);
+                        const uint32_t idesc = cnt == 3 ? IDESC_FULL : (IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17));
+                        const uint32_t d = tbase + p0 * 32;
+                        const uint64_t bd = bdesc0 + (uint64_t)((dy * 1024) >> 4);
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx)
+#pragma unroll
+                            for (int kc = 0; kc < 2; ++kc)
+                                mma_ss(d, adesc + (uint64_t)((dx * 64 + kc * 32) >> 4),
+                                       bd + (uint64_t)(((dx * 2 + kc) * TILE) >> 4), idesc, 1u);
+                        dy += cnt;
+                    }
+                }
+                if (leader) {
+                    tc_commit(&stage_empty[st]);
+                    if (ri >= 2) tc_commit(&accA_full[(pn + 2) & (TP_NB - 1)]);
+                    if (ri >= nout) tc_commit(&accA_full[pn]);  // block unused this lap: complete its phase
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp == W_MMA_B) {
+        // =========================== MMA ISSUER B (cat(x_a, layer A) -> layer B) ===========================
+        constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
+        constexpr uint32_t IDESC_FULL = IDESC0 | ((uint32_t)(96 >> 3) << 17);
+        const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_wB), 128, 256);
+        const uint64_t xdesc0 = smem_desc_sw64(stage_u32);
+        const uint64_t mdesc0 = smem_desc_sw64(mid_u32);
+        const bool leader = elect_one();
+        uint32_t g = 0, ga = 0;  // layer-B input rows; x_a rows at the start of the item
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int seg = (item / args.nstrip) % args.nseg;
+            const int nout = min(R, H - seg * R);  // layer-B output rows
+            const int nin = nout + 2;
+            // x_a rows 0 and nin + 1 of the item feed layer A only: issuer B still owes their stages one arrival each
+            // (as commits, so that they stay ordered behind the commits of earlier rows on the same barriers)
+            if (leader) tc_commit(&stage_empty[ga % TP_NST]);
+            for (int ri = 0; ri < nin; ++ri, ++g) {
+                const uint32_t gx = ga + ri + 1;  // the x_a row under layer-A output row ri
+                const uint32_t st = gx % TP_NST, ms = g % TP_NM;
+                const int pn = TP_NB - 1 - (int)(g & (TP_NB - 1));
+                mbar_wait_guard(&mid_full[ms], (g / TP_NM) & 1);
+                mbar_wait_guard(&stage_full[st], (gx / TP_NST) & 1);
+                if (g >= TP_NB) mbar_wait_guard(&accB_empty[pn], ((g >> NB_SH) & 1) ^ 1);
+                tc_fence_after();
+                const uint64_t xdesc = xdesc0 + (uint64_t)((st * TC_SRC_STRIDE) >> 4);
+                const uint64_t mdesc = mdesc0 + (uint64_t)((ms * TC_SRC_STRIDE) >> 4);
+                // layer-B pixel m = image column x0 + m reads x_a tile row m + 1 + dx (tile column 0 = x0 - 2) and
+                // layer-A slot row m + dx (slot row 0 = x0 - 1)
+                if (ri >= 2 && ri < nout && pn + 3 <= TP_NB) {
+                    if (leader) {
+                        const uint32_t d = tbase + (TP_NB + pn) * 32;
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx) {
+#pragma unroll
+                            for (int kc = 0; kc < 2; ++kc)
+                                mma_ss(d, xdesc + (uint64_t)(((1 + dx) * 64 + kc * 32) >> 4),
+                                       bdesc0 + (uint64_t)(((dx * 4 + kc) * TILE) >> 4), IDESC_FULL, 1u);
+#pragma unroll
+                            for (int kc = 0; kc < 2; ++kc)
+                                mma_ss(d, mdesc + (uint64_t)((dx * 64 + kc * 32) >> 4),
+                                       bdesc0 + (uint64_t)(((dx * 4 + 2 + kc) * TILE) >> 4), IDESC_FULL, 1u);
+                        }
+                    }
+                } else if (leader) {
+                    int dy = max(0, ri - (nout - 1));
+                    const int dy_hi = min(2, ri);
+                    while (dy <= dy_hi) {
+                        const int p0 = (pn + dy) & (TP_NB - 1);
+                        const int cnt = min(dy_hi - dy + 1, TP_NB - p0);
+                        const uint32_t idesc = cnt == 3 ? IDESC_FULL : (IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17));
+                        const uint32_t d = tbase + (TP_NB + p0) * 32;
+                        const uint64_t bd = bdesc0 + (uint64_t)((dy * 1024) >> 4);
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx) {
+#pragma unroll
+                            for (int kc = 0; kc < 2; ++kc)
+                                mma_ss(d, xdesc + (uint64_t)(((1 + dx) * 64 + kc * 32) >> 4),
+                                       bd + (uint64_t)(((dx * 4 + kc) * TILE) >> 4), idesc, 1u);
+#pragma unroll
+                            for (int kc = 0; kc < 2; ++kc)
+                                mma_ss(d, mdesc + (uint64_t)((dx * 64 + kc * 32) >> 4),
+                                       bd + (uint64_t)(((dx * 4 + 2 + kc) * TILE) >> 4), idesc, 1u);
+                        }
+                        dy += cnt;
+                    }
+                }
+                if (leader) {
+                    tc_commit(&stage_empty[st]);
+                    tc_commit(&mid_empty[ms]);
+                    if (ri >= 2) tc_commit(&accB_full[(pn + 2) & (TP_NB - 1)]);
+                    if (ri >= nout) tc_commit(&accB_full[pn]);
+                }
+                __syncwarp();
+            }
+            if (leader) tc_commit(&stage_empty[(ga + nin + 1) % TP_NST]);
+            ga += nin + 2;
+        }
+    } else {
+        // =========================== TMA PRODUCER (rows of x_a) ===========================
+        const bool leader = elect_one();
+        uint32_t g = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            for (int ri = 0; ri < nB + 4; ++ri, ++g) {
+                const uint32_t st = g % TP_NST;
+                if (g >= TP_NST) mbar_wait_guard(&stage_empty[st], ((g / TP_NST) - 1) & 1);
+                if (leader) {
+                    mbar_arrive_expect_tx(&stage_full[st], TC_SRC_BYTES);
+                    tma_load_4d(stage_u32 + st * TC_SRC_STRIDE, &tma, 0, x0 - 2, y0 - 2 + ri, b, &stage_full[st]);
+                }
+                __syncwarp();
+            }
+        }
+    }
+
+    // ---- teardown ----
+    if (warp >= W_EPB && warp < W_MMA_A && (warp & 3) == 0 && lane == 0) tma_store_wait<0>();  // smem outlives the stores
+    tc_fence_before();
+    __syncthreads();
+    if (warp == W_MMA_A) {
+        tc_fence_after();
+        tmem_dealloc(tbase, 512);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
 static size_t tc_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -605,6 +1009,32 @@ static int tc_launch(const TcArgs& a, const void* s0, const void* s1, cudaStream
     const long long slots = (long long)B200_NUM_SMS * tc_ctas<FIRST>();  // persistent CTAs: one resident wave
     const int grid = (int)(items < slots ? items : slots);
     kern<<<grid, tc_threads<FIRST>(), smem, s>>>(a, m0, m1, mo);
+    return launch_status();
+}
+
+// e_conv4 + e_conv5 in one launch: src = x3, dst = x5 (x4 never exists in HBM)
+static int tc_launch_pair(const TcArgs& a, const void* src, __nv_bfloat16* dst, const uint8_t* wA, const uint8_t* wB,
+                          cudaStream_t s) {
+    auto kern = dce_tc_pair_kernel;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return B200_ERR_LAUNCH;
+    }
+    CUtensorMap mi, mo;
+    memset(&mi, 0, sizeof(mi));
+    memset(&mo, 0, sizeof(mo));
+    int rc;
+    if ((rc = tc_make_map(&mi, src, a.B, a.H, a.W))) return rc;
+    if ((rc = tc_make_map(&mo, dst, a.B, a.H, a.W, TP_VALID))) return rc;
+    TpArgs t{};
+    t.dst = dst;
+    t.wpackA = wA;
+    t.wpackB = wB;
+    t.B = a.B, t.H = a.H, t.W = a.W, t.R = a.R, t.nseg = a.nseg;
+    t.nstrip = (a.W + TP_VALID - 1) / TP_VALID;
+    const long long items = (long long)t.B * t.nseg * t.nstrip;
+    const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
+    kern<<<grid, TP_THREADS, TP_SMEM, s>>>(t, mi, mo);
     return launch_status();
 }
 
@@ -665,10 +1095,16 @@ int dce_tc_forward(const float* x, const void* packed, float* adjust, float* enh
     if ((rc = tc_launch<1, false, false>(a, x1, nullptr, s))) return rc;
     layer(2, x3);
     if ((rc = tc_launch<1, false, false>(a, x2, nullptr, s))) return rc;
-    layer(3, x4);
-    if ((rc = tc_launch<1, false, false>(a, x3, nullptr, s))) return rc;
-    layer(4, x5);
-    if ((rc = tc_launch<2, false, false>(a, x3, x4, s))) return rc;
+    // B200DCE_DCE_PAIR=0 (tuning / A-B aid): e_conv4 and e_conv5 as two launches with x4 in HBM
+    const char* pe = getenv("B200DCE_DCE_PAIR");
+    if (pe && pe[0] == '0') {
+        layer(3, x4);
+        if ((rc = tc_launch<1, false, false>(a, x3, nullptr, s))) return rc;
+        layer(4, x5);
+        if ((rc = tc_launch<2, false, false>(a, x3, x4, s))) return rc;
+    } else if ((rc = tc_launch_pair(a, x3, x5, pk + tc_layer_offset(3), pk + tc_layer_offset(4), s))) {
+        return rc;
+    }
     layer(5, x6);
     if ((rc = tc_launch<2, false, false>(a, x2, x5, s))) return rc;
     layer(6, nullptr);
