@@ -17,8 +17,8 @@ LIB_PATH = PKG / "lib" / "libb200dce.so"
 OK = 0
 ERR_NULL, ERR_BAD_SHAPE, ERR_MISALIGNED, ERR_UNSUPPORTED = -1, -2, -3, -4
 ERR_WORKSPACE, ERR_LAUNCH, ERR_NO_DEVICE = -5, -6, -7
-PREC_FP32, PREC_BF16, PREC_BF16X3 = 0, 1, 2
-PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3}
+PREC_FP32, PREC_BF16, PREC_BF16X3, PREC_BF16X3_MMA = 0, 1, 2, 3
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3, "bf16x3_mma": PREC_BF16X3_MMA}
 SCI_PACKED_FLOATS = 252
 RUAS_PACKED_FLOATS = 3438
 

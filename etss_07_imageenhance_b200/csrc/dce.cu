@@ -201,7 +201,7 @@ using namespace b200;
 extern "C" size_t b200_dce_packed_bytes(int precision, int iters) {
     if (iters < 1 || iters > 8) return 0;
     if (precision == B200_PREC_FP32) return (size_t)DCE_F32_TOTAL * sizeof(float);
-    if (precision == B200_PREC_BF16X3) return dce_x3_packed_bytes(iters);
+    if (precision == B200_PREC_BF16X3_MMA) return dce_x3_packed_bytes(iters);
     return dce_tc_packed_bytes(precision, iters);
 }
 
@@ -221,7 +221,7 @@ extern "C" int b200_dce_pack_weights(const float* const* w, const float* const* 
         dce_pack_f32_kernel<<<7, 256, 0, (cudaStream_t)stream>>>(a, (float*)packed, 3 * iters);
         return launch_status();
     }
-    if (precision == B200_PREC_BF16X3) return dce_x3_pack_weights(w, b, packed, iters, (cudaStream_t)stream);
+    if (precision == B200_PREC_BF16X3_MMA) return dce_x3_pack_weights(w, b, packed, iters, (cudaStream_t)stream);
     return dce_tc_pack_weights(w, b, packed, precision, iters, (cudaStream_t)stream);
 }
 
@@ -234,7 +234,7 @@ extern "C" size_t b200_dce_workspace_bytes(int B, int H, int W, int precision) {
         const size_t amap = dce_align_up(fb * 24 * plane * sizeof(float), 256);
         return 5 * fmap + amap;
     }
-    if (precision == B200_PREC_BF16X3) return dce_x3_workspace_bytes(B, H, W);
+    if (precision == B200_PREC_BF16X3_MMA) return dce_x3_workspace_bytes(B, H, W);
     return dce_tc_workspace_bytes(B, H, W, precision);
 }
 
@@ -251,7 +251,7 @@ extern "C" int b200_dce_forward(const float* x, const void* packed, float* adjus
     if (precision == B200_PREC_FP32)
         return dce_forward_f32(x, (const float*)packed, adjust, enhanced, B, H, W, iters, workspace, workspace_bytes,
                                (cudaStream_t)stream);
-    if (precision == B200_PREC_BF16X3)
+    if (precision == B200_PREC_BF16X3_MMA)
         return dce_x3_forward(x, packed, adjust, enhanced, B, H, W, iters, workspace, workspace_bytes,
                               (cudaStream_t)stream);
     return dce_tc_forward(x, packed, adjust, enhanced, B, H, W, iters, precision, workspace, workspace_bytes,

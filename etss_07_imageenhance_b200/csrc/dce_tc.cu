@@ -57,23 +57,32 @@ constexpr int TC_MIN_SMEM = 120 * 1024;            // > half an SM: one CTA per 
 // producer and four epilogue warps: one issuing warp cannot keep the tensor pipe busy (its per-row control flow costs
 // more cycles than the row's MMAs), two interleave.  Layer 1 (one MMA per row, eight A-tile builder warps) keeps one
 // CTA per SM with the whole TMEM.
-template <bool FIRST>
-__host__ __device__ constexpr int tc_ctas() { return FIRST ? 1 : 2; }
-template <bool FIRST>
-__host__ __device__ constexpr int tc_nb() { return FIRST ? 16 : 8; }      // accumulator blocks (32 columns each)
-template <bool FIRST>
-__host__ __device__ constexpr int tc_epg() { return FIRST ? 2 : 1; }      // epilogue groups of 4 warps (alternating rows)
-template <int NSRC, bool FIRST>
+//
+// X3 = the fp32-contract mode on the same machinery (B200_PREC_BF16X3): every activation map is stored as TWO bf16 maps
+// {hi = bf16(v), lo = bf16(v - hi)}, every weight as {hi, lo}, and each product is the 3-term split
+//     a.w ~= a_hi.w_hi + a_lo.w_hi + a_hi.w_lo      (|err| ~ 2^-16, fp32 accumulate in TMEM)
+// i.e. three tcgen05.mma per (dx, 16-channel chunk) into the same accumulator blocks; a stage holds the hi and the lo
+// tile of every source, the epilogue splits its fp32 row and stores two rows.  One CTA per SM (72 KB of weights for
+// the 64-channel layers), whose single issuing warp now has 18 / 36 MMAs per row to amortise its control flow over.
+template <bool FIRST, bool X3>
+__host__ __device__ constexpr int tc_ctas() { return FIRST || X3 ? 1 : 2; }
+template <bool FIRST, bool X3>
+__host__ __device__ constexpr int tc_nb() { return FIRST || X3 ? 16 : 8; }  // accumulator blocks (32 columns each)
+template <int NSRC, bool FIRST, bool LAST, bool X3>
+__host__ __device__ constexpr int tc_epg() {       // epilogue groups of 4 warps (alternating rows)
+    return FIRST ? 2 : (X3 ? (NSRC == 2 && !LAST ? 1 : 2) : 1);
+}
+template <int NSRC, bool FIRST, bool X3>
 __host__ __device__ constexpr int tc_nst() {       // smem stages (input rows in flight) per CTA
-    return FIRST ? 16 : (NSRC == 2 ? 3 : 8);
+    return FIRST ? 16 : (X3 ? (NSRC == 2 ? 3 : 6) : (NSRC == 2 ? 3 : 8));
 }
-template <int NSRC, bool FIRST>
+template <int NSRC, bool FIRST, bool X3>
 __host__ __device__ constexpr int tc_stage_bytes() {
-    return FIRST ? TC_A1_BYTES : NSRC * TC_SRC_STRIDE;
+    return (X3 ? 2 : 1) * (FIRST ? TC_A1_BYTES : NSRC * TC_SRC_STRIDE);
 }
-template <bool FIRST>
-__host__ __device__ constexpr int tc_threads() {
-    return FIRST ? 576 : 192;  // 4 x EPG epilogue warps + MMA + TMA (+ 8 builders)
+template <int NSRC, bool FIRST, bool LAST, bool X3>
+__host__ __device__ constexpr int tc_threads() {   // 4 x EPG epilogue warps + MMA + TMA (+ 8 builders)
+    return (4 * tc_epg<NSRC, FIRST, LAST, X3>() + 2 + (FIRST ? 8 : 0)) * 32;
 }
 
 // packed weights per layer: B tiles then 32 fp32 biases.
@@ -83,25 +92,25 @@ __host__ __device__ constexpr int tc_threads() {
 __host__ __device__ constexpr int tc_kc(int l) { return l == 0 ? 1 : (l <= 3 ? 2 : 4); }
 __host__ __device__ constexpr int tc_ntiles(int l) { return l == 0 ? 1 : 3 * tc_kc(l); }
 __host__ __device__ constexpr int tc_wbytes(int l) { return tc_ntiles(l) * 3072; }
-__host__ __device__ constexpr int tc_layer_bytes(int l) { return tc_wbytes(l) + 128; }
-__host__ __device__ constexpr int tc_layer_offset(int l) {
+__host__ __device__ constexpr int tc_layer_bytes(int l, bool x3 = false) { return (x3 ? 2 : 1) * tc_wbytes(l) + 128; }
+__host__ __device__ constexpr int tc_layer_offset(int l, bool x3 = false) {
     int o = 0;
-    for (int i = 0; i < l; ++i) o += tc_layer_bytes(i);
+    for (int i = 0; i < l; ++i) o += tc_layer_bytes(i, x3);
     return o;
 }
-constexpr int TC_PACKED_BYTES = tc_layer_offset(7);
+constexpr int TC_PACKED_BYTES = tc_layer_offset(7), TC_PACKED_BYTES_X3 = tc_layer_offset(7, true);
 
 struct TcPackArgs {
     const float* w[7];
     const float* b[7];
 };
 
-__global__ void dce_tc_pack_kernel(TcPackArgs a, uint8_t* __restrict__ packed, int cout_last) {
+__global__ void dce_tc_pack_kernel(TcPackArgs a, uint8_t* __restrict__ packed, int cout_last, bool x3) {
     const int l = blockIdx.x;
     const int kc_n = tc_kc(l);
     const int cin = l == 0 ? 3 : (l <= 3 ? 32 : 64);
     const int cout = l == 6 ? cout_last : 32;
-    uint8_t* base = packed + tc_layer_offset(l);
+    uint8_t* base = packed + tc_layer_offset(l, x3);
     __nv_bfloat16* tiles = reinterpret_cast<__nv_bfloat16*>(base);
     const int n_el = tc_ntiles(l) * 1536;
     for (int i = threadIdx.x; i < n_el; i += blockDim.x) {
@@ -117,34 +126,38 @@ __global__ void dce_tc_pack_kernel(TcPackArgs a, uint8_t* __restrict__ packed, i
             const int ci = kc * 16 + kk;
             if (oc < cout && ci < cin) v = a.w[l][(oc * cin + ci) * 9 + dy * 3 + dx];
         }
-        tiles[tile * 1536 + (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7)] = __float2bfloat16_rn(v);
+        const int at = tile * 1536 + (n >> 3) * 128 + (kk >> 3) * 64 + (n & 7) * 8 + (kk & 7);
+        const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+        tiles[at] = hi;
+        if (x3) tiles[n_el + at] = __float2bfloat16_rn(v - __bfloat162float(hi));  // the lo tiles follow the hi tiles
     }
-    float* bias = reinterpret_cast<float*>(base + tc_wbytes(l));
+    float* bias = reinterpret_cast<float*>(base + (x3 ? 2 : 1) * tc_wbytes(l));
     for (int i = threadIdx.x; i < 32; i += blockDim.x) bias[i] = i < cout ? a.b[l][i] : 0.f;
 }
 
 // ------------------------------------------------------------------------------------------------
 struct TcArgs {
     const float* x;        // network input, NCHW fp32 (layer 1 source; layer 7 curve input)
-    __nv_bfloat16* dst;    // NHWC bf16 [B,H,W,32]   (!LAST)
+    __nv_bfloat16* dst;    // NHWC bf16 [B,H,W,32]   (!LAST; X3: the hi map, the lo map has its own tensor map)
     float* adjust;         // LAST: [B,3*iters,H,W] or nullptr
     float* enhanced;       // LAST: [B,3,H,W]
     const uint8_t* wpack;  // this layer's packed block
     int B, H, W, R, nseg, nstrip, iters;
 };
 
-template <int NSRC, bool FIRST>
-__host__ __device__ constexpr int tc_wbytes_t() {
-    return FIRST ? 3072 : 3 * 2 * NSRC * 3072;
+template <int NSRC, bool FIRST, bool X3>
+__host__ __device__ constexpr int tc_wbytes_t() {  // X3: the hi tiles, then the lo tiles
+    return (X3 ? 2 : 1) * (FIRST ? 3072 : 3 * 2 * NSRC * 3072);
 }
-template <int NSRC, bool FIRST, bool LAST>
+template <int NSRC, bool FIRST, bool LAST, bool X3>
 constexpr int tc_smem_bytes() {
-    // weights | bias 128 | barriers | tmem addr 16 | pad to 1024 | output staging (EPG x TC_NOUT tiles) | stages
-    constexpr int need = tc_wbytes_t<NSRC, FIRST>() + 128 + TC_BAR_BYTES + 16 + 1024 +
-                         (LAST ? 0 : tc_epg<FIRST>() * TC_NOUT * TC_OUT_BYTES) +
-                         tc_nst<NSRC, FIRST>() * tc_stage_bytes<NSRC, FIRST>();
-    static_assert(FIRST || need <= TC_SMEM_2CTA, "two CTAs per SM");
-    return FIRST && need < TC_MIN_SMEM ? TC_MIN_SMEM : need;
+    // weights | bias 128 | barriers | tmem addr 16 | pad to 1024 | output staging (EPG x TC_NOUT tiles, x 2 for X3) | stages
+    constexpr int need = tc_wbytes_t<NSRC, FIRST, X3>() + 128 + TC_BAR_BYTES + 16 + 1024 +
+                         (LAST ? 0 : tc_epg<NSRC, FIRST, LAST, X3>() * TC_NOUT * (X3 ? 2 : 1) * TC_OUT_BYTES) +
+                         tc_nst<NSRC, FIRST, X3>() * tc_stage_bytes<NSRC, FIRST, X3>();
+    static_assert(FIRST || X3 || need <= TC_SMEM_2CTA, "two CTAs per SM");
+    static_assert(need <= 227 * 1024, "shared memory budget");
+    return (FIRST || X3) && need < TC_MIN_SMEM ? TC_MIN_SMEM : need;
 }
 
 // flattened (item, row) iterator of one layer-1 builder group: every second input row of this CTA's items
@@ -154,21 +167,27 @@ struct TcRowIt {
     bool valid;
 };
 
-template <int NSRC, bool FIRST, bool LAST>
-__global__ void __launch_bounds__(tc_threads<FIRST>(), tc_ctas<FIRST>())
-dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
-                    const __grid_constant__ CUtensorMap tmo) {
+// the tensor maps of one launch: sources (X3: hi / lo of each) and outputs
+struct TcMaps {
+    CUtensorMap s0, s1, s0lo, s1lo, o, olo;
+};
+
+template <int NSRC, bool FIRST, bool LAST, bool X3>
+__global__ void __launch_bounds__(tc_threads<NSRC, FIRST, LAST, X3>(), tc_ctas<FIRST, X3>())
+dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ TcMaps tm) {
     constexpr int KC = FIRST ? 1 : 2 * NSRC;            // K chunks of 16 per dx
     constexpr int NDY = 3;                              // output rows one input row feeds
     constexpr int NDX = FIRST ? 1 : 3;                  // layer 1 folds dx into K
-    constexpr int NST = tc_nst<NSRC, FIRST>();
-    constexpr int STAGE = tc_stage_bytes<NSRC, FIRST>();
-    constexpr int WBYTES = tc_wbytes_t<NSRC, FIRST>();
+    constexpr int NST = tc_nst<NSRC, FIRST, X3>();
+    constexpr int STAGE = tc_stage_bytes<NSRC, FIRST, X3>();
+    constexpr int WBYTES = tc_wbytes_t<NSRC, FIRST, X3>();
+    constexpr int WHALF = WBYTES / (X3 ? 2 : 1);        // X3: byte offset of the lo tiles
     constexpr int TILE = 3072;
-    constexpr int NTHREADS = tc_threads<FIRST>();
-    constexpr int TC_NB = tc_nb<FIRST>();               // accumulator ring: block NB-1 - g % NB, parity (g / NB) & 1
-    constexpr int NB_SH = FIRST ? 4 : 3;
-    constexpr int EPG = tc_epg<FIRST>();
+    constexpr int NTHREADS = tc_threads<NSRC, FIRST, LAST, X3>();
+    constexpr int TC_NB = tc_nb<FIRST, X3>();           // accumulator ring: block NB-1 - g % NB, parity (g / NB) & 1
+    constexpr int NB_SH = FIRST || X3 ? 4 : 3;
+    constexpr int EPG = tc_epg<NSRC, FIRST, LAST, X3>();
+    constexpr int OUT_TILES = X3 ? 2 : 1;               // staging tiles per output row
     constexpr int W_MMA = 4 * EPG, W_TMA = W_MMA + 1, W_BUILD = W_MMA + 2;  // warp roles
     static_assert((1 << NB_SH) == TC_NB, "accumulator ring is indexed with masks / shifts of the row counter");
     static_assert(!FIRST || (NST & (NST - 1)) == 0, "layer-1 builders index the stage ring with a mask");
@@ -186,7 +205,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
     // stage area: 1024-byte aligned in the shared window (swizzle phase = address bits 7-8)
     const uint32_t out_u32 = (smem_u32(smem_raw + WBYTES + 128 + TC_BAR_BYTES + 16) + 1023u) & ~1023u;
     uint8_t* s_out = smem_raw + (out_u32 - smem_u32(smem_raw));
-    const uint32_t stage_u32 = out_u32 + (LAST ? 0 : EPG * TC_NOUT * TC_OUT_BYTES);
+    const uint32_t stage_u32 = out_u32 + (LAST ? 0 : EPG * TC_NOUT * OUT_TILES * TC_OUT_BYTES);
     uint8_t* s_stage = smem_raw + (stage_u32 - smem_u32(smem_raw));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -216,9 +235,14 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
         tmem_alloc(s_tmem, TC_NB * 32);
     }
     if (warp == W_TMA && lane == 0) {
-        if (!FIRST) tma_prefetch_desc(&tm0);
-        if (NSRC == 2) tma_prefetch_desc(&tm1);
-        if (!LAST) tma_prefetch_desc(&tmo);
+        if (!FIRST) tma_prefetch_desc(&tm.s0);
+        if (NSRC == 2) tma_prefetch_desc(&tm.s1);
+        if (!LAST) tma_prefetch_desc(&tm.o);
+        if (X3) {
+            if (!FIRST) tma_prefetch_desc(&tm.s0lo);
+            if (NSRC == 2) tma_prefetch_desc(&tm.s1lo);
+            if (!LAST) tma_prefetch_desc(&tm.olo);
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -286,25 +310,37 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                     // bias + ReLU -> bf16, staged in the TMA SWIZZLE_64B layout (16-byte chunk c of pixel m at
                     // m*64 + ((c ^ ((m >> 1) & 3)) << 4): conflict-free 128-bit stores), then ONE bulk tensor store
                     // of the [128 px][32 ch] row by an elected lane; columns >= W are clipped by the TMA unit.
-                    uint32_t pk[16];
+                    uint32_t pk[16], pl[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
                         const float a0 = fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f);
                         const float a1 = fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f);
                         __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
                         pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                        if (X3) {  // lo = bf16(v - hi): the next layer multiplies (hi + lo)
+                            __nv_bfloat162 l2 = __floats2bfloat162_rn(a0 - __low2float(h), a1 - __high2float(h));
+                            pl[i] = *reinterpret_cast<uint32_t*>(&l2);
+                        }
                     }
-                    const uint32_t ob = (uint32_t)(par * TC_NOUT + (int)obuf) * TC_OUT_BYTES;
+                    const uint32_t ob = (uint32_t)((par * TC_NOUT + (int)obuf) * OUT_TILES) * TC_OUT_BYTES;
                     uint8_t* op = s_out + ob + m * 64;
                     const int sw = (m >> 1) & 3;
                     *reinterpret_cast<uint4*>(op + ((0 ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     *reinterpret_cast<uint4*>(op + ((1 ^ sw) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                     *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
                     *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+                    if (X3) {
+                        uint8_t* ol = op + TC_OUT_BYTES;
+                        *reinterpret_cast<uint4*>(ol + ((0 ^ sw) << 4)) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+                        *reinterpret_cast<uint4*>(ol + ((1 ^ sw) << 4)) = make_uint4(pl[4], pl[5], pl[6], pl[7]);
+                        *reinterpret_cast<uint4*>(ol + ((2 ^ sw) << 4)) = make_uint4(pl[8], pl[9], pl[10], pl[11]);
+                        *reinterpret_cast<uint4*>(ol + ((3 ^ sw) << 4)) = make_uint4(pl[12], pl[13], pl[14], pl[15]);
+                    }
                     fence_proxy_async_smem();
                     named_bar_sync(1 + par, 128);
                     if (q == 0 && lane == 0) {
-                        tma_store_4d(&tmo, out_u32 + ob, 0, strip * TC_M, y, b);
+                        tma_store_4d(&tm.o, out_u32 + ob, 0, strip * TC_M, y, b);
+                        if (X3) tma_store_4d(&tm.olo, out_u32 + ob + TC_OUT_BYTES, 0, strip * TC_M, y, b);
                         tma_store_commit();
                         // the other tile is written during the next row by threads that only passed THIS row's
                         // barrier, the tile stored now during the row after: this store's read must be over before
@@ -331,7 +367,8 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                         if (i < iters) {
 #pragma unroll
                             for (int c = 0; c < 3; ++c) {
-                                const float a = tanh_approx(__uint_as_float(v[i * 3 + c]) + bias[i * 3 + c]);
+                                const float pre = __uint_as_float(v[i * 3 + c]) + bias[i * 3 + c];
+                                const float a = X3 ? tanhf(pre) : tanh_approx(pre);  // X3 is held to the 1e-3 contract
                                 if (ap) ap[(size_t)(i * 3 + c) * plane] = a;
                                 yv[c] = curve_step(yv[c], a);
                             }
@@ -368,19 +405,28 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                 if (g >= TC_NB) mbar_wait(&acc_empty[pn], ((g >> NB_SH) & 1) ^ 1);
                 tc_fence_after();
                 const uint64_t adesc = adesc0 + (uint64_t)((st * STAGE) >> 4);
-                auto a_of = [&](int dx, int kc) -> uint64_t {  // compile-time offsets after unrolling
-                    return FIRST ? adesc : adesc + (uint64_t)(((kc >> 1) * TC_SRC_STRIDE + dx * 64 + (kc & 1) * 32) >> 4);
+                // tap (dx, kc): A = tile of source kc / 2 (X3: `lo` selects its lo copy, stored behind the hi copies of all
+                // sources), B = weight tile (dx, kc) (X3: `wlo` selects the lo tiles); compile-time offsets after unrolling
+                auto a_of = [&](int dx, int kc, int lo) -> uint64_t {
+                    return FIRST ? adesc + (uint64_t)((lo * TC_A1_BYTES) >> 4)
+                                 : adesc + (uint64_t)(((lo * NSRC + (kc >> 1)) * TC_SRC_STRIDE + dx * 64 + (kc & 1) * 32) >> 4);
+                };
+                auto taps = [&](uint32_t d, uint64_t bd, uint32_t idesc) {
+#pragma unroll
+                    for (int dx = 0; dx < NDX; ++dx)
+#pragma unroll
+                        for (int kc = 0; kc < KC; ++kc) {
+                            const uint64_t bt = bd + (uint64_t)(((dx * KC + kc) * TILE) >> 4);
+                            mma_ss(d, a_of(dx, kc, 0), bt, idesc, 1u);                                     // a_hi . w_hi
+                            if (X3) {
+                                mma_ss(d, a_of(dx, kc, 1), bt, idesc, 1u);                                 // a_lo . w_hi
+                                mma_ss(d, a_of(dx, kc, 0), bt + (uint64_t)(WHALF >> 4), idesc, 1u);        // a_hi . w_lo
+                            }
+                        }
                 };
                 if (ri >= NDY - 1 && ri < nout && pn + NDY <= TC_NB) {
-                    // interior row, no ring wrap: one N = 32*NDY MMA per (dx, kc)
-                    if (leader) {
-                        const uint32_t d = tbase + pn * 32;
-#pragma unroll
-                        for (int dx = 0; dx < NDX; ++dx)
-#pragma unroll
-                            for (int kc = 0; kc < KC; ++kc)
-                                mma_ss(d, a_of(dx, kc), bdesc0 + (uint64_t)(((dx * KC + kc) * TILE) >> 4), IDESC_FULL, 1u);
-                    }
+                    // interior row, no ring wrap: one N = 32*NDY MMA per tap
+                    if (leader) taps(tbase + pn * 32, bdesc0, IDESC_FULL);
                 } else if (leader) {
                     // segment borders (output row j = ri - dy must lie in [0, nout)) and ring wrap: split into groups
                     int dy = max(0, ri - (nout - 1));
@@ -389,13 +435,7 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                         const int p0 = (pn + dy) & (TC_NB - 1);
                         const int cnt = min(dy_hi - dy + 1, TC_NB - p0);
                         const uint32_t idesc = IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17);
-                        const uint32_t d = tbase + p0 * 32;
-                        const uint64_t bd = bdesc0 + (uint64_t)((dy * 1024) >> 4);
-#pragma unroll
-                        for (int dx = 0; dx < NDX; ++dx)
-#pragma unroll
-                            for (int kc = 0; kc < KC; ++kc)
-                                mma_ss(d, a_of(dx, kc), bd + (uint64_t)(((dx * KC + kc) * TILE) >> 4), idesc, 1u);
+                        taps(tbase + p0 * 32, bdesc0 + (uint64_t)((dy * 1024) >> 4), idesc);
                         dy += cnt;
                     }
                 }
@@ -427,11 +467,17 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                 for (int ri = 0; ri < nin; ++ri) {
                     if (!lap0) mbar_wait(&stage_empty[st], sph ^ 1);
                     if (leader) {
-                        mbar_arrive_expect_tx(&stage_full[st], NSRC * TC_SRC_BYTES);
+                        mbar_arrive_expect_tx(&stage_full[st], (X3 ? 2 : 1) * NSRC * TC_SRC_BYTES);
                         const uint32_t dst = stage_u32 + st * STAGE;
-                        tma_load_4d(dst, &tm0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[st]);
+                        tma_load_4d(dst, &tm.s0, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[st]);
                         if (NSRC == 2)
-                            tma_load_4d(dst + TC_SRC_STRIDE, &tm1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[st]);
+                            tma_load_4d(dst + TC_SRC_STRIDE, &tm.s1, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[st]);
+                        if (X3) {  // the lo copies, behind the hi copies of all sources
+                            tma_load_4d(dst + NSRC * TC_SRC_STRIDE, &tm.s0lo, 0, x0 - 1, y0 - 1 + ri, b, &stage_full[st]);
+                            if (NSRC == 2)
+                                tma_load_4d(dst + (NSRC + 1) * TC_SRC_STRIDE, &tm.s1lo, 0, x0 - 1, y0 - 1 + ri, b,
+                                            &stage_full[st]);
+                        }
                     }
                     __syncwarp();
                     if (++st == NST) {
@@ -519,6 +565,19 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ CUtensorMap tm0, 
                         make_uint4(pk(v[0 + j], v[6 + j]), pk(v[12 + j], v[0 + j + 1]), pk(v[6 + j + 1], v[12 + j + 1]),
                                    pk(v[0 + j + 2], v[6 + j + 2]));
                     *reinterpret_cast<uint4*>(tp + j * 16 + 128) = make_uint4(pk(v[12 + j + 2], 0.f), 0u, 0u, 0u);
+                }
+                if (X3) {  // the lo tile (x - bf16(x)) behind the hi tile
+                    float lo[18];
+#pragma unroll
+                    for (int i = 0; i < 18; ++i) lo[i] = v[i] - __bfloat162float(__float2bfloat16_rn(v[i]));
+                    uint8_t* tl = tp + TC_A1_BYTES;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        *reinterpret_cast<uint4*>(tl + j * 16) =
+                            make_uint4(pk(lo[0 + j], lo[6 + j]), pk(lo[12 + j], lo[0 + j + 1]),
+                                       pk(lo[6 + j + 1], lo[12 + j + 1]), pk(lo[0 + j + 2], lo[6 + j + 2]));
+                        *reinterpret_cast<uint4*>(tl + j * 16 + 128) = make_uint4(pk(lo[12 + j + 2], 0.f), 0u, 0u, 0u);
+                    }
                 }
                 fence_proxy_async_smem();
                 mbar_arrive(&stage_full[s]);
@@ -986,29 +1045,39 @@ static int tc_make_map(CUtensorMap* m, const void* base, int B, int H, int W, in
     return r == CUDA_SUCCESS ? B200_OK : B200_ERR_LAUNCH;
 }
 
-template <int NSRC, bool FIRST, bool LAST>
-static int tc_launch(const TcArgs& a, const void* s0, const void* s1, cudaStream_t s) {
-    auto kern = dce_tc_layer_kernel<NSRC, FIRST, LAST>;
-    constexpr int smem = tc_smem_bytes<NSRC, FIRST, LAST>();
-    static_assert(smem <= 227 * 1024, "shared memory budget");
+// one source / destination map pair: hi (or the only) copy, lo copy (X3)
+struct TcPair {
+    const void* hi;
+    const void* lo;
+};
+
+template <int NSRC, bool FIRST, bool LAST, bool X3>
+static int tc_launch(const TcArgs& a, TcPair s0, TcPair s1, TcPair dst, cudaStream_t s) {
+    auto kern = dce_tc_layer_kernel<NSRC, FIRST, LAST, X3>;
+    constexpr int smem = tc_smem_bytes<NSRC, FIRST, LAST, X3>();
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
         (void)cudaGetLastError();
         return B200_ERR_LAUNCH;
     }
-    CUtensorMap m0, m1, mo;
-    memset(&m0, 0, sizeof(m0));
-    memset(&m1, 0, sizeof(m1));
-    memset(&mo, 0, sizeof(mo));
+    TcMaps m;
+    memset(&m, 0, sizeof(m));
     int rc;
     if (!FIRST) {
-        if ((rc = tc_make_map(&m0, s0, a.B, a.H, a.W))) return rc;
-        if (NSRC == 2 && (rc = tc_make_map(&m1, s1, a.B, a.H, a.W))) return rc;
+        if ((rc = tc_make_map(&m.s0, s0.hi, a.B, a.H, a.W))) return rc;
+        if (NSRC == 2 && (rc = tc_make_map(&m.s1, s1.hi, a.B, a.H, a.W))) return rc;
+        if (X3) {
+            if ((rc = tc_make_map(&m.s0lo, s0.lo, a.B, a.H, a.W))) return rc;
+            if (NSRC == 2 && (rc = tc_make_map(&m.s1lo, s1.lo, a.B, a.H, a.W))) return rc;
+        }
     }
-    if (!LAST && (rc = tc_make_map(&mo, a.dst, a.B, a.H, a.W, TC_M))) return rc;  // output row tiles (bulk stores)
+    if (!LAST) {  // output row tiles (bulk stores)
+        if ((rc = tc_make_map(&m.o, dst.hi, a.B, a.H, a.W, TC_M))) return rc;
+        if (X3 && (rc = tc_make_map(&m.olo, dst.lo, a.B, a.H, a.W, TC_M))) return rc;
+    }
     const long long items = (long long)a.B * a.nseg * a.nstrip;
-    const long long slots = (long long)B200_NUM_SMS * tc_ctas<FIRST>();  // persistent CTAs: one resident wave
+    const long long slots = (long long)B200_NUM_SMS * tc_ctas<FIRST, X3>();  // persistent CTAs: one resident wave
     const int grid = (int)(items < slots ? items : slots);
-    kern<<<grid, tc_threads<FIRST>(), smem, s>>>(a, m0, m1, mo);
+    kern<<<grid, tc_threads<NSRC, FIRST, LAST, X3>(), smem, s>>>(a, m);
     return launch_status();
 }
 
@@ -1039,40 +1108,38 @@ static int tc_launch_pair(const TcArgs& a, const void* src, __nv_bfloat16* dst, 
 }
 
 size_t dce_tc_packed_bytes(int precision, int iters) {
-    if (precision != B200_PREC_BF16 || iters < 1 || iters > 8) return 0;
-    return (size_t)TC_PACKED_BYTES;
+    if (iters < 1 || iters > 8) return 0;
+    if (precision == B200_PREC_BF16) return (size_t)TC_PACKED_BYTES;
+    if (precision == B200_PREC_BF16X3) return (size_t)TC_PACKED_BYTES_X3;
+    return 0;
 }
 
 int dce_tc_pack_weights(const float* const* w, const float* const* b, void* packed, int precision, int iters,
                         cudaStream_t s) {
-    if (precision != B200_PREC_BF16) return B200_ERR_UNSUPPORTED;
+    if (precision != B200_PREC_BF16 && precision != B200_PREC_BF16X3) return B200_ERR_UNSUPPORTED;
     TcPackArgs a;
     for (int l = 0; l < 7; ++l) {
         a.w[l] = w[l];
         a.b[l] = b[l];
     }
-    dce_tc_pack_kernel<<<7, 256, 0, s>>>(a, (uint8_t*)packed, 3 * iters);
+    dce_tc_pack_kernel<<<7, 256, 0, s>>>(a, (uint8_t*)packed, 3 * iters, precision == B200_PREC_BF16X3);
     return launch_status();
 }
 
-// 5 NHWC bf16 feature maps [B,H,W,32] (x4's buffer is reused for x6)
+// 5 NHWC bf16 feature maps [B,H,W,32] (x4's buffer is reused for x6); BF16X3: a hi and a lo copy of each
 size_t dce_tc_workspace_bytes(int B, int H, int W, int precision) {
-    if (precision != B200_PREC_BF16) return 0;
-    return 5 * tc_align_up((size_t)B * H * W * 64, 256);
+    if (precision != B200_PREC_BF16 && precision != B200_PREC_BF16X3) return 0;
+    return (precision == B200_PREC_BF16X3 ? 10 : 5) * tc_align_up((size_t)B * H * W * 64, 256);
 }
 
-int dce_tc_forward(const float* x, const void* packed, float* adjust, float* enhanced, int B, int H, int W, int iters,
-                   int precision, void* workspace, size_t workspace_bytes, cudaStream_t s) {
-    if (precision != B200_PREC_BF16) return B200_ERR_UNSUPPORTED;
+template <bool X3>
+static int dce_tc_forward_t(const float* x, const void* packed, float* adjust, float* enhanced, int B, int H, int W,
+                            int iters, void* workspace, size_t workspace_bytes, cudaStream_t s) {
     const size_t fmap = tc_align_up((size_t)B * H * W * 64, 256);
-    if (workspace_bytes < 5 * fmap) return B200_ERR_WORKSPACE;
+    if (workspace_bytes < (X3 ? 10 : 5) * fmap) return B200_ERR_WORKSPACE;
     uint8_t* ws = (uint8_t*)workspace;
-    __nv_bfloat16* x1 = (__nv_bfloat16*)(ws + 0 * fmap);
-    __nv_bfloat16* x2 = (__nv_bfloat16*)(ws + 1 * fmap);
-    __nv_bfloat16* x3 = (__nv_bfloat16*)(ws + 2 * fmap);
-    __nv_bfloat16* x4 = (__nv_bfloat16*)(ws + 3 * fmap);
-    __nv_bfloat16* x5 = (__nv_bfloat16*)(ws + 4 * fmap);
-    __nv_bfloat16* x6 = x4;
+    auto map = [&](int i) { return TcPair{ws + (size_t)i * fmap, X3 ? ws + (size_t)(5 + i) * fmap : nullptr}; };
+    const TcPair x1 = map(0), x2 = map(1), x3 = map(2), x4 = map(3), x5 = map(4), x6 = x4, none{nullptr, nullptr};
     const uint8_t* pk = (const uint8_t*)packed;
 
     TcArgs a{};
@@ -1085,33 +1152,42 @@ int dce_tc_forward(const float* x, const void* packed, float* adjust, float* enh
     a.nseg = (H + a.R - 1) / a.R;
     a.nstrip = (W + TC_M - 1) / TC_M;
     int rc;
-    auto layer = [&](int l, __nv_bfloat16* dst) {
-        a.dst = dst;
-        a.wpack = pk + tc_layer_offset(l);
+    auto layer = [&](int l, TcPair dst) {
+        a.dst = (__nv_bfloat16*)dst.hi;
+        a.wpack = pk + tc_layer_offset(l, X3);
     };
     layer(0, x1);
-    if ((rc = tc_launch<1, true, false>(a, nullptr, nullptr, s))) return rc;
+    if ((rc = tc_launch<1, true, false, X3>(a, none, none, x1, s))) return rc;
     layer(1, x2);
-    if ((rc = tc_launch<1, false, false>(a, x1, nullptr, s))) return rc;
+    if ((rc = tc_launch<1, false, false, X3>(a, x1, none, x2, s))) return rc;
     layer(2, x3);
-    if ((rc = tc_launch<1, false, false>(a, x2, nullptr, s))) return rc;
+    if ((rc = tc_launch<1, false, false, X3>(a, x2, none, x3, s))) return rc;
     // B200DCE_DCE_PAIR=0 (tuning / A-B aid): e_conv4 and e_conv5 as two launches with x4 in HBM
     const char* pe = getenv("B200DCE_DCE_PAIR");
-    if (pe && pe[0] == '0') {
+    if (X3 || (pe && pe[0] == '0')) {
         layer(3, x4);
-        if ((rc = tc_launch<1, false, false>(a, x3, nullptr, s))) return rc;
+        if ((rc = tc_launch<1, false, false, X3>(a, x3, none, x4, s))) return rc;
         layer(4, x5);
-        if ((rc = tc_launch<2, false, false>(a, x3, x4, s))) return rc;
-    } else if ((rc = tc_launch_pair(a, x3, x5, pk + tc_layer_offset(3), pk + tc_layer_offset(4), s))) {
+        if ((rc = tc_launch<2, false, false, X3>(a, x3, x4, x5, s))) return rc;
+    } else if ((rc = tc_launch_pair(a, x3.hi, (__nv_bfloat16*)x5.hi, pk + tc_layer_offset(3), pk + tc_layer_offset(4), s))) {
         return rc;
     }
     layer(5, x6);
-    if ((rc = tc_launch<2, false, false>(a, x2, x5, s))) return rc;
-    layer(6, nullptr);
+    if ((rc = tc_launch<2, false, false, X3>(a, x2, x5, x6, s))) return rc;
+    layer(6, none);
     a.adjust = adjust;
     a.enhanced = enhanced;
-    if ((rc = tc_launch<2, false, true>(a, x1, x6, s))) return rc;
+    if ((rc = tc_launch<2, false, true, X3>(a, x1, x6, none, s))) return rc;
     return B200_OK;
+}
+
+int dce_tc_forward(const float* x, const void* packed, float* adjust, float* enhanced, int B, int H, int W, int iters,
+                   int precision, void* workspace, size_t workspace_bytes, cudaStream_t s) {
+    if (precision == B200_PREC_BF16)
+        return dce_tc_forward_t<false>(x, packed, adjust, enhanced, B, H, W, iters, workspace, workspace_bytes, s);
+    if (precision == B200_PREC_BF16X3)
+        return dce_tc_forward_t<true>(x, packed, adjust, enhanced, B, H, W, iters, workspace, workspace_bytes, s);
+    return B200_ERR_UNSUPPORTED;
 }
 
 }  // namespace b200

@@ -43,7 +43,8 @@ extern "C" {
 /* precision selector for the Zero-DCE conv stack */
 #define B200_PREC_FP32 0   /* fp32 CUDA-core direct convolution (FFMA2), fp32 accumulate            */
 #define B200_PREC_BF16 1   /* bf16 operands on tcgen05 tensor cores, fp32 accumulate in TMEM         */
-#define B200_PREC_BF16X3 2 /* 3-term split-bf16 (hi*hi + lo*hi + hi*lo) tensor-core MMAs: ~fp32 accuracy */
+#define B200_PREC_BF16X3 2 /* 3-term split-bf16 (hi*hi + lo*hi + hi*lo) on tcgen05, fp32 accumulate in TMEM: ~fp32 accuracy */
+#define B200_PREC_BF16X3_MMA 3 /* the same split on warp-level mma.sync (round-1 kernels; kept for A/B) */
 
 int b200_version(void);
 const char* b200_strerror(int code);
