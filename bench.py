@@ -277,8 +277,9 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
     guarded("c2_dce_bf16_1080p_b16", c2("bf16", 16, 10))
     guarded("c4_ruas_1080p_b16", c4_ruas(True))
     guarded("c4_ruas_no_denoise_1080p_b16", c4_ruas(False))
-    guarded("c2_dce_fp32_1080p_b2", c2("fp32", 2, 3))
-    guarded("c2_dce_bf16x3_1080p_b16", c2("bf16x3", 16, 3))
+    guarded("c2_dce_fp32_1080p_b16", c2("fp32", 16, 5))            # the fp32 contract: split-bf16 on tcgen05
+    guarded("c2_dce_fp32_exact_1080p_b2", c2("fp32_exact", 2, 3))  # CUDA-core fp32 products
+    guarded("c2_dce_bf16x3_mma_sync_1080p_b16", c2("bf16x3_mma", 16, 3))  # round-1 kernels, for the A/B
     guarded("c1_dcepp_sf1_512", sf1)
     return out
 

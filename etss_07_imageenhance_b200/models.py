@@ -234,8 +234,9 @@ def _init_conv_weights(module: nn.Module) -> None:
 # --------------------------------------------------------------------------------------------- Zero-DCE
 @MODELS.register(name="zero_dce_re", arch="zero_dce")
 class ZeroDCE_RE(_EnhancementModel):
-    """Zero-DCE (zero_dce.py:86-191).  `precision`: "fp32" (default; CUDA-core fp32, <=1e-3 parity),
-    "bf16" (tcgen05 tensor cores, PSNR >= 50 dB) or "bf16x3" (split-bf16 on tensor cores)."""
+    """Zero-DCE (zero_dce.py:86-191).  `precision`: "fp32" (default: the reference's fp32 contract, max-abs <= 1e-3,
+    on the tcgen05 tensor cores as a 3-term split-bf16 product with fp32 accumulation -- alias "bf16x3"), "bf16"
+    (tcgen05, PSNR >= 50 dB, 2.6x faster) or "fp32_exact" (every product in fp32 on the CUDA cores, ~1e-6, 10x slower)."""
 
     arch = "zero_dce"
 

@@ -180,7 +180,7 @@ class FramePipeline:
     # kernels per chunk, for the bench's gpu_launches claim
     def _launches_per_chunk(self, n: int) -> int:
         fused = self.sf >= 4 and self.W % 4 == 0 and os.environ.get("B200DCE_DCEPP_FUSE", "1") != "0"
-        k = {"dcepp": 2 if fused else 3, "dce": 8 * ((n + 1) // 2) if self.prec == 0 else 8, "sci": 1,
+        k = {"dcepp": 2 if fused else 3, "dce": 8 * ((n + 1) // 2) if self.prec == 0 else {1: 6, 2: 7}.get(self.prec, 8), "sci": 1,
              "ruas": 8 if getattr(self.model, "denoise", False) else 3}[self.kind]
         return k + (2 if self.wire == "u8" else 0)
 

@@ -16,6 +16,7 @@ pytestmark = pytest.mark.gpu
 GOLDEN_DIR = Path(__file__).resolve().parent / "golden"
 TOL = 1e-3      # contract (BASELINE.json north_star, fp32 mode)
 TIGHT = 1e-4    # what the fp32 kernels actually have to meet here
+X3_TIGHT = 2.5e-4  # Zero-DCE in the split-bf16 tensor-core mode (the "fp32" contract path): ~2^-16 per product
 TIGHT_PP = 2.5e-4  # Zero-DCE++ end to end: the pointwise convs run as 3-term split-bf16 tensor-core MMAs (~2^-16 per product)
 
 
@@ -180,11 +181,11 @@ def test_dcepp_weight_cache_invalidation(cuda_dev):
     assert maxerr(b, O.zero_dcepp_forward(x.cpu(), sd, 12)["enhanced"]) <= TIGHT_PP
 
 
-# ------------------------------------------------------------------ Zero-DCE (fp32 mode)
+# ------------------------------------------------------------------ Zero-DCE (fp32_exact: CUDA-core fp32 products)
 @pytest.mark.parametrize("regime", ["init", "stress"])
 def test_dce_fp32_golden(cuda_dev, golden, regime):
     x, sd, outs = golden(f"dce_{regime}")
-    m = load_into(P.MODELS.build(name="zero_dce_re"), sd).to(cuda_dev)
+    m = load_into(P.MODELS.build(config={"name": "zero_dce_re", "precision": "fp32_exact"}), sd).to(cuda_dev)
     out = m({"image": x.to(cuda_dev)})
     assert list(out.keys()) == [f"adjust_{i}" for i in range(8)] + ["adjust", "enhanced"]
     for i in range(8):   # views of adjust, as in the reference
@@ -198,7 +199,7 @@ def test_dce_fp32_golden(cuda_dev, golden, regime):
 def test_dce_fp32_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
     x = O.synthetic_lowlight(B, H, W, seed=60 + iters)
     sd = O.make_dce_state_dict(17, "stress", num_iters=iters)
-    m = load_into(P.ZeroDCE_RE(num_iters=iters), sd).to(cuda_dev)
+    m = load_into(P.ZeroDCE_RE(num_iters=iters, precision="fp32_exact"), sd).to(cuda_dev)
     out = m({"image": x.to(cuda_dev)})
     ref = O.zero_dce_forward(x, sd, num_iters=iters)
     assert out["adjust"].shape == (B, 3 * iters, H, W)
@@ -208,10 +209,23 @@ def test_dce_fp32_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
 
 def test_dce_fp32_zero_weights_identity_1080p(cuda_dev):
     sd = {k: torch.zeros_like(v) for k, v in O.make_dce_state_dict(1).items()}
-    m = load_into(P.ZeroDCE_RE(), sd).to(cuda_dev)
+    m = load_into(P.ZeroDCE_RE(precision="fp32_exact"), sd).to(cuda_dev)
     x = O.synthetic_lowlight(1, 1080, 1920, seed=8).to(cuda_dev)
     out = m({"image": x})
     assert torch.equal(out["enhanced"], x) and not out["adjust"].any()
+
+
+def test_dce_default_precision_is_the_fp32_contract_on_tensor_cores(cuda_dev, golden):
+    """`ZeroDCE_RE()` / registry build without a precision = "fp32" = the split-bf16 tcgen05 kernels: within the fp32
+    contract (1e-3) of the reference's golden output, bit-identical to precision="bf16x3"."""
+    x, sd, outs = golden("dce_stress")
+    m = load_into(P.MODELS.build(name="zero_dce_re"), sd).to(cuda_dev)
+    assert m.precision == "fp32"
+    out = m({"image": x.to(cuda_dev)})
+    ea, ee = maxerr(out["adjust"], outs["adjust"]), maxerr(out["enhanced"], outs["enhanced"])
+    assert ea <= X3_TIGHT and ee <= X3_TIGHT, (ea, ee)
+    o3 = load_into(P.ZeroDCE_RE(precision="bf16x3"), sd).to(cuda_dev)({"image": x.to(cuda_dev)})
+    assert torch.equal(o3["enhanced"], out["enhanced"]) and torch.equal(o3["adjust"], out["adjust"])
 
 
 # ------------------------------------------------------------------ Zero-DCE (bf16 tensor-core mode, tcgen05)
@@ -262,7 +276,7 @@ def test_dce_bf16_matches_fp32_mode_1080p(cuda_dev):
     # full BASELINE frame size: the two precision modes of the SAME weights agree to bf16 noise
     sd = O.make_dce_state_dict(5, "init")
     x = O.synthetic_lowlight(2, 1080, 1920, seed=9).to(cuda_dev)
-    a = load_into(P.ZeroDCE_RE(precision="fp32"), sd).to(cuda_dev)({"image": x})
+    a = load_into(P.ZeroDCE_RE(precision="fp32_exact"), sd).to(cuda_dev)({"image": x})
     b = load_into(P.ZeroDCE_RE(precision="bf16"), sd).to(cuda_dev)({"image": x})
     assert O.psnr(b["enhanced"].cpu(), a["enhanced"].cpu()) >= 50.0
     assert maxerr(b["adjust"], a["adjust"]) <= 2e-2
@@ -517,7 +531,6 @@ def test_dcepp_batch_stream_matches_direct_forward(cuda_dev):
 
 # ------------------------------------------------------------------ Zero-DCE (bf16x3: 3-term split-bf16 tensor-core mode)
 # fp32-class accuracy on the tensor cores: the fp32-mode contract (max-abs <= 1e-3) applies; measured ~1e-5.
-X3_TIGHT = 2.5e-4
 
 
 @pytest.mark.parametrize("regime", ["init", "stress"])
@@ -547,7 +560,7 @@ def test_dce_bf16x3_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
 def test_dce_bf16x3_1080p_matches_fp32_mode_and_identity(cuda_dev):
     x = O.synthetic_lowlight(2, 1080, 1920, seed=9).to(cuda_dev)
     sd = O.make_dce_state_dict(19, "stress")
-    a = load_into(P.ZeroDCE_RE(precision="fp32"), sd).to(cuda_dev)({"image": x})
+    a = load_into(P.ZeroDCE_RE(precision="fp32_exact"), sd).to(cuda_dev)({"image": x})
     b = load_into(P.ZeroDCE_RE(precision="bf16x3"), sd).to(cuda_dev)({"image": x})
     assert maxerr(b["adjust"], a["adjust"].cpu()) <= X3_TIGHT and maxerr(b["enhanced"], a["enhanced"].cpu()) <= X3_TIGHT
     z = load_into(P.ZeroDCE_RE(precision="bf16x3"), {k: torch.zeros_like(v) for k, v in sd.items()}).to(cuda_dev)
@@ -556,7 +569,7 @@ def test_dce_bf16x3_1080p_matches_fp32_mode_and_identity(cuda_dev):
 
 
 # ------------------------------------------------------------------ full-size parity at the BASELINE configs (C2, C3, C4)
-@pytest.mark.parametrize("precision", ["fp32", "bf16x3", "bf16"])
+@pytest.mark.parametrize("precision", ["fp32_exact", "bf16x3", "bf16x3_mma", "bf16"])
 def test_dce_1080p_frame_vs_oracle(cuda_dev, precision):
     """C2 frame size against the CPU oracle itself (not mode against mode): fp32 / bf16x3 under the <= 1e-3 contract,
     bf16 under the PSNR >= 50 dB contract; stress weights so the curve maps are not ~0."""
@@ -638,3 +651,12 @@ def test_frame_pipeline_follows_load_state_dict(cuda_dev):
     assert not torch.equal(a, b)
     assert torch.equal(b, m({"image": hin.to(cuda_dev)})["enhanced"].cpu())
     assert maxerr(b, O.zero_dcepp_forward(hin, sd2, 12)["enhanced"]) <= TIGHT_PP
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_dce_bf16x3_mma_sync_kernels_still_match(cuda_dev, golden, regime):
+    """The round-1 warp-level split-bf16 kernels stay reachable (precision "bf16x3_mma") as the A/B partner of the
+    tcgen05 ones."""
+    x, sd, outs = golden(f"dce_{regime}")
+    out = load_into(P.ZeroDCE_RE(precision="bf16x3_mma"), sd).to(cuda_dev)({"image": x.to(cuda_dev)})
+    assert maxerr(out["adjust"], outs["adjust"]) <= X3_TIGHT and maxerr(out["enhanced"], outs["enhanced"]) <= X3_TIGHT
