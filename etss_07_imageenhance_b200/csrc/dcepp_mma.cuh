@@ -90,8 +90,8 @@ static_assert(MM_SLOT_BYTES % 128 == 0 && (mm_blob_words(1) * 4) % 16 == 0 && (m
               "bulk-copy sizes / TMA destinations");
 constexpr int MM_VCOLS = 64;                      // low-res columns under one block of the full-resolution pass
 constexpr int MM_VROW_FLOATS = 8 * 3 * MM_VCOLS;  // per CTA: [consumer warp][channel][column]
-// ring | full / empty barriers | 4 item descriptors | per-warp strips of the full-resolution pass
-constexpr int MM_HALF_SMEM = MM_NS * MM_SLOT_BYTES + 2 * MM_NS * 8 + 4 * 16 + MM_VROW_FLOATS * 4;
+// ring | full / empty barriers | 4 item descriptors | 4 tile arrival counters (+ pad) | per-warp strips of the full-res pass
+constexpr int MM_HALF_SMEM = MM_NS * MM_SLOT_BYTES + 2 * MM_NS * 8 + 4 * 16 + 128 + MM_VROW_FLOATS * 4;
 constexpr int MM_NET_SMEM = 2 * MM_HALF_SMEM;
 static_assert(MM_HALF_SMEM % 128 == 0, "the second half's ring stays 128-byte aligned");
 static_assert(MM_NET_SMEM <= 227 * 1024, "one CTA per SM");
@@ -476,7 +476,8 @@ dcepp_net_kernel(const MmNetArgs a, const MmApplyArgs ap, const __grid_constant_
     // item descriptors, producer -> consumers: {item number q (-1 = end), kind + 8 * frame, y0, x0};
     // kind 0..5 = tile of e_conv2..7, 6 = block of the full-resolution pass
     volatile int4* s_tq = reinterpret_cast<volatile int4*>(empty + MM_NS);
-    float* s_vrow = reinterpret_cast<float*>(mm_smem + MM_NS * MM_SLOT_BYTES + 2 * MM_NS * 8 + 64);
+    int* s_cnt = reinterpret_cast<int*>(mm_smem + MM_NS * MM_SLOT_BYTES + 2 * MM_NS * 8 + 64);  // [4] warps done with a tile
+    float* s_vrow = reinterpret_cast<float*>(mm_smem + MM_NS * MM_SLOT_BYTES + 2 * MM_NS * 8 + 64 + 128);
 
     const int t = threadIdx.x - half * MM_HALF, lane = t & 31, warp = t >> 5;
     const int ntx = (w + MM_TW - 1) / MM_TW, nty = (h + MM_TH - 1) / MM_TH;
@@ -489,6 +490,7 @@ dcepp_net_kernel(const MmNetArgs a, const MmApplyArgs ap, const __grid_constant_
         for (int i = 0; i < MM_NS; ++i) {
             tc::mbar_init(&full[i], 1);   // the producer's expect_tx arrive (+ the stage's bytes)
             tc::mbar_init(&empty[i], 8);  // one arrive per consumer warp
+            s_cnt[i] = 0;
         }
         tc::mbar_fence_init();
     }
@@ -646,7 +648,7 @@ dcepp_net_kernel(const MmNetArgs a, const MmApplyArgs ap, const __grid_constant_
     }
 
     // ================= consumer warps =================
-    int ck = 0, tk = 0;
+    int ck = 0, tk = 0, nk = 0;  // stages, items, net tiles consumed so far
     uint32_t tr_wait = 0, tr_start = 0, tr_id = 0;
     const bool tracing = TRACE && t == 0;
     if (tracing) {
@@ -686,13 +688,26 @@ dcepp_net_kernel(const MmNetArgs a, const MmApplyArgs ap, const __grid_constant_
             mm_tile<2, 4, false>(t, ring, full, empty, ck, ds, h, w, wp, b, y0, x0);
         else
             mm_tile<2, 1, true>(t, ring, full, empty, ck, ds, h, w, wp, b, y0, x0, ap.total > 0 ? ap.wq : w);
-        tc::named_bar_sync(1 + half, 256);  // all of this tile's stores are issued
-        if (t == 0) {
-            if (l < 5)
-                mm_st_release(flags + q, 1);
-            else if (ap.total > 0)
-                mm_red_release_add(sync + MM_FDONE0 + b, 1);  // one more layer-7 tile of frame b
+        // Publication without a CTA barrier: every warp counts itself done (acq_rel at CTA scope behind its own stores),
+        // the LAST one resets the counter and publishes the tile (release at GPU scope, cumulative over what it acquired);
+        // the other seven go straight on to the next item.  At most two tiles are in flight per half (4 ring slots, >= 2
+        // stages per tile), so four counters cannot be lapped.
+        __syncwarp();
+        if (lane == 0) {
+            int old;
+            asm volatile("atom.acq_rel.cta.shared.add.s32 %0, [%1], 1;"
+                         : "=r"(old)
+                         : "r"(tc::smem_u32(s_cnt + (nk & 3)))
+                         : "memory");
+            if (old == 7) {
+                s_cnt[nk & 3] = 0;
+                if (l < 5)
+                    mm_st_release(flags + q, 1);
+                else if (ap.total > 0)
+                    mm_red_release_add(sync + MM_FDONE0 + b, 1);  // one more layer-7 tile of frame b
+            }
         }
+        ++nk;
         ++tk;
         if (tracing) trace_item(l);
     }
