@@ -3,6 +3,7 @@
 Public surface (mirrors the reference for this path only):
   MODELS                         registry with mon's ModelFactory semantics (registry.py)
   ZeroDCE_RE, ZeroDCEpp_RE       `mon` model classes (models.py) — forward(datapoint) -> dict
+  ZeroDCEV                       ZeroDCE-V, core of the forward only (forward_core; SURVEY 8f-3, partial)
   SCI_RE                         upstream SCI Finetunemodel
   RUAS_RE                        upstream RUAS Network (3 IEM iterations + denoise net)
   torch.ops.b200dce.*            custom ops over the C ABI (ops.py, include/b200dce.h)
@@ -13,7 +14,7 @@ There is no CPU fallback: the kernels live in lib/libb200dce.so (build: `python 
 etss_07_imageenhance_b200.build`); a missing library or a CPU tensor raises.
 """
 from . import ops  # registers torch.ops.b200dce.*
-from .models import (DSConv2d, DepthwiseSeparableConv2d, SCI_RE, RUAS_RE, ZeroDCE_RE, ZeroDCEpp_RE, ZeroDCELoss,
+from .models import (DSConv2d, DepthwiseSeparableConv2d, SCI_RE, RUAS_RE, ZeroDCE_RE, ZeroDCEV, ZeroDCEpp_RE, ZeroDCELoss,
                      remap_upstream_dcepp_keys)
 from .registry import MODELS, ModelFactory, register_into_mon
 from .sched import DceppBatchStream, FramePipeline, gather_max_ms, gather_objects, shard_range
@@ -23,6 +24,6 @@ from .sched import DceppBatchStream, FramePipeline, gather_max_ms, gather_object
 MON_REGISTERED = register_into_mon()
 
 __version__ = "0.2.0"
-__all__ = ["ops", "MODELS", "ModelFactory", "register_into_mon", "ZeroDCE_RE", "ZeroDCEpp_RE", "SCI_RE", "RUAS_RE", "DSConv2d",
+__all__ = ["ops", "MODELS", "ModelFactory", "register_into_mon", "ZeroDCE_RE", "ZeroDCEV", "ZeroDCEpp_RE", "SCI_RE", "RUAS_RE", "DSConv2d",
            "DepthwiseSeparableConv2d", "ZeroDCELoss", "remap_upstream_dcepp_keys", "FramePipeline", "DceppBatchStream", "shard_range",
            "gather_max_ms", "gather_objects"]

@@ -194,9 +194,124 @@ static int dce_forward_f32(const float* x, const float* packed, float* adjust, f
     return B200_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// ZeroDCE-V core (ZeroDCEV.forward, zero_dce_v.py:172-197): V channel of the RGB image, nearest resize
+// to down_size x down_size, DCE-Net with in_channels = 1 -> num_iters (15) curve maps, num_iters curve steps on V.
+// The convolutions are the fp32 CUDA-core kernel above (its source / output channel counts are run-time values);
+// packed layout as for Zero-DCE with cin(layer 1) = 1.
+// ------------------------------------------------------------------------------------------------
+__host__ __device__ constexpr int dcev_cin(int l) { return l == 0 ? 1 : (l <= 3 ? 32 : 64); }
+__host__ __device__ constexpr int dcev_layer_offset(int l) {
+    int o = 0;
+    for (int i = 0; i < l; ++i) o += dcev_cin(i) * 9 * 32 + 32;
+    return o;
+}
+constexpr int DCEV_TOTAL = dcev_layer_offset(7);
+
+__global__ void dcev_pack_kernel(DcePackArgs a, float* __restrict__ packed, int cout_last) {
+    const int l = blockIdx.x;
+    const int cin = dcev_cin(l);
+    const int cout = l == 6 ? cout_last : 32;
+    float* out = packed + dcev_layer_offset(l);
+    const int nw = cin * 9 * 32;
+    for (int i = threadIdx.x; i < nw; i += blockDim.x) {
+        const int o = i & 31;
+        const int tap = (i >> 5) % 9;
+        const int c = (i >> 5) / 9;
+        out[i] = o < cout ? a.w[l][(o * cin + c) * 9 + tap] : 0.f;  // OIHW -> [cin][tap][cout]
+    }
+    for (int i = threadIdx.x; i < 32; i += blockDim.x) out[nw + i] = i < cout ? a.b[l][i] : 0.f;
+}
+
+// image_v = max(R, G, B) (kornia rgb_to_hsv: v = image.max(-3)) at full resolution, and its nearest-neighbour
+// resize to S x S (F.interpolate(size=(S, S)), mode "nearest": src = min(floor(dst * scale), in - 1),
+// scale = (float)in / out, ATen nearest_neighbor_compute_source_index)
+__global__ void __launch_bounds__(256)
+dcev_v_kernel(const float* __restrict__ rgb, float* __restrict__ v, long long n, long long plane) {
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+        const long long b = i / plane, p = i - b * plane;
+        const float* s = rgb + b * 3 * plane + p;
+        v[i] = fmaxf(fmaxf(s[0], s[plane]), s[2 * plane]);
+    }
+}
+__global__ void __launch_bounds__(256)
+dcev_nearest_kernel(const float* __restrict__ v, float* __restrict__ v_lr, int B, int H, int W, int S, float sh, float sw) {
+    const long long n = (long long)B * S * S;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+        const int X = (int)(i % S), Y = (int)((i / S) % S);
+        const long long b = i / ((long long)S * S);
+        const int ys = min((int)floorf(__fmul_rn((float)Y, sh)), H - 1);
+        const int xs = min((int)floorf(__fmul_rn((float)X, sw)), W - 1);
+        v_lr[i] = v[(b * H + ys) * (long long)W + xs];
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" size_t b200_dcev_packed_floats(void) { return (size_t)DCEV_TOTAL; }
+
+extern "C" int b200_dcev_pack_weights(const float* const* w, const float* const* b, float* packed, int iters,
+                                      void* stream) {
+    if (!w || !b || !packed) return B200_ERR_NULL;
+    if (iters < 1 || iters > 32) return B200_ERR_UNSUPPORTED;
+    DcePackArgs a;
+    for (int l = 0; l < 7; ++l) {
+        if (!w[l] || !b[l]) return B200_ERR_NULL;
+        a.w[l] = w[l];
+        a.b[l] = b[l];
+    }
+    dcev_pack_kernel<<<7, 256, 0, (cudaStream_t)stream>>>(a, packed, iters);
+    return launch_status();
+}
+
+extern "C" size_t b200_dcev_workspace_bytes(int B, int S) {
+    if (B <= 0 || S <= 0) return 0;
+    return 5 * dce_align_up((size_t)B * 32 * S * S * sizeof(float), 256);
+}
+
+extern "C" int b200_dcev_core(const float* image_rgb, const float* packed, float* image_v, float* image_v_lr,
+                              float* adjust, float* image_v_fixed_lr, int B, int H, int W, int S, int iters,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+    if (!image_rgb || !packed || !image_v || !image_v_lr || !adjust || !image_v_fixed_lr || !workspace)
+        return B200_ERR_NULL;
+    if (B <= 0 || H <= 0 || W <= 0 || S <= 0) return B200_ERR_BAD_SHAPE;
+    if (iters < 1 || iters > 32 || B > 65535) return B200_ERR_UNSUPPORTED;
+    if (!aligned16(image_rgb) || !aligned16(packed) || !aligned16(image_v) || !aligned16(image_v_lr) ||
+        !aligned16(adjust) || !aligned16(image_v_fixed_lr) || !aligned16(workspace))
+        return B200_ERR_MISALIGNED;
+    if (workspace_bytes < b200_dcev_workspace_bytes(B, S)) return B200_ERR_WORKSPACE;
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long plane = (long long)H * W, n = (long long)B * plane;
+    long long blocks = (n + 255) / 256;
+    if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
+    dcev_v_kernel<<<(unsigned)blocks, 256, 0, s>>>(image_rgb, image_v, n, plane);
+    blocks = ((long long)B * S * S + 255) / 256;
+    if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
+    // ATen: scale = (float)input_size / output_size (no scale_factor given)
+    dcev_nearest_kernel<<<(unsigned)blocks, 256, 0, s>>>(image_v, image_v_lr, B, H, W, S, (float)H / (float)S,
+                                                        (float)W / (float)S);
+    int rc = launch_status();
+    if (rc) return rc;
+    const size_t fmap = dce_align_up((size_t)B * 32 * S * S * sizeof(float), 256);
+    char* ws = (char*)workspace;
+    float* x1 = (float*)(ws + 0 * fmap);
+    float* x2 = (float*)(ws + 1 * fmap);
+    float* x3 = (float*)(ws + 2 * fmap);
+    float* x4 = (float*)(ws + 3 * fmap);
+    float* x5 = (float*)(ws + 4 * fmap);
+    float* x6 = x4;
+    auto wl = [&](int l) { return packed + dcev_layer_offset(l); };
+    if ((rc = launch_conv_f32(image_v_lr, 1, nullptr, 0, x1, wl(0), 32, false, B, S, S, s))) return rc;
+    if ((rc = launch_conv_f32(x1, 32, nullptr, 0, x2, wl(1), 32, false, B, S, S, s))) return rc;
+    if ((rc = launch_conv_f32(x2, 32, nullptr, 0, x3, wl(2), 32, false, B, S, S, s))) return rc;
+    if ((rc = launch_conv_f32(x3, 32, nullptr, 0, x4, wl(3), 32, false, B, S, S, s))) return rc;
+    if ((rc = launch_conv_f32(x3, 32, x4, 32, x5, wl(4), 32, false, B, S, S, s))) return rc;
+    if ((rc = launch_conv_f32(x2, 32, x5, 32, x6, wl(5), 32, false, B, S, S, s))) return rc;
+    if ((rc = launch_conv_f32(x1, 32, x6, 32, adjust, wl(6), iters, true, B, S, S, s))) return rc;
+    return curve_per_iter_unaligned_ok(image_v_lr, adjust, image_v_fixed_lr, B, 1, S, S, iters, s);
+}
 
 extern "C" size_t b200_dce_packed_bytes(int precision, int iters) {
     if (iters < 1 || iters > 8) return 0;

@@ -26,7 +26,7 @@ from . import ops
 from ._lib import PRECISIONS
 from .registry import MODELS
 
-__all__ = ["DSConv2d", "DepthwiseSeparableConv2d", "ZeroDCELoss", "ZeroDCE_RE", "ZeroDCEpp_RE", "SCI_RE", "RUAS_RE",
+__all__ = ["DSConv2d", "DepthwiseSeparableConv2d", "ZeroDCELoss", "ZeroDCE_RE", "ZeroDCEV", "ZeroDCEpp_RE", "SCI_RE", "RUAS_RE",
            "remap_upstream_dcepp_keys", "WEIGHTS_EXTENSIONS"]
 
 WEIGHTS_EXTENSIONS = (".pt", ".pth", ".onnx")  # src/mon/globals.py:709
@@ -304,6 +304,72 @@ class ZeroDCE_RE(_EnhancementModel):
         (enhanced, adjust)."""
         out = self.forward({"image": x})
         return out["enhanced"], out["adjust"]
+
+
+# --------------------------------------------------------------------------------------------- ZeroDCE-V (core)
+@MODELS.register(name="zero_dce_v", arch="zero_dce")
+class ZeroDCEV(_EnhancementModel):
+    """ZeroDCE-V (zero_dce_v.py:92-218), PARTIAL: constructor, attribute names and state_dict layout of
+    the reference class, and `forward_core` = its forward up to `image_v_fixed_lr` (:172-193: V channel, nearest resize
+    to `down_size`, DCE-Net with in_channels=1, `num_iters` curve steps on V) on the fp32 kernels.  The rest of the
+    reference forward -- `FastGuidedFilter` upsample (:194), HSV recomposition through kornia and the division by the
+    global maximum (:195-197) -- is not built; `forward` says so instead of returning something else."""
+
+    arch = "zero_dce"
+    schemes: list = ["unsupervised", "zero_reference", "instance"]
+
+    def __init__(self, in_channels: int = 1, num_channels: int = 32, num_iters: int = 15, down_size: int = 256,
+                 weights: Any = None, *args, **kwargs):
+        kwargs.pop("name", None)
+        super().__init__(name="zero_dce_v", in_channels=in_channels, weights=weights, *args, **kwargs)
+        if isinstance(self.weights, dict):
+            in_channels = self.weights.get("in_channels", in_channels)
+            num_channels = self.weights.get("num_channels", num_channels)
+            num_iters = self.weights.get("num_iters", num_iters)
+            down_size = self.weights.get("down_size", down_size)
+        self.in_channels = in_channels or self.in_channels
+        self.num_channels = num_channels
+        self.num_iters = num_iters
+        self.out_channels = self.in_channels * self.num_iters
+        self.down_size = down_size
+        nc = self.num_channels
+        self.relu = nn.ReLU(inplace=True)
+        self.e_conv1 = nn.Conv2d(self.in_channels, nc, 3, 1, 1, bias=True)
+        self.e_conv2 = nn.Conv2d(nc, nc, 3, 1, 1, bias=True)
+        self.e_conv3 = nn.Conv2d(nc, nc, 3, 1, 1, bias=True)
+        self.e_conv4 = nn.Conv2d(nc, nc, 3, 1, 1, bias=True)
+        self.e_conv5 = nn.Conv2d(nc * 2, nc, 3, 1, 1, bias=True)
+        self.e_conv6 = nn.Conv2d(nc * 2, nc, 3, 1, 1, bias=True)
+        self.e_conv7 = nn.Conv2d(nc * 2, self.out_channels, 3, 1, 1, bias=True)
+        self.loss = ZeroDCELoss()
+        if self.weights:
+            self.load_weights()
+        else:
+            _init_conv_weights(self)
+
+    def packed_weights(self) -> torch.Tensor:
+        convs = [getattr(self, f"e_conv{i}") for i in range(1, 8)]
+        ws, bs = [c.weight for c in convs], [c.bias for c in convs]
+        key = (self.num_iters,) + self._params_key(ws + bs)
+        if self._packed is None or self._packed_key != key:
+            self._packed = torch.ops.b200dce.dcev_pack([w.detach() for w in ws], [b.detach() for b in bs],
+                                                       self.num_iters)
+            self._packed_key = key
+        return self._packed
+
+    @torch.no_grad()
+    def forward_core(self, datapoint: dict, *args, **kwargs) -> dict:
+        """The first four entries of the reference's output dict (zero_dce_v.py:198-203), same keys and order."""
+        x = self._image(datapoint)
+        v, v_lr, adjust, fixed = torch.ops.b200dce.dcev_core(x, self.packed_weights(), int(self.down_size),
+                                                             self.num_iters)
+        return {"image_v": v, "image_v_lr": v_lr, "adjust": adjust, "image_v_fixed_lr": fixed}
+
+    def forward(self, datapoint: dict, *args, **kwargs) -> dict:
+        raise NotImplementedError(
+            "ZeroDCEV: only the core of the forward is built on the B200 path (forward_core: image_v, image_v_lr, "
+            "adjust, image_v_fixed_lr); the guided-filter upsample and the HSV recomposition of zero_dce_v.py:194-197 "
+            "are not")
 
 
 # --------------------------------------------------------------------------------------------- Zero-DCE++

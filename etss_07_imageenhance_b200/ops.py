@@ -23,7 +23,7 @@ from ._lib import PRECISIONS, check, lib, ptr_array
 
 __all__ = [
     "curve_shared", "curve_per_iter", "dcepp_pack", "dcepp_forward", "dcepp_lowres", "dcepp_apply",
-    "dce_pack", "dce_forward", "sci_pack", "sci_forward", "ruas_pack", "ruas_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
+    "dce_pack", "dce_forward", "dcev_pack", "dcev_core", "sci_pack", "sci_forward", "ruas_pack", "ruas_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
     "current_stream_ptr", "require_device",
 ]
 
@@ -268,6 +268,66 @@ def dce_forward(x: Tensor, packed: Tensor, iters: int, precision: int,
 def _(x, packed, iters, precision, return_adjust):
     B, _, H, W = x.shape
     return (x.new_empty(B, 3 * iters, H, W) if return_adjust else x.new_empty(0)), torch.empty_like(x)
+
+
+# ----------------------------------------------------------------------------- ZeroDCE-V core (partial)
+@torch.library.custom_op("b200dce::dcev_pack", mutates_args=(), device_types="cuda")
+def dcev_pack(weights: List[Tensor], biases: List[Tensor], iters: int) -> Tensor:
+    """Re-pack ZeroDCEV's e_conv{1..7}.{weight,bias} (zero_dce_v.py:127-133: in_channels=1, num_channels=32,
+    out = num_iters maps) for the fp32 kernels."""
+    if not (len(weights) == len(biases) == 7):
+        raise ValueError("b200dce::dcev_pack expects 7 layers")
+    cin = [1, 32, 32, 32, 64, 64, 64]
+    cout = [32] * 6 + [iters]
+    for i in range(7):
+        if tuple(weights[i].shape) != (cout[i], cin[i], 3, 3) or tuple(biases[i].shape) != (cout[i],):
+            raise NotImplementedError(
+                f"b200dce: the ZeroDCE-V kernels implement in_channels=1, num_channels=32, num_iters<=32 only; "
+                f"layer {i + 1} weight shape {tuple(weights[i].shape)}")
+    dev = weights[0].device
+    w, b = _f32c(weights, dev), _f32c(biases, dev)
+    packed = torch.empty(lib().b200_dcev_packed_floats(), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().b200_dcev_pack_weights(ptr_array([t.data_ptr() for t in w]), ptr_array([t.data_ptr() for t in b]),
+                                           packed.data_ptr(), iters, current_stream_ptr()), "b200_dcev_pack_weights")
+    return packed
+
+
+@dcev_pack.register_fake
+def _(weights, biases, iters):
+    return weights[0].new_empty(lib().b200_dcev_packed_floats(), dtype=torch.float32)
+
+
+@torch.library.custom_op("b200dce::dcev_core", mutates_args=(), device_types="cuda")
+def dcev_core(image: Tensor, packed: Tensor, down_size: int, iters: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """image [B,3,H,W] -> (image_v [B,1,H,W], image_v_lr [B,1,S,S], adjust [B,iters,S,S], image_v_fixed_lr [B,1,S,S]):
+    ZeroDCEV.forward up to `image_v_fixed_lr` (zero_dce_v.py:172-193)."""
+    image = _img(image, "image")
+    B, _, H, W = image.shape
+    S = int(down_size)
+    if S <= 0:
+        raise ValueError(f"b200dce::dcev_core: bad down_size {down_size}")
+    v = image.new_empty(B, 1, H, W)
+    v_lr = image.new_empty(B, 1, S, S)
+    adjust = image.new_empty(B, iters, S, S)
+    fixed = image.new_empty(B, 1, S, S)
+    if B:
+        L = lib()
+        ws_bytes = L.b200_dcev_workspace_bytes(B, S)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=image.device)
+        with torch.cuda.device(image.device):
+            check(L.b200_dcev_core(image.data_ptr(), packed.data_ptr(), v.data_ptr(), v_lr.data_ptr(), adjust.data_ptr(),
+                                   fixed.data_ptr(), B, H, W, S, iters, ws.data_ptr(), ws_bytes, current_stream_ptr()),
+                  "b200_dcev_core")
+    return v, v_lr, adjust, fixed
+
+
+@dcev_core.register_fake
+def _(image, packed, down_size, iters):
+    B, _, H, W = image.shape
+    S = int(down_size)
+    return (image.new_empty(B, 1, H, W), image.new_empty(B, 1, S, S), image.new_empty(B, iters, S, S),
+            image.new_empty(B, 1, S, S))
 
 
 # ----------------------------------------------------------------------------- SCI

@@ -180,6 +180,25 @@ int b200_ruas_forward(const float* x, const float* packed_host, float* u, float*
                       float* noise_or_null, int B, int H, int W, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * "next" row (partial): the core of ZeroDCE-V, ZeroDCEV.forward
+ * src/mon/vision/enhance/llie/zero_dce/zero_dce_v.py:172-197 up to `image_v_fixed_lr`:
+ *   image_v    = V channel of the RGB image (= max over channels)            :175-176
+ *   image_v_lr = F.interpolate(image_v, size=(S, S))  (nearest)              :177,204-206
+ *   adjust     = tanh(DCE-Net(image_v_lr)), in_channels = 1, `iters` maps    :179-187
+ *   image_v_fixed_lr = `iters` curve steps on image_v_lr                     :189-193
+ * fp32 CUDA-core convolutions (every product in fp32).  NOT built: the guided-filter upsample (:194,208-218), the
+ * HSV decomposition / recomposition (kornia) and the division by the global maximum (:195-197).
+ * w[i], b[i]: e_conv{i+1}.weight [cout, cin, 3, 3] / .bias with cin(1) = 1, cout(7) = iters (HOST arrays of 7
+ * device pointers).  Outputs: image_v [B,1,H,W], image_v_lr [B,1,S,S], adjust [B,iters,S,S], image_v_fixed_lr [B,1,S,S].
+ * ------------------------------------------------------------------------- */
+size_t b200_dcev_packed_floats(void);
+int b200_dcev_pack_weights(const float* const* w, const float* const* b, float* packed, int iters, void* stream);
+size_t b200_dcev_workspace_bytes(int B, int S);
+int b200_dcev_core(const float* image_rgb, const float* packed, float* image_v, float* image_v_lr, float* adjust,
+                   float* image_v_fixed_lr, int B, int H, int W, int S, int iters, void* workspace,
+                   size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * "next" rows: u8 HWC <-> fp32 NCHW frame conversion.
  * Replaces src/mon/core/image/utils.py:801-848 (to_image_tensor(normalize=True)
  * -> normalize_image_by_range, src/mon/core/image/photometry.py:262-263:

@@ -219,6 +219,31 @@ def zero_dce_forward(x: torch.Tensor, sd: dict, num_iters: int = 8) -> dict:
 
 
 @torch.no_grad()
+def zero_dce_v_core(x: torch.Tensor, sd: dict, down_size: int = 256, num_iters: int = 15) -> dict:
+    """ZeroDCEV.forward (src/mon/vision/enhance/llie/zero_dce/zero_dce_v.py:172-193) up to `image_v_fixed_lr`:
+    `core.rgb_to_v` = V of kornia's rgb_to_hsv = the maximum over the channels (src/mon/core/image/color.py:198-221),
+    `interpolate_image` = F.interpolate(size=(down_size, down_size)) (nearest, :204-206), the 7-layer DCE-Net with
+    in_channels = 1 (:179-186) and `num_iters` curve steps on the low-resolution V (:189-192)."""
+    image_v = x.max(dim=1, keepdim=True)[0]
+    image_v_lr = F.interpolate(image_v, size=(down_size, down_size))
+
+    def conv(t, i):
+        return F.conv2d(t, sd[f"e_conv{i}.weight"], sd[f"e_conv{i}.bias"], stride=1, padding=1)
+    x1 = F.relu(conv(image_v_lr, 1))
+    x2 = F.relu(conv(x1, 2))
+    x3 = F.relu(conv(x2, 3))
+    x4 = F.relu(conv(x3, 4))
+    x5 = F.relu(conv(torch.cat([x3, x4], 1), 5))
+    x6 = F.relu(conv(torch.cat([x2, x5], 1), 6))
+    x_r = torch.tanh(conv(torch.cat([x1, x6], 1), 7))
+    x_rs = torch.split(x_r, 1, dim=1)
+    y = image_v_lr
+    for i in range(num_iters):
+        y = y + x_rs[i] * (torch.pow(y, 2) - y)
+    return {"image_v": image_v, "image_v_lr": image_v_lr, "adjust": x_r, "image_v_fixed_lr": y}
+
+
+@torch.no_grad()
 def zero_dce_forward_bf16_operands(x: torch.Tensor, sd: dict, num_iters: int = 8) -> dict:
     """`zero_dce_forward` with the OPERAND rounding of the tensor-core mode: every conv input and every
     weight is rounded to bf16 (round-to-nearest-even), products/accumulation/bias/activation stay fp32.

@@ -21,6 +21,8 @@ src/mon/vision/enhance/base.py:32-47).  The arithmetic (`forward`) and the
 parameter names are the reference's own code.
 
 Assertions (all on CPU, fp32): oracle == reference bit-for-bit.
+  * src/mon/vision/enhance/llie/zero_dce/zero_dce_v.py   (class ZeroDCEV; kornia's HSV conversions and the
+    plum-dispatched guided filter are stubbed, only the four outputs that do not depend on them are pinned)
   * src/mon/core/image/photometry.py, src/mon/core/image/utils.py  (to_image_tensor(normalize=True) /
     to_image_nparray(denormalize=True): the u8 HWC <-> fp32 NCHW frame format)
 Outputs: tests/golden/{dce,dcepp_sf1,dcepp_sf2,dcepp_sf12,sci,ruas}_{init,stress}.npz
@@ -108,6 +110,7 @@ def install_stub_mon():
         UNSUPERVISED = "unsupervised"
         ZERO_REFERENCE = "zero_reference"
         SUPERVISED = "supervised"
+        INSTANCE = "instance"
 
     class _Models(dict):
         def register(self, name=None, arch=None, replace=False):
@@ -188,6 +191,37 @@ def load_reference_image_utils():
     utils = _load_file("mon.core.image.utils", d / "utils.py")
     image.photometry, image.utils = phot, utils
     return phot, utils
+
+
+def load_reference_zero_dce_v():
+    """src/mon/vision/enhance/llie/zero_dce/zero_dce_v.py, unmodified, under the stub `mon`.  Its forward calls three
+    things that are not available here and do not feed the outputs we pin: `core.rgb_to_hsv` / `core.hsv_to_rgb`
+    (kornia) and `filtering.FastGuidedFilter` (needs `plum`).  The stubs: rgb_to_hsv returns (0, 0, V) with V = the
+    channel maximum -- kornia's own definition of V (`v = image.max(-3)`), which is all `core.rgb_to_v` takes from it
+    (src/mon/core/image/color.py:216-219) --, hsv_to_rgb is the identity, the guided filter returns a nearest resize.
+    Pinned: `image_v`, `image_v_lr`, `adjust`, `image_v_fixed_lr`; NOT pinned: `image_v_fixed`, `enhanced`."""
+    core = sys.modules["mon.core"]
+
+    def rgb_to_hsv(image, eps=1e-8):
+        v = image.max(dim=-3, keepdim=True)[0]
+        return torch.cat([torch.zeros_like(v), torch.zeros_like(v), v], dim=-3)
+    core.rgb_to_hsv = rgb_to_hsv
+    core.rgb_to_v = lambda image, eps=1e-8: rgb_to_hsv(image, eps)[:, 2:3, :, :]   # color.py:216-219
+    core.hsv_to_rgb = lambda image: image
+    vision = sys.modules["mon.vision"]
+    filtering = types.ModuleType("mon.vision.filtering")
+
+    class FastGuidedFilter(torch.nn.Module):
+        def __init__(self, radius=1, **kw):
+            super().__init__()
+
+        def forward(self, x_lr, y_lr, x_hr):
+            return torch.nn.functional.interpolate(y_lr, size=x_hr.shape[-2:])
+    filtering.FastGuidedFilter = FastGuidedFilter
+    vision.filtering = filtering
+    sys.modules["mon.vision.filtering"] = filtering
+    zv = _load_file("ref_zero_dce_v", REF / "src/mon/vision/enhance/llie/zero_dce/zero_dce_v.py")
+    return zv.ZeroDCEV
 
 
 def to_upstream_keys(sd: dict) -> dict:
@@ -336,6 +370,34 @@ def main():
         save(f"ruas_{regime}", x, sd, u=torch.stack(u_ref), t=torch.stack(t_ref), denoised=ud_ref, noise=n_ref)
         report.append(f"ruas/{regime}: oracle == upstream EnhanceNetwork -> DenoiseNetwork; "
                       f"t in [{t_ref[-1].min():.3f}, {t_ref[-1].max():.3f}], |noise|max={n_ref.abs().max():.3f}")
+
+    # ---------------- ZeroDCE-V core (partial) ----------------
+    ZeroDCEV = load_reference_zero_dce_v()
+    assert MODELS["zero_dce"]["zero_dce_v"] is ZeroDCEV
+    mv = ZeroDCEV()
+    assert list(mv.state_dict().keys()) == [f"e_conv{i}.{p}" for i in range(1, 8) for p in ("weight", "bias")] + \
+        [f"loss.loss_spa.weight_{d}" for d in ("left", "right", "up", "down")]
+    assert (mv.in_channels, mv.num_iters, mv.out_channels, mv.down_size) == (1, 15, 15, 256)
+    assert mv.e_conv1.weight.shape == (32, 1, 3, 3) and mv.e_conv7.weight.shape == (15, 64, 3, 3)
+    for regime in ("init", "stress"):
+        # batch 1 per call: the reference's replace_v_component (:221-230) assigns a [B,1,H,W] tensor into a [B,H,W]
+        # slice, which only broadcasts for B == 1 -- the class does not run on larger batches as written
+        x = O.synthetic_lowlight(2, 70, 90, seed=601)
+        sd = O.make_dce_state_dict(19, regime, num_iters=15, in_channels=1)
+        m = ZeroDCEV(down_size=48).eval()
+        m.load_state_dict(sd, strict=False)
+        refs = []
+        with torch.no_grad():
+            for i in range(2):
+                refs.append(m({"image": x[i:i + 1].clone()}))
+        assert list(refs[0].keys()) == ["image_v", "image_v_lr", "adjust", "image_v_fixed_lr", "image_v_fixed", "enhanced"]
+        got = O.zero_dce_v_core(x, sd, down_size=48, num_iters=15)
+        ref = {k: torch.cat([r[k] for r in refs]) for k in got}
+        for k in got:
+            eq(got[k], ref[k], f"dcev/{regime}/{k}")
+        save(f"dcev_{regime}", x, sd, **ref)
+        report.append(f"dcev/{regime}: oracle == mon ZeroDCEV.forward for image_v, image_v_lr, adjust, image_v_fixed_lr "
+                      f"(HSV / guided filter stubbed, their outputs not pinned); |adjust|max={ref['adjust'].abs().max():.3f}")
 
     # ---------------- u8 HWC <-> fp32 NCHW frame format ----------------
     phot, iutils = load_reference_image_utils()

@@ -660,3 +660,28 @@ def test_dce_bf16x3_mma_sync_kernels_still_match(cuda_dev, golden, regime):
     x, sd, outs = golden(f"dce_{regime}")
     out = load_into(P.ZeroDCE_RE(precision="bf16x3_mma"), sd).to(cuda_dev)({"image": x.to(cuda_dev)})
     assert maxerr(out["adjust"], outs["adjust"]) <= X3_TIGHT and maxerr(out["enhanced"], outs["enhanced"]) <= X3_TIGHT
+
+
+# ------------------------------------------------------------------ ZeroDCE-V core (partial)
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_zero_dce_v_core_golden(cuda_dev, golden, regime):
+    """forward_core against the first four outputs of the reference's own ZeroDCEV.forward."""
+    x, sd, outs = golden(f"dcev_{regime}")
+    m = load_into(P.MODELS.build(config={"name": "zero_dce_v", "down_size": 48}), sd).to(cuda_dev)
+    out = m.forward_core({"image": x.to(cuda_dev)})
+    assert list(out.keys()) == ["image_v", "image_v_lr", "adjust", "image_v_fixed_lr"]
+    assert torch.equal(out["image_v"].cpu(), outs["image_v"]) and torch.equal(out["image_v_lr"].cpu(), outs["image_v_lr"])
+    assert maxerr(out["adjust"], outs["adjust"]) <= TIGHT
+    assert maxerr(out["image_v_fixed_lr"], outs["image_v_fixed_lr"]) <= TIGHT
+
+
+@pytest.mark.parametrize("B,H,W,S", [(1, 37, 45, 16), (3, 64, 64, 64), (2, 30, 50, 96), (1, 1080, 1920, 256), (1, 5, 5, 1)])
+def test_zero_dce_v_core_shapes_vs_oracle(cuda_dev, B, H, W, S):
+    x = O.synthetic_lowlight(B, H, W, seed=90 + S)
+    sd = O.make_dce_state_dict(29, "stress", num_iters=15, in_channels=1)
+    m = load_into(P.ZeroDCEV(down_size=S), sd).to(cuda_dev)
+    out = m.forward_core({"image": x.to(cuda_dev)})
+    ref = O.zero_dce_v_core(x, sd, down_size=S, num_iters=15)
+    assert torch.equal(out["image_v"].cpu(), ref["image_v"]) and torch.equal(out["image_v_lr"].cpu(), ref["image_v_lr"])
+    assert out["adjust"].shape == (B, 15, S, S)
+    assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT and maxerr(out["image_v_fixed_lr"], ref["image_v_fixed_lr"]) <= TIGHT

@@ -114,3 +114,13 @@ def test_oracle_u8_wire_matches_reference_golden():
     assert torch.equal(f, torch.from_numpy(z["f32"]))
     assert torch.equal(O.f32nchw_to_u8hwc(image), torch.from_numpy(z["u8"]))
     assert (f != frames.permute(0, 3, 1, 2).float() / 255.0).any()   # the division is a different function
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_oracle_zero_dce_v_core_matches_reference_golden(golden, regime):
+    """tests/golden/dcev_*.npz = the first four outputs of the reference's own ZeroDCEV.forward (batch 1 per call)."""
+    x, sd, outs = golden(f"dcev_{regime}")
+    got = O.zero_dce_v_core(x, sd, down_size=48, num_iters=15)
+    assert list(got.keys()) == ["image_v", "image_v_lr", "adjust", "image_v_fixed_lr"]
+    for k in got:
+        assert torch.equal(got[k], outs[k]), k
