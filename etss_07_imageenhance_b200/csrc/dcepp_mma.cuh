@@ -22,26 +22,34 @@
 // so there is no per-thread halo addressing at all.  With 380 float2 per pair plane the (g, c) access pattern of the
 // 64-bit shared loads is bank-conflict free.
 //
-// Schedule.  The 6 x (B x tiles) output tiles form a single layer-major work list.  Each CTA has a producer warp
-// that draws tile numbers from a global counter, waits until the (up to) nine layer l-1 tiles under the tile's halo
-// are published (acquire), and streams the tile's 2 or 4 stages through a 4-slot ring (full / empty mbarriers) --
-// running up to a whole tile ahead of the 8 consumer warps, so tile-fetch, dependency and load latencies are off the
-// critical path.  There is no launch boundary or wave tail between layers.  Deadlock-free: a producer only waits on
-// tiles with smaller numbers, drawn earlier by CTAs that are resident (grid <= one resident wave) and whose consumers
-// never wait on anything but their own producer.
+// Schedule.  One CTA per SM holds two independent HALVES (a producer warp + 8 consumer warps each, own 4-slot ring and
+// barriers; 18 warps are allocated as 20, i.e. 96 registers per thread, like two 9-warp CTAs).  The 6 x (B x tiles)
+// output tiles form one work list ordered in frame groups (see below), layer-major inside a group.  A half's producer
+// draws tile numbers from a global counter, waits until the (up to) nine layer l-1 tiles under the tile's halo are
+// published (acquire), and streams the tile's 2 or 4 stages through the ring (full / empty mbarriers) -- running up
+// to a whole tile ahead of its consumers, so tile-fetch, dependency and load latencies are off the critical path.
+// Every stage carries, behind its feature-map box, the 2.8 KB weight blob of its k16 block (a bulk copy into the same
+// slot on the same barrier): a half holds no resident weights and changes layers from one tile to the next for
+// free.  A tile is published by the LAST consumer warp to finish it (shared-memory arrival counter, then a release
+// at GPU scope); there is no CTA barrier anywhere in the loop.  No launch boundary or wave tail between layers.
+// Deadlock-free: a producer only waits on tiles with smaller numbers, drawn earlier by halves that are resident
+// (grid <= one resident wave) and whose consumers never wait on anything but their own producer.
 //
-// Whole forward in one launch (b200_dcepp_forward, scale_factor >= 4).  The full-resolution pass (bilinear upsample,
-// align_corners=True, + the 8-iteration curve; zero_dcepp.py:198-203) is cut into blocks of `br` rows x `bw` pixels
-// x 3 planes of x that fit one ring stage and joins the same queue: a block of frame f becomes runnable when all
-// layer-7 tiles of f have published (per-frame counter, release / acquire), the producer fetches its x values with one
-// cp.async.bulk.tensor (up to four blocks = 92 KB in flight per CTA, so the HBM read stream never depends on
-// registers or occupancy), the consumer warps lerp the low-resolution map straight from L2 (18 scalar loads per
-// 4 pixels x 3 channels), run the curve and store `enhanced` / `adjust` with 128-bit streaming stores.  The net tiles
-// are ordered frame group by frame group (a group = enough frames to give every CTA a tile per layer), so the
-// HBM-bound blocks of early frames run on the same SMs, at the same time, as the FMA / shared-memory-bound tiles of
-// later frames: per SM one CTA prefers blocks (falls back to tiles while no frame is ready), the other prefers tiles
-// (falls back to blocks when the tiles are exhausted).  Nobody ever waits for a block: blocks are claimed by
-// compare-and-swap only once their frame is complete, so the deadlock argument above is unchanged.
+// Whole forward in one launch (b200_dcepp_forward; W % 4 == 0 and at most 64 low-res columns under a block).  The
+// full-resolution pass (bilinear upsample, align_corners=True, + the 8-iteration curve; zero_dcepp.py:198-203) is cut
+// into blocks of `br` rows x `bw` pixels x 3 planes of x that fit one ring slot together with the tile of the
+// low-resolution map under them, and joins the same queue: a block of frame f becomes runnable when all layer-7
+// tiles of f have published (per-frame counter, release / acquire); the producer fetches x AND the low-res tile with
+// two bulk tensor copies (up to four blocks = 96 KB in flight per half, so the HBM read stream never depends on
+// registers or occupancy), the consumer warps work from shared memory only, run the curve and store `enhanced` /
+// `adjust` with 128-bit streaming stores.  Blocks are claimed four at a time with one atomicAdd whether or not their
+// frame is ready; a claimed block whose frame is not ready stays pending while the producer goes on with tiles, so
+// nobody ever waits for a block and the deadlock argument above is unchanged.  One half per SM prefers blocks (falls
+// back to tiles while none is ready), the other prefers tiles (falls back to blocks when the tiles are exhausted).
+// Frame groups: tiles are ordered group by group so that the blocks of early groups can run while later groups are
+// still in the net; measured (profiles/r02_summary.md), what pays is a group of ~3.25 tiles per half and layer --
+// smaller groups start the blocks earlier but stall producers on predecessors still in flight, and the sum of
+// half-time (tiles + blocks) is conserved: both paths are latency-bound at 18 warps per SM.
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -161,9 +169,8 @@ __device__ __forceinline__ void mm_red_release_add(int* p, int v) {
 
 // sync words (caller's workspace, zeroed by layer 1's launch):
 //   [0] tile counter | [1] block counter (full-resolution pass) | [2] abort flag (a spin guard tripped) |
-//   [MM_SMCNT0 + smid % MM_NSMCNT] CTAs that have started on that SM (decides which of the two prefers blocks) |
 //   [MM_FDONE0 + b] layer-7 tiles of frame b published | [mm_flag0(B) + q] tile q of layers 2..6 published
-constexpr int MM_SMCNT0 = 32, MM_NSMCNT = 192, MM_FDONE0 = MM_SMCNT0 + MM_NSMCNT;
+constexpr int MM_FDONE0 = 32;
 __host__ __device__ inline int mm_flag0(int B) { return (MM_FDONE0 + B + 31) & ~31; }
 __host__ __device__ inline size_t mm_sync_words(int B, int h, int w) {
     const size_t tiles = (size_t)B * ((h + MM_TH - 1) / MM_TH) * ((w + MM_TW - 1) / MM_TW);
@@ -359,7 +366,7 @@ __device__ __forceinline__ void mm_tile(int t, const uint8_t* ring, uint64_t* fu
 // second (the order of the unfused kernel): per row, the lanes lerp the <= MM_VCOLS low-res columns under the block
 // vertically into the warp's strip of shared memory (column index clamped at w - 1, so the "+1" neighbour of the last
 // column is itself, as in ATen); a group then needs 2 shared loads per pixel and channel.  The slot goes back to the
-// producer as soon as a warp holds its last x values in registers and has built its last strip.
+// producer when the warp has read its last x values.
 template <bool ITERS8>
 __device__ __forceinline__ void mm_curve4(float4& xv, const float4& av, int iters) {
     // y <- y + a * (y*y - y) (zero_dcepp.py:203), ATen's rounding sequence, two pixels per instruction:
@@ -400,7 +407,6 @@ __device__ __forceinline__ void mm_apply_block(int t, const uint8_t* ring, uint6
     const int xb = cb & ~3;
     const int yb = tap_align_corners(Y0, ap.sh, h).i0;
     const int nrows = min(ap.br, ap.H - Y0);
-    const int rlast = warp + ((nrows - 1 - warp) & ~7);  // this warp's last row (< warp when it has none)
     const int npass = (gw + 31) >> 5;                    // 1 or 2
     for (int r = warp; r < nrows; r += 8) {
         const int Y = Y0 + r;
