@@ -337,15 +337,16 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ TcMaps tm) {
                         *reinterpret_cast<uint4*>(ol + ((3 ^ sw) << 4)) = make_uint4(pl[12], pl[13], pl[14], pl[15]);
                     }
                     fence_proxy_async_smem();
+                    // The other staging tile is written during the next row by threads that only passed THIS row's
+                    // barrier, the tile stored now during the row after: the previous row's store must have finished
+                    // reading before the issuing thread reaches this barrier.  The wait sits here, behind the row's
+                    // TMEM load and packing, rather than right after the store it waits for.
+                    if (q == 0 && lane == 0) tma_store_wait_read<0>();
                     named_bar_sync(1 + par, 128);
                     if (q == 0 && lane == 0) {
                         tma_store_4d(&tm.o, out_u32 + ob, 0, strip * TC_M, y, b);
                         if (X3) tma_store_4d(&tm.olo, out_u32 + ob + TC_OUT_BYTES, 0, strip * TC_M, y, b);
                         tma_store_commit();
-                        // the other tile is written during the next row by threads that only passed THIS row's
-                        // barrier, the tile stored now during the row after: this store's read must be over before
-                        // this thread reaches the next barrier
-                        tma_store_wait_read<0>();
                     }
                     if (++obuf == TC_NOUT) obuf = 0;
                 } else {
@@ -853,11 +854,11 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
                 *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
                 *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
                 fence_proxy_async_smem();
+                if (q == 0 && lane == 0) tma_store_wait_read<0>();  // the previous row's store (see the per-layer kernel)
                 named_bar_sync(1 + par, 128);
                 if (q == 0 && lane == 0) {  // the box is TP_VALID pixels: pixels 126 / 127 of the tile are not results
                     tma_store_4d(&tmo, out_u32 + ob, 0, x0, y0 + j, b);
                     tma_store_commit();
-                    tma_store_wait_read<0>();
                 }
                 if (++obuf == TC_NOUT) obuf = 0;
             }
