@@ -1027,6 +1027,436 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
 }
 
 // ------------------------------------------------------------------------------------------------
+// Fused e_conv1 + e_conv2 (zero_dce.py:176-177): layer A = conv3x3(x; 3 -> 32) + ReLU straight from the fp32 NCHW
+// input, layer B = conv3x3(A(x); 32 -> 32) + ReLU.  Same coupling as dce_tc_pair_kernel (layer A's rows go through a
+// shared-memory ring in the MMA operand layout into layer B's MMAs), but x1 is ALSO needed later (e_conv7 reads
+// cat(x1, x6)), so epilogue A's rows are bulk-stored to HBM from the very slot layer B reads: x1 is written once and
+// never read back by e_conv2; the separate layer-1 launch (epilogue-bound, 141 us per 4 frames) disappears.
+//   TMA producer     rows of x: fp32, 3 planes x 132 pixels (16-byte aligned start at or below x0 - 2), zero filled
+//                    outside the image -> x ring
+//   4 converter warps (one row each): x ring -> bf16 [128 px][K = 16] core-matrix tiles, k = dx*3 + c (the layer-1
+//                    operand of the per-layer kernel) -> A-tile ring
+//   MMA issuer A     ONE K = 16 MMA per input row (N = 96: three output rows) -> accumulator ring A
+//   epilogue A       TMEM -> bias + ReLU -> bf16 row (zeros outside the image) -> slot ring
+//   x1 store warp    bulk-stores every slot row the item owns to x1 (128 pixels from x0 - 1: neighbouring strips
+//                    overlap by two pixels and write identical values there)
+//   MMA issuer B     6 MMAs per row from the slot -> accumulator ring B
+//   epilogue B       TMEM -> bias + ReLU -> bf16 -> staging -> bulk store to x2 (126 pixels)
+// ------------------------------------------------------------------------------------------------
+constexpr int TF_XPX = 132;                       // pixels per x row box
+constexpr int TF_XBYTES = 3 * TF_XPX * 4;         // bytes per x row box (3 planes)
+constexpr int TF_XROW = (TF_XBYTES + 127) / 128 * 128;  // x ring slot pitch (bulk tensor copies land 128-byte aligned)
+constexpr int TF_NX = 8, TF_NA = 8, TF_NM = 4, TF_NB = 8;  // x rows, A tiles, layer-A output rows, accumulator blocks
+constexpr int TF_WA = 3072, TF_WB = 3 * 2 * 3072;
+constexpr int TF_THREADS = 16 * 32;  // epilogue A (0-3), epilogue B (4-7), converters (8-11), issuers A / B, TMA, x1 store
+constexpr int TF_BAR_BYTES = 1024;
+constexpr int TF_HEAD = TF_WA + TF_WB + 256 + TF_BAR_BYTES + 16;
+constexpr int TF_XRING = (TF_NX * TF_XROW + 1023) / 1024 * 1024;
+constexpr int TF_SMEM = TF_HEAD + 1024 + TC_NOUT * TC_OUT_BYTES + TF_NM * TC_SRC_STRIDE + TF_NA * TC_A1_BYTES + TF_XRING;
+static_assert(TF_SMEM <= 227 * 1024, "shared memory budget");
+
+struct TfArgs {
+    __nv_bfloat16* x1;      // e_conv1 output, NHWC bf16 [B,H,W,32] (strip 0 is written with plain stores)
+    const uint8_t* wpackA;  // packed block of e_conv1 (one 3 KB tile + 32 biases)
+    const uint8_t* wpackB;  // packed block of e_conv2 (18 KB + 32 biases)
+    int B, H, W, R, nseg, nstrip;
+};
+
+__global__ void __launch_bounds__(TF_THREADS, 1)
+dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tm1,
+                         const __grid_constant__ CUtensorMap tm2) {
+    constexpr int NB_SH = 3;
+    constexpr int TILE = 3072;
+    constexpr int W_EPB = 4, W_CONV = 8, W_MMA_A = 12, W_MMA_B = 13, W_TMA = 14;  // warp 15: x1 store
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* s_wA = smem_raw;
+    uint8_t* s_wB = smem_raw + TF_WA;
+    float* s_biasA = reinterpret_cast<float*>(smem_raw + TF_WA + TF_WB);
+    float* s_biasB = s_biasA + 32;
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(smem_raw + TF_WA + TF_WB + 256);
+    uint64_t* x_full = s_bar;                   // [NX] TMA complete_tx
+    uint64_t* x_empty = x_full + TF_NX;         // [NX] the converter warp of the row (1)
+    uint64_t* a_full = x_empty + TF_NX;         // [NA] the converter warp of the row (1)
+    uint64_t* a_empty = a_full + TF_NA;         // [NA] issuer A commit
+    uint64_t* accA_full = a_empty + TF_NA;      // [NB] issuer A commit
+    uint64_t* accA_empty = accA_full + TF_NB;   // [NB] epilogue A (128)
+    uint64_t* accB_full = accA_empty + TF_NB;   // [NB] issuer B commit
+    uint64_t* accB_empty = accB_full + TF_NB;   // [NB] epilogue B (128)
+    uint64_t* mid_full = accB_empty + TF_NB;    // [NM] epilogue A (128)
+    uint64_t* mid_empty = mid_full + TF_NM;     // [NM] issuer B commit + the x1 store warp (2)
+    static_assert((2 * TF_NX + 2 * TF_NA + 4 * TF_NB + 2 * TF_NM) * 8 <= TF_BAR_BYTES, "mbarrier area");
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + TF_WA + TF_WB + 256 + TF_BAR_BYTES);
+    const uint32_t out_u32 = (smem_u32(smem_raw + TF_HEAD) + 1023u) & ~1023u;  // swizzle phase = address bits 7-8
+    uint8_t* s_out = smem_raw + (out_u32 - smem_u32(smem_raw));
+    const uint32_t mid_u32 = out_u32 + TC_NOUT * TC_OUT_BYTES;
+    uint8_t* s_mid = smem_raw + (mid_u32 - smem_u32(smem_raw));
+    const uint32_t at_u32 = mid_u32 + TF_NM * TC_SRC_STRIDE;  // A tiles (no swizzle, core matrices)
+    uint8_t* s_at = smem_raw + (at_u32 - smem_u32(smem_raw));
+    const uint32_t xr_u32 = at_u32 + TF_NA * TC_A1_BYTES;     // x rows (fp32)
+    const float* s_xr = reinterpret_cast<const float*>(smem_raw + (xr_u32 - smem_u32(smem_raw)));
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int H = args.H, W = args.W, R = args.R;
+    const int n_items = args.B * args.nseg * args.nstrip;
+
+    // ---- one-time setup ----
+    {
+        const uint4* gA = reinterpret_cast<const uint4*>(args.wpackA);
+        const uint4* gB = reinterpret_cast<const uint4*>(args.wpackB);
+        uint4* sA = reinterpret_cast<uint4*>(s_wA);
+        uint4* sB = reinterpret_cast<uint4*>(s_wB);
+        for (int i = tid; i < TF_WA / 16; i += TF_THREADS) sA[i] = __ldg(gA + i);
+        for (int i = tid; i < TF_WB / 16; i += TF_THREADS) sB[i] = __ldg(gB + i);
+        if (tid < 32) s_biasA[tid] = __ldg(reinterpret_cast<const float*>(args.wpackA + TF_WA) + tid);
+        if (tid >= 32 && tid < 64) s_biasB[tid - 32] = __ldg(reinterpret_cast<const float*>(args.wpackB + TF_WB) + tid - 32);
+        fence_proxy_async_smem();  // B tiles are read through the async proxy
+    }
+    if (warp == W_MMA_A) {
+        if (lane == 0) {
+            for (int i = 0; i < TF_NX; ++i) {
+                mbar_init(&x_full[i], 1);
+                mbar_init(&x_empty[i], 1);
+            }
+            for (int i = 0; i < TF_NA; ++i) {
+                mbar_init(&a_full[i], 1);
+                mbar_init(&a_empty[i], 1);
+            }
+            for (int i = 0; i < TF_NB; ++i) {
+                mbar_init(&accA_full[i], 1);
+                mbar_init(&accA_empty[i], 128);
+                mbar_init(&accB_full[i], 1);
+                mbar_init(&accB_empty[i], 128);
+            }
+            for (int i = 0; i < TF_NM; ++i) {
+                mbar_init(&mid_full[i], 128);
+                mbar_init(&mid_empty[i], 2);
+            }
+            mbar_fence_init();
+        }
+        __syncwarp();
+        tmem_alloc(s_tmem, 512);
+    }
+    if (warp == W_TMA && lane == 0) {
+        tma_prefetch_desc(&tmx);
+        tma_prefetch_desc(&tm1);
+        tma_prefetch_desc(&tm2);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tbase = *s_tmem;
+    if (warp < 4) {  // every MMA accumulates: start from zeroed accumulator blocks
+        const uint32_t tl = tbase + ((uint32_t)(warp * 32) << 16);
+        for (int i = 0; i < 2 * TF_NB; ++i) tmem_zero32(tl + i * 32);
+        tc_wait_st();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+
+    // Per item: nB = layer-B output rows, layer A produces nB + 2 rows from nB + 4 rows of x.  Running row counters as
+    // in dce_tc_pair_kernel: ga = x rows (x ring, A-tile ring, accumulator ring A), gb = layer-A output rows.
+    auto item_geom = [&](int item, int& b, int& y0, int& x0, int& nB) {
+        const int strip = item % args.nstrip;
+        const int seg = (item / args.nstrip) % args.nseg;
+        b = item / (args.nstrip * args.nseg);
+        y0 = seg * R;
+        x0 = strip * TP_VALID;
+        nB = min(R, H - y0);
+    };
+
+    if (warp < W_EPB) {
+        // =========================== EPILOGUE A: accumulator ring A -> on-chip row slots ===========================
+        const int q = warp, m = q * 32 + lane;
+        const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+        float bias[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) bias[i] = s_biasA[i];
+        uint32_t ga = 0, gb = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            const int nA = nB + 2;
+            const int px = x0 - 1 + m;  // image column of this lane's pixel
+            const bool px_ok = px >= 0 && px < W;
+            for (int j = 0; j < nA + 2; ++j) {
+                const uint32_t g = ga + j;
+                const int p = TF_NB - 1 - (int)(g & (TF_NB - 1));
+                mbar_wait_guard(&accA_full[p], (g >> NB_SH) & 1);
+                if (j >= nA) {
+                    mbar_arrive(&accA_empty[p]);
+                    continue;
+                }
+                tc_fence_after();
+                uint32_t v[32];
+                tmem_ld32(tlane + p * 32, v);
+                tc_wait_ld();
+                tmem_zero32(tlane + p * 32);
+                tc_wait_st();
+                tc_fence_before();
+                mbar_arrive(&accA_empty[p]);
+                const int y = y0 - 1 + j;  // image row of this layer-A output row
+                const bool ok = px_ok && y >= 0 && y < H;
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float a0 = ok ? fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f) : 0.f;
+                    const float a1 = ok ? fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f) : 0.f;
+                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
+                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                }
+                const uint32_t gm = gb + j;
+                const int ms = (int)(gm % TF_NM);
+                if (gm >= TF_NM) mbar_wait_guard(&mid_empty[ms], ((gm / TF_NM) - 1) & 1);
+                uint8_t* op = s_mid + ms * TC_SRC_STRIDE + m * 64;
+                const int sw = (m >> 1) & 3;
+                *reinterpret_cast<uint4*>(op + ((0 ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(op + ((1 ^ sw) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
+                *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+                fence_proxy_async_smem();  // read by issuer B's MMAs and the x1 store through the async proxy
+                mbar_arrive(&mid_full[ms]);
+                if (x0 == 0 && j >= 1 && j < nA - 1 && px_ok) {  // strip 0: slot row 0 is column -1, see the x1 store warp
+                    uint4* gp = reinterpret_cast<uint4*>(args.x1 + (((size_t)b * H + y) * W + px) * 32);
+                    gp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    gp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    gp[2] = make_uint4(pk[8], pk[9], pk[10], pk[11]);
+                    gp[3] = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+                }
+            }
+            ga += nA + 2;
+            gb += nA;
+        }
+    } else if (warp < W_CONV) {
+        // =========================== EPILOGUE B: accumulator ring B -> x2 ===========================
+        const int q = warp & 3, m = q * 32 + lane;
+        const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16) + TF_NB * 32;
+        float bias[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) bias[i] = s_biasB[i];
+        uint32_t gb = 0, obuf = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            for (int j = 0; j < nB + 2; ++j) {
+                const uint32_t g = gb + j;
+                const int p = TF_NB - 1 - (int)(g & (TF_NB - 1));
+                mbar_wait_guard(&accB_full[p], (g >> NB_SH) & 1);
+                if (j >= nB) {
+                    mbar_arrive(&accB_empty[p]);
+                    continue;
+                }
+                tc_fence_after();
+                uint32_t v[32];
+                tmem_ld32(tlane + p * 32, v);
+                tc_wait_ld();
+                tmem_zero32(tlane + p * 32);
+                tc_wait_st();
+                tc_fence_before();
+                mbar_arrive(&accB_empty[p]);
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float a0 = fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f);
+                    const float a1 = fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f);
+                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
+                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                }
+                const uint32_t ob = obuf * TC_OUT_BYTES;
+                uint8_t* op = s_out + ob + m * 64;
+                const int sw = (m >> 1) & 3;
+                *reinterpret_cast<uint4*>(op + ((0 ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(op + ((1 ^ sw) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
+                *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+                fence_proxy_async_smem();
+                if (q == 0 && lane == 0) tma_store_wait_read<0>();  // the previous row's store (see the per-layer kernel)
+                named_bar_sync(1, 128);
+                if (q == 0 && lane == 0) {  // the box is TP_VALID pixels: pixels 126 / 127 of the tile are not results
+                    tma_store_4d(&tm2, out_u32 + ob, 0, x0, y0 + j, b);
+                    tma_store_commit();
+                }
+                if (++obuf == TC_NOUT) obuf = 0;
+            }
+            gb += nB + 2;
+        }
+    } else if (warp < W_MMA_A) {
+        // =========================== CONVERTERS: fp32 x rows -> bf16 [128 px][K = 16] tiles ===========================
+        // warp cw takes the rows g = cw mod 4 of this CTA's flattened x-row sequence; lane l builds tile rows l, l + 32,
+        // l + 64, l + 96: 9 conflict-free 32-bit shared loads (k = dx*3 + c <-> x[c][x0 - 2 + p + dx]) and two 128-bit
+        // stores per tile row (TC_A1_SBO keeps the eight-row groups on different banks)
+        const int cw = warp - W_CONV;
+        auto pk = [](float a, float b) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+            return *reinterpret_cast<uint32_t*>(&h);
+        };
+        uint32_t g = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            const int o = (x0 - 2) - ((x0 - 2) & ~3);  // the box starts at the 16-byte boundary at or below x0 - 2
+            for (int ri = 0; ri < nB + 4; ++ri, ++g) {
+                if ((int)(g & 3) != cw) continue;
+                const uint32_t xs = g % TF_NX, as = g % TF_NA;
+                mbar_wait_guard(&x_full[xs], (g / TF_NX) & 1);
+                if (g >= TF_NA) mbar_wait_guard(&a_empty[as], ((g / TF_NA) - 1) & 1);
+                const float* xr = s_xr + xs * (TF_XROW / 4) + o + lane;
+                uint8_t* tp = s_at + as * TC_A1_BYTES + (lane >> 3) * TC_A1_SBO + (lane & 7) * 16;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float e[9];  // e[dx*3 + c]
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx) e[dx * 3 + c] = xr[c * TF_XPX + i * 32 + dx];
+                    uint8_t* t = tp + i * 4 * TC_A1_SBO;
+                    *reinterpret_cast<uint4*>(t) = make_uint4(pk(e[0], e[1]), pk(e[2], e[3]), pk(e[4], e[5]), pk(e[6], e[7]));
+                    *reinterpret_cast<uint4*>(t + 128) = make_uint4(pk(e[8], 0.f), 0u, 0u, 0u);
+                }
+                fence_proxy_async_smem();  // the tile is read by issuer A's MMA through the async proxy
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(&a_full[as]);
+                    mbar_arrive(&x_empty[xs]);
+                }
+            }
+        }
+    } else if (warp == W_MMA_A) {
+        // =========================== MMA ISSUER A (x tiles -> e_conv1) ===========================
+        constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
+        constexpr uint32_t IDESC_FULL = IDESC0 | ((uint32_t)(96 >> 3) << 17);
+        const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_wA), 128, 256);
+        const uint64_t adesc0 = smem_desc_kmajor(at_u32, 128, TC_A1_SBO);
+        const bool leader = elect_one();
+        uint32_t g = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int seg = (item / args.nstrip) % args.nseg;
+            const int nout = min(R, H - seg * R) + 2;  // layer-A output rows
+            const int nin = nout + 2;
+            for (int ri = 0; ri < nin; ++ri, ++g) {
+                const uint32_t as = g % TF_NA;
+                const int pn = TF_NB - 1 - (int)(g & (TF_NB - 1));
+                mbar_wait_guard(&a_full[as], (g / TF_NA) & 1);
+                if (g >= TF_NB) mbar_wait_guard(&accA_empty[pn], ((g >> NB_SH) & 1) ^ 1);
+                tc_fence_after();
+                const uint64_t adesc = adesc0 + (uint64_t)((as * TC_A1_BYTES) >> 4);
+                if (leader) {
+                    int dy = max(0, ri - (nout - 1));
+                    const int dy_hi = min(2, ri);
+                    while (dy <= dy_hi) {  // segment borders / ring wrap: split into groups of output rows
+                        const int p0 = (pn + dy) & (TF_NB - 1);
+                        const int cnt = min(dy_hi - dy + 1, TF_NB - p0);
+                        const uint32_t idesc = cnt == 3 ? IDESC_FULL : (IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17));
+                        mma_ss(tbase + p0 * 32, adesc, bdesc0 + (uint64_t)((dy * 1024) >> 4), idesc, 1u);
+                        dy += cnt;
+                    }
+                    tc_commit(&a_empty[as]);
+                    if (ri >= 2) tc_commit(&accA_full[(pn + 2) & (TF_NB - 1)]);
+                    if (ri >= nout) tc_commit(&accA_full[pn]);  // block unused this lap: complete its phase
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp == W_MMA_B) {
+        // =========================== MMA ISSUER B (e_conv1 rows on chip -> e_conv2) ===========================
+        constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
+        constexpr uint32_t IDESC_FULL = IDESC0 | ((uint32_t)(96 >> 3) << 17);
+        const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_wB), 128, 256);
+        const uint64_t mdesc0 = smem_desc_sw64(mid_u32);
+        const bool leader = elect_one();
+        uint32_t g = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int seg = (item / args.nstrip) % args.nseg;
+            const int nout = min(R, H - seg * R);  // layer-B output rows
+            const int nin = nout + 2;
+            for (int ri = 0; ri < nin; ++ri, ++g) {
+                const uint32_t ms = g % TF_NM;
+                const int pn = TF_NB - 1 - (int)(g & (TF_NB - 1));
+                mbar_wait_guard(&mid_full[ms], (g / TF_NM) & 1);
+                if (g >= TF_NB) mbar_wait_guard(&accB_empty[pn], ((g >> NB_SH) & 1) ^ 1);
+                tc_fence_after();
+                // layer-B pixel m = image column x0 + m reads slot row m + dx (slot row 0 = x0 - 1)
+                const uint64_t mdesc = mdesc0 + (uint64_t)((ms * TC_SRC_STRIDE) >> 4);
+                if (leader) {
+                    int dy = max(0, ri - (nout - 1));
+                    const int dy_hi = min(2, ri);
+                    while (dy <= dy_hi) {
+                        const int p0 = (pn + dy) & (TF_NB - 1);
+                        const int cnt = min(dy_hi - dy + 1, TF_NB - p0);
+                        const uint32_t idesc = cnt == 3 ? IDESC_FULL : (IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17));
+                        const uint32_t d = tbase + (TF_NB + p0) * 32;
+                        const uint64_t bd = bdesc0 + (uint64_t)((dy * 1024) >> 4);
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx)
+#pragma unroll
+                            for (int kc = 0; kc < 2; ++kc)
+                                mma_ss(d, mdesc + (uint64_t)((dx * 64 + kc * 32) >> 4),
+                                       bd + (uint64_t)(((dx * 2 + kc) * TILE) >> 4), idesc, 1u);
+                        dy += cnt;
+                    }
+                    tc_commit(&mid_empty[ms]);
+                    if (ri >= 2) tc_commit(&accB_full[(pn + 2) & (TF_NB - 1)]);
+                    if (ri >= nout) tc_commit(&accB_full[pn]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp == W_TMA) {
+        // =========================== TMA PRODUCER (rows of x, fp32 planes) ===========================
+        const bool leader = elect_one();
+        uint32_t g = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            const int xs0 = (x0 - 2) & ~3;
+            for (int ri = 0; ri < nB + 4; ++ri, ++g) {
+                const uint32_t xs = g % TF_NX;
+                if (g >= TF_NX) mbar_wait_guard(&x_empty[xs], ((g / TF_NX) - 1) & 1);
+                if (leader) {
+                    mbar_arrive_expect_tx(&x_full[xs], TF_XBYTES);
+                    tma_load_4d(xr_u32 + xs * TF_XROW, &tmx, xs0, y0 - 2 + ri, 0, b, &x_full[xs]);
+                }
+                __syncwarp();
+            }
+        }
+    } else {
+        // =========================== x1 STORE (slot rows the item owns -> HBM) ===========================
+        const bool leader = elect_one();
+        uint32_t g = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            const int nA = nB + 2;
+            for (int j = 0; j < nA; ++j, ++g) {
+                const uint32_t ms = g % TF_NM;
+                mbar_wait_guard(&mid_full[ms], (g / TF_NM) & 1);
+                if (leader) {
+                    // rows 0 / nA - 1 are the halo rows: the neighbouring segments own them; a bulk tensor STORE that starts
+                    // at a negative coordinate is an illegal instruction (loads may): strip 0 is stored by epilogue A
+                    if (j >= 1 && j < nA - 1 && x0 > 0) {
+                        tma_store_4d(&tm1, mid_u32 + ms * TC_SRC_STRIDE, 0, x0 - 1, y0 - 1 + j, b);
+                        tma_store_commit();
+                        tma_store_wait_read<0>();
+                    }
+                    mbar_arrive(&mid_empty[ms]);
+                }
+                __syncwarp();
+            }
+        }
+        if (leader) tma_store_wait<0>();  // shared memory outlives the stores
+    }
+
+    // ---- teardown ----
+    if (warp == W_EPB && lane == 0) tma_store_wait<0>();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == W_MMA_A) {
+        tc_fence_after();
+        tmem_dealloc(tbase, 512);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
 static size_t tc_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -1108,6 +1538,45 @@ static int tc_launch_pair(const TcArgs& a, const void* src, __nv_bfloat16* dst, 
     return launch_status();
 }
 
+// e_conv1 + e_conv2 in one launch: x (fp32 NCHW, W % 4 == 0, 16-byte aligned) -> x1 and x2
+static int tc_launch_first_pair(const TcArgs& a, __nv_bfloat16* x1, __nv_bfloat16* x2, const uint8_t* wA, const uint8_t* wB,
+                                cudaStream_t s) {
+    auto kern = dce_tc_first_pair_kernel;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TF_SMEM) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return B200_ERR_LAUNCH;
+    }
+    tma_encode_fn enc = tma_encoder();
+    if (!enc) return B200_ERR_LAUNCH;
+    CUtensorMap mx, m1, m2;
+    memset(&mx, 0, sizeof(mx));
+    memset(&m1, 0, sizeof(m1));
+    memset(&m2, 0, sizeof(m2));
+    {  // x as a 4-D fp32 tensor (x, y, c, b); box = 132 pixels of one row in all three planes; zero fill outside
+        const cuuint64_t dims[4] = {(cuuint64_t)a.W, (cuuint64_t)a.H, 3, (cuuint64_t)a.B};
+        const cuuint64_t strides[3] = {(cuuint64_t)a.W * 4, (cuuint64_t)a.H * a.W * 4, (cuuint64_t)a.H * a.W * 12};
+        const cuuint32_t box[4] = {TF_XPX, 1, 3, 1};
+        const cuuint32_t estr[4] = {1, 1, 1, 1};
+        if (enc(&mx, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(a.x), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return B200_ERR_LAUNCH;
+    }
+    int rc;
+    if ((rc = tc_make_map(&m1, x1, a.B, a.H, a.W, TC_M))) return rc;
+    if ((rc = tc_make_map(&m2, x2, a.B, a.H, a.W, TP_VALID))) return rc;
+    TfArgs t{};
+    t.x1 = x1;
+    t.wpackA = wA;
+    t.wpackB = wB;
+    t.B = a.B, t.H = a.H, t.W = a.W, t.R = a.R, t.nseg = a.nseg;
+    t.nstrip = (a.W + TP_VALID - 1) / TP_VALID;
+    const long long items = (long long)t.B * t.nseg * t.nstrip;
+    const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
+    kern<<<grid, TF_THREADS, TF_SMEM, s>>>(t, mx, m1, m2);
+    return launch_status();
+}
+
 size_t dce_tc_packed_bytes(int precision, int iters) {
     if (iters < 1 || iters > 8) return 0;
     if (precision == B200_PREC_BF16) return (size_t)TC_PACKED_BYTES;
@@ -1157,10 +1626,18 @@ static int dce_tc_forward_t(const float* x, const void* packed, float* adjust, f
         a.dst = (__nv_bfloat16*)dst.hi;
         a.wpack = pk + tc_layer_offset(l, X3);
     };
-    layer(0, x1);
-    if ((rc = tc_launch<1, true, false, X3>(a, none, none, x1, s))) return rc;
-    layer(1, x2);
-    if ((rc = tc_launch<1, false, false, X3>(a, x1, none, x2, s))) return rc;
+    // B200DCE_DCE_FIRST_PAIR=0 (tuning / A-B aid): e_conv1 and e_conv2 as two launches
+    const char* fe = getenv("B200DCE_DCE_FIRST_PAIR");
+    if (!X3 && (W & 3) == 0 && ((uintptr_t)x & 15) == 0 && !(fe && fe[0] == '0')) {
+        if ((rc = tc_launch_first_pair(a, (__nv_bfloat16*)x1.hi, (__nv_bfloat16*)x2.hi, pk + tc_layer_offset(0),
+                                       pk + tc_layer_offset(1), s)))
+            return rc;
+    } else {
+        layer(0, x1);
+        if ((rc = tc_launch<1, true, false, X3>(a, none, none, x1, s))) return rc;
+        layer(1, x2);
+        if ((rc = tc_launch<1, false, false, X3>(a, x1, none, x2, s))) return rc;
+    }
     layer(2, x3);
     if ((rc = tc_launch<1, false, false, X3>(a, x2, none, x3, s))) return rc;
     // B200DCE_DCE_PAIR=0 (tuning / A-B aid): e_conv4 and e_conv5 as two launches with x4 in HBM

@@ -5,6 +5,9 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#ifdef B200_MBAR_DEBUG
+#include <stdio.h>
+#endif
 
 namespace b200 {
 namespace tc {
@@ -71,7 +74,15 @@ __device__ __forceinline__ void mbar_wait_guard(uint64_t* bar, uint32_t parity) 
     const long long t0 = clock64();
     uint32_t n = 0;
     while (!mbar_try_wait_hint(bar, parity, 20000u)) {
+#ifdef B200_MBAR_DEBUG  // deadlock hunting: name the barrier and run on (the results are garbage, the launch ends)
+        if ((++n & 63u) == 0 && clock64() - t0 > 100000000LL) {
+            printf("mbar timeout: block %d warp %d barrier word %u parity %u\n", (int)blockIdx.x, (int)(threadIdx.x >> 5),
+                   (smem_u32(bar) & 1023u) >> 3, parity);
+            return;
+        }
+#else
         if ((++n & 63u) == 0 && clock64() - t0 > 4000000000LL) __trap();
+#endif
     }
 }
 

@@ -264,6 +264,19 @@ def test_dce_bf16_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
     assert O.psnr(out["enhanced"].cpu(), ref["enhanced"]) >= 50.0   # the contract (BASELINE.json north_star)
 
 
+@pytest.mark.parametrize("H,W,B", [(83, 256, 3), (120, 380, 1), (37, 252, 2), (3, 4, 1), (200, 1000, 1)])
+def test_dce_bf16_fused_launches_equal_per_layer_launches(cuda_dev, monkeypatch, H, W, B):
+    # e_conv1 + e_conv2 and e_conv4 + e_conv5 as fused launches (126-pixel strips, rows handed over on chip) against
+    # the seven per-layer launches: the same MMAs in the same order per pixel -> bit-identical
+    x = O.synthetic_lowlight(B, H, W, seed=77).to(cuda_dev)
+    m = load_into(P.ZeroDCE_RE(precision="bf16"), O.make_dce_state_dict(29, "stress")).to(cuda_dev)
+    fused = m({"image": x})
+    monkeypatch.setenv("B200DCE_DCE_FIRST_PAIR", "0")
+    monkeypatch.setenv("B200DCE_DCE_PAIR", "0")
+    plain = m({"image": x})
+    assert torch.equal(fused["enhanced"], plain["enhanced"]) and torch.equal(fused["adjust"], plain["adjust"])
+
+
 def test_dce_bf16_zero_weights_identity_1080p(cuda_dev):
     sd = {k: torch.zeros_like(v) for k, v in O.make_dce_state_dict(1).items()}
     m = load_into(P.ZeroDCE_RE(precision="bf16"), sd).to(cuda_dev)
