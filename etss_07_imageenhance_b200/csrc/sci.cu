@@ -2,19 +2,25 @@
 // EnhanceNetwork.forward :36-45, layers=1, channels=3, BatchNorm2d eval) as ONE fused pass:
 //   fea1 = relu(conv3x3(x));  fea2 = fea1 + relu(bn(conv3x3(fea1)));  fea3 = sigmoid(conv3x3(fea2));
 //   illu = clamp(fea3 + x, 1e-4, 1);  r = clamp(x / illu, 0, 1)
-// CTA tile 24x32 output pixels; the three stacked 3x3 layers are evaluated on shrinking halo regions held in
-// shared memory (x: 30x38, fea1: 28x36, fea2: 26x34), so x is read once from HBM and illu / r written once.
+// CTA tile 24x64 output pixels; the three stacked 3x3 layers are evaluated on shrinking halo regions held in
+// shared memory (x: 30x70, fea1: 28x68, fea2: 28x66), so x is read once from HBM and illu / r written once.
 //
-// The work is 3 x 81 MAC per position on the fp32 pipe (~580 FLOP per output pixel with the halo recompute): the
-// kernel is bound by the packed-FMA pipe, not by HBM, so the inner loop is built to be (almost) nothing but FFMA2:
-//   * a thread computes FOUR vertically adjacent positions x 3 output channels; every FFMA2 carries one weight (scalar
-//     broadcast from a uniform register; all 252 weights travel as a by-value kernel parameter in the constant bank)
-//     times a vertical value pair (rows r, r+1);
-//   * fea1 / fea2 are stored ROW-PAIR INTERLEAVED, twice: copy A holds (row 2p, 2p+1), copy B holds (row 2p+1, 2p+2),
-//     so all five pairs a 4-row item needs per (channel, column) are aligned 64-bit shared loads -- no register moves
-//     to assemble operands (the row-major version spent as many MOVs as FFMA2s);
-//   * item counts per layer (7 x 36, 7 x 34, 6 x 32) are just under the 256 threads: one round per layer, a warp
-//     per row group so that its 64-bit shared accesses are conflict free.
+// The work is 3 x 81 MAC per position on the fp32 pipe (~560 FLOP per output pixel with the halo recompute): the
+// kernel is bound by the packed-FMA pipe and by instruction issue, not by HBM, so the inner loop is built to be
+// (almost) nothing but FFMA2, with as few other instructions per FFMA2 as the data flow allows:
+//   * all three planes (x, fea1, fea2) are stored ROW-PAIR INTERLEAVED: element [pair row p][column] is the float2
+//     (row 2p, row 2p+1), so a vertical pair of inputs is one aligned 64-bit operand of an FFMA2 and two adjacent
+//     columns are one 128-bit shared access;
+//   * a thread computes an item of FOUR rows x TWO columns x 3 output channels (324 FFMA2 per layer): per input
+//     channel six 128-bit loads bring the 6 x 4 input window; the pairs that start on an odd row (r+1, r+2) are put
+//     together in registers (two moves each -- a second, odd-aligned copy of the planes would save the moves and cost
+//     twice the shared memory, i.e. half the resident warps);
+//   * every FFMA2 carries one weight as a scalar broadcast from a uniform register; the 252 weights travel as a by-value
+//     kernel parameter in the constant bank, reordered on the host to the order the loop consumes them so that they
+//     arrive as 128-bit uniform loads;
+//   * item counts per layer (7 x 34, 7 x 33, 6 x 32) are just under the 256 threads: one round per layer, a warp per
+//     row group (its 128-bit shared accesses are consecutive: conflict free), the last warp takes the two / one
+//     left-over column pairs of every group.
 #include <math.h>
 
 #include "common.cuh"
@@ -22,200 +28,321 @@
 
 namespace b200 {
 
+// b200_sci_pack_weights_host's layout (the ABI: OIHW as in the state dict, BatchNorm folded into w2 / b2)
 struct SciWeights {
     float w1[81], b1[3];  // in_conv.0
     float w2[81], b2[3];  // conv.0 with BatchNorm folded in
     float w3[81], b3[3];  // out_conv.0
 };
 static_assert(sizeof(SciWeights) == B200_SCI_PACKED_FLOATS * sizeof(float), "packed size");
+// the kernel parameter: each layer's weights as [ci][kx][co][ky] (the order the loop consumes them), every input
+// channel's 27 padded to 28 floats so that the loop over ci can stay rolled with 128-bit uniform loads
+constexpr int SCI_WCI = 28, SCI_WL = 3 * SCI_WCI + 4;  // per layer: 3 x 28 weights, 3 biases (+1)
+struct __align__(16) SciKernelWeights {
+    float w[3][SCI_WL];
+};
 
-constexpr int S_TH = 24, S_TW = 32;
-constexpr int SX_H = S_TH + 6, SX_W = 40;  // 30 rows x (4 + 32 + 4) columns: image column x0 - 4 at column 0, so every
-                                           // row is ten 16-byte cp.async chunks
-constexpr int S1_G = 7, S1_W = S_TW + 4;   // fea1: rows y0-2 .. y0+25 (7 groups of 4), columns x0-2 .. x0+33
-constexpr int S2_G = 7, S2_W = S_TW + 2;   // fea2: rows y0-1 .. y0+26 (the last two are never read), columns x0-1 .. x0+32
-constexpr int S3_G = S_TH / 4;
-constexpr int S1_RP = 2 * S1_G + 1, S2_RP = 2 * S2_G + 1;  // row pairs per plane (+1: the B copy's last half pair, and
-                                                            // fea2's unused rows read one pair past fea1's end)
-// fea2 reuses the x tile's bytes (x is only read by layer 1; the epilogue re-reads its 12 centre values from L2)
-constexpr int SCI_SX_BYTES = 4 * 3 * SX_H * SX_W, SCI_S2_BYTES = 8 * 2 * 3 * S2_RP * S2_W;
-constexpr int SCI_SMEM = (SCI_SX_BYTES > SCI_S2_BYTES ? SCI_SX_BYTES : SCI_S2_BYTES) + 8 * 2 * 3 * S1_RP * S1_W;
+constexpr int S_TH = 24, S_TW = 64;
+constexpr int SX_RP = 15, SX_W = S_TW + 6;  // x:    rows y0-3 .. y0+26 as 15 row pairs, columns x0-3 .. x0+66
+constexpr int S1_RP = 15, S1_W = S_TW + 4;  // fea1: rows y0-2 .. y0+25 (+ one pair never written, read by the two
+                                            //       fea2 rows that feed nothing), columns x0-2 .. x0+65
+constexpr int S2_RP = 14, S2_W = S_TW + 2;  // fea2: rows y0-1 .. y0+26, columns x0-1 .. x0+64
+constexpr int S1_G = 7, S2_G = 7, S3_G = S_TH / 4;  // row groups (4 rows) per layer
+constexpr int SCI_SX_BYTES = 8 * 3 * SX_RP * SX_W, SCI_S1_BYTES = 8 * 3 * S1_RP * S1_W, SCI_S2_BYTES = 8 * 3 * S2_RP * S2_W;
+// fea2 reuses the x planes' bytes (x is only read by layer 1); 50 KB: four CTAs per SM.  During layer 3 the dead fea1
+// region holds each thread's own x values for the epilogue (fetched by cp.async under the conv)
+constexpr int SCI_SMEM = (SCI_SX_BYTES > SCI_S2_BYTES ? SCI_SX_BYTES : SCI_S2_BYTES) + SCI_S1_BYTES;
+static_assert(12 * 32 * S3_G * 8 <= SCI_S1_BYTES, "layer 3's x slots fit the fea1 region");
+static_assert(SCI_SX_BYTES % 16 == 0 && SCI_S1_BYTES % 16 == 0 && (SX_W * 8) % 16 == 0 && (S1_W * 8) % 16 == 0 && (S2_W * 8) % 16 == 0, "128-bit rows");
 
-// four vertically adjacent outputs (rows b .. b+3 as two pairs) x 3 channels from row-pair planes:
-//   a = copy A at pair row b/2 (rows b, b+1), b2 = copy B at pair row b/2 (rows b+1, b+2); planes are PLANE float2 apart
-template <int W_IN, int PLANE>
-__device__ __forceinline__ void conv3_quad(const float2* __restrict__ a, const float2* __restrict__ b2, const float* w,
-                                           const float* bias, float2 out[3][2]) {
+// One item: output rows b .. b+3 (two row pairs) x columns j, j+1 x 3 channels from a row-pair plane whose origin lies
+// one row above and one column left of the output's origin.  `in` points at (pair row b/2, column j) of channel 0;
+// W_IN / PLANE in float2 units.  out[col][co][pair].  The loop over the input channel stays ROLLED: the body (144 FMA
+// instructions) then lives in the instruction cache -- fully unrolled, the three layers are 50 KB of straight-line code
+// and a fifth of all issue slots went to instruction fetch.
+template <int W_IN, int PLANE, bool RESIDUAL>
+__device__ __forceinline__ void conv3_item(const float2* __restrict__ in, const float* __restrict__ w, float2 out[2][3][2],
+                                           float2 res[2][3][2]) {
 #pragma unroll
-    for (int co = 0; co < 3; ++co) out[co][0] = out[co][1] = make_float2(bias[co], bias[co]);
+    for (int col = 0; col < 2; ++col)
 #pragma unroll
+        for (int co = 0; co < 3; ++co) out[col][co][0] = out[col][co][1] = make_float2(w[3 * SCI_WCI + co], w[3 * SCI_WCI + co]);
+    // RESIDUAL (layer 2 only): unrolled, so that res[col][ci][pair] = the input at the output's own position (rows b+1 ..
+    // b+4, columns j+1, j+2) is taken from the registers of iteration ci
+#pragma unroll(RESIDUAL ? 3 : 1)
     for (int ci = 0; ci < 3; ++ci) {
+        float2 a[3][4];  // a[t][k] = rows (b+2t, b+2t+1) at column j+k
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-            const float2 a0 = a[ci * PLANE + kx], a1 = a[ci * PLANE + W_IN + kx], a2 = a[ci * PLANE + 2 * W_IN + kx];
-            const float2 b0 = b2[ci * PLANE + kx], b1 = b2[ci * PLANE + W_IN + kx];
+        for (int t = 0; t < 3; ++t) {
+            const float4 lo = *reinterpret_cast<const float4*>(in + ci * PLANE + t * W_IN);
+            const float4 hi = *reinterpret_cast<const float4*>(in + ci * PLANE + t * W_IN + 2);
+            a[t][0] = make_float2(lo.x, lo.y), a[t][1] = make_float2(lo.z, lo.w);
+            a[t][2] = make_float2(hi.x, hi.y), a[t][3] = make_float2(hi.z, hi.w);
+        }
+        if (RESIDUAL) {
 #pragma unroll
-            for (int co = 0; co < 3; ++co) {
-                const float w0 = w[((co * 3 + ci) * 3 + 0) * 3 + kx], w1 = w[((co * 3 + ci) * 3 + 1) * 3 + kx],
-                            w2 = w[((co * 3 + ci) * 3 + 2) * 3 + kx];
-                out[co][0] = __ffma2_rn(make_float2(w0, w0), a0, out[co][0]);
-                out[co][1] = __ffma2_rn(make_float2(w0, w0), a1, out[co][1]);
-                out[co][0] = __ffma2_rn(make_float2(w1, w1), b0, out[co][0]);
-                out[co][1] = __ffma2_rn(make_float2(w1, w1), b1, out[co][1]);
-                out[co][0] = __ffma2_rn(make_float2(w2, w2), a1, out[co][0]);
-                out[co][1] = __ffma2_rn(make_float2(w2, w2), a2, out[co][1]);
+            for (int col = 0; col < 2; ++col) {
+                res[col][ci][0] = make_float2(a[0][1 + col].y, a[1][1 + col].x);
+                res[col][ci][1] = make_float2(a[1][1 + col].y, a[2][1 + col].x);
             }
         }
-    }
-}
-
-// the same from a row-major plane (the x tile): `in` points at row b, left tap column, channel 0
-template <int IN_W, int IN_PLANE>
-__device__ __forceinline__ void conv3_quad_rowmajor(const float* __restrict__ in, const float* w, const float* bias,
-                                                    float2 out[3][2]) {
-#pragma unroll
-    for (int co = 0; co < 3; ++co) out[co][0] = out[co][1] = make_float2(bias[co], bias[co]);
-#pragma unroll
-    for (int ci = 0; ci < 3; ++ci) {
+        const float* wc = w + ci * SCI_WCI;
 #pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
-            float v[6];
 #pragma unroll
-            for (int rr = 0; rr < 6; ++rr) v[rr] = in[ci * IN_PLANE + rr * IN_W + kx];
+            for (int co = 0; co < 3; ++co) {
+                const float* wp = wc + (kx * 3 + co) * 3;
+                const float2 w0 = make_float2(wp[0], wp[0]), w2 = make_float2(wp[2], wp[2]);
+                const float w1 = wp[1];
 #pragma unroll
-            for (int ky = 0; ky < 3; ++ky) {
-                const float2 p0 = make_float2(v[ky], v[ky + 1]), p1 = make_float2(v[ky + 2], v[ky + 3]);
-#pragma unroll
-                for (int co = 0; co < 3; ++co) {
-                    const float wv = w[((co * 3 + ci) * 3 + ky) * 3 + kx];
-                    out[co][0] = __ffma2_rn(make_float2(wv, wv), p0, out[co][0]);
-                    out[co][1] = __ffma2_rn(make_float2(wv, wv), p1, out[co][1]);
+                for (int col = 0; col < 2; ++col) {
+                    const int k = col + kx;
+                    // ky = 0 / 2: the input pairs are aligned row pairs -> FFMA2; ky = 1: the pair (b+1, b+2) straddles
+                    // two row pairs -> two scalar FFMAs on the halves (the same FMA-lane cycles, no register moves)
+                    out[col][co][0] = __ffma2_rn(w0, a[0][k], out[col][co][0]);
+                    out[col][co][1] = __ffma2_rn(w0, a[1][k], out[col][co][1]);
+                    out[col][co][0].x = fmaf(w1, a[0][k].y, out[col][co][0].x);
+                    out[col][co][0].y = fmaf(w1, a[1][k].x, out[col][co][0].y);
+                    out[col][co][1].x = fmaf(w1, a[1][k].y, out[col][co][1].x);
+                    out[col][co][1].y = fmaf(w1, a[2][k].x, out[col][co][1].y);
+                    out[col][co][0] = __ffma2_rn(w2, a[1][k], out[col][co][0]);
+                    out[col][co][1] = __ffma2_rn(w2, a[2][k], out[col][co][1]);
                 }
             }
         }
     }
 }
 
-// store rows b .. b+3 (b = 4 * gi) of one channel at column c into the two row-pair copies
-template <int W_OUT>
-__device__ __forceinline__ void store_quad(float2* __restrict__ A, float2* __restrict__ B, int gi, int c, float o0,
-                                           float o1, float o2, float o3) {
-    A[(2 * gi) * W_OUT + c] = make_float2(o0, o1);
-    A[(2 * gi + 1) * W_OUT + c] = make_float2(o2, o3);
-    B[(2 * gi) * W_OUT + c] = make_float2(o1, o2);
-    if (gi > 0) B[(2 * gi - 1) * W_OUT + c].y = o0;
-    B[(2 * gi + 1) * W_OUT + c].x = o3;
+// sigmoid and x / illu on the SFU: ex2.approx / rcp.approx (~2 ulp), flush-to-zero forms -- the default forms wrap
+// every MUFU in a denormal-range fix-up (two multiplies and a compare each), the IEEE-rounded ones cost as many
+// FMA-pipe instructions per pixel as a whole conv layer; the contract is 1e-3.  Neither operand range comes near a
+// denormal: 1 + 2^t >= 1, illu is clamped to [1e-4, 1].
+__device__ __forceinline__ float sfu_ex2(float v) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+    return r;
+}
+__device__ __forceinline__ float sfu_rcp(float v) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+    return r;
 }
 
-// item (row group gi, column cc) of thread t for a layer with G groups of COLS >= 32 columns: warp gi takes columns
-// 0..31 of its group (consecutive lanes = consecutive columns: conflict-free 64-bit shared accesses), the last warp
-// takes the COLS - 32 leftover columns of every group
-template <int G, int COLS>
-__device__ __forceinline__ bool sci_item(int t, int& gi, int& cc) {
-    static_assert(G <= 7 && COLS >= 32 && (COLS - 32) * G <= 32, "one round of 8 warps");
+// item (row group gi, column pair ci2) of thread t for a layer with G row groups of NP >= 32 column pairs: warp gi takes
+// pairs 0..31 of its group, the last warp takes the NP - 32 left-over pairs of every group
+template <int G, int NP>
+__device__ __forceinline__ bool sci_item(int t, int& gi, int& ci2) {
+    static_assert(G <= 7 && NP >= 32 && (NP - 32) * G <= 32, "one round of 8 warps");
     const int warp = t >> 5, lane = t & 31;
     if (warp < G) {
-        gi = warp, cc = lane;
+        gi = warp, ci2 = lane;
         return true;
     }
-    if (COLS == 32 || warp != 7 || lane >= (COLS - 32) * G) return false;
-    gi = lane / (COLS - 32 > 0 ? COLS - 32 : 1), cc = 32 + lane % (COLS - 32 > 0 ? COLS - 32 : 1);
+    if (NP == 32 || warp != 7 || lane >= (NP - 32) * G) return false;
+    gi = lane / (NP - 32 > 0 ? NP - 32 : 1), ci2 = 32 + lane % (NP - 32 > 0 ? NP - 32 : 1);
     return true;
 }
 
-__global__ void __launch_bounds__(256, 4)
+// relu / optional residual / (MASKED: zero outside the image = the next conv's zero padding), then the two row pairs of
+// the two columns of channel c as two 128-bit stores; (yy, xx) = image position of the item's first row / column
+template <int W_OUT, int RP, bool RESIDUAL, bool MASKED>
+__device__ __forceinline__ void sci_store_item(float2* __restrict__ plane, int gi, int j, const float2 out[2][3][2],
+                                               const float2 res[2][3][2], int yy, int xx, int H, int W) {
+    bool rin[4], cin[2];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) rin[q] = !MASKED || (yy + q >= 0 && yy + q < H);
+#pragma unroll
+    for (int col = 0; col < 2; ++col) cin[col] = !MASKED || (xx + col >= 0 && xx + col < W);
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int pr = 0; pr < 2; ++pr) {
+            float v[2][2];
+#pragma unroll
+            for (int col = 0; col < 2; ++col) {
+                float e0 = fmaxf(out[col][c][pr].x, 0.f), e1 = fmaxf(out[col][c][pr].y, 0.f);
+                if (RESIDUAL) e0 += res[col][c][pr].x, e1 += res[col][c][pr].y;
+                v[col][0] = cin[col] && rin[2 * pr] ? e0 : 0.f;
+                v[col][1] = cin[col] && rin[2 * pr + 1] ? e1 : 0.f;
+            }
+            *reinterpret_cast<float4*>(plane + (c * RP + 2 * gi + pr) * W_OUT + j) =
+                make_float4(v[0][0], v[0][1], v[1][0], v[1][1]);
+        }
+}
+
+__global__ void __launch_bounds__(256, 3)
 sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* __restrict__ r,
-                 const __grid_constant__ SciWeights wt, int H, int W) {
-    extern __shared__ __align__(16) float sci_smem[];
-    float* sx = sci_smem;                                                     // [3][SX_H][SX_W]
-    float2* s2a = reinterpret_cast<float2*>(sci_smem);                        // [3][S2_RP][S2_W], over the dead x tile
-    float2* s2b = s2a + 3 * S2_RP * S2_W;
-    float2* s1a = reinterpret_cast<float2*>(sci_smem + (SCI_SMEM - 8 * 2 * 3 * S1_RP * S1_W) / 4);  // [3][S1_RP][S1_W]
-    float2* s1b = s1a + 3 * S1_RP * S1_W;
+                 const __grid_constant__ SciKernelWeights wt, int H, int W) {
+    extern __shared__ __align__(16) float2 sci_smem[];
+    float2* sx = sci_smem;                                   // [3][SX_RP][SX_W]
+    float2* s2 = sci_smem;                                   // [3][S2_RP][S2_W], over the dead x planes
+    float2* s1 = sci_smem + (SCI_SMEM - SCI_S1_BYTES) / 8;   // [3][S1_RP][S1_W]
     const int t = threadIdx.x;
     const int b = blockIdx.z;
     const int y0 = blockIdx.y * S_TH, x0 = blockIdx.x * S_TW;
     const size_t plane = (size_t)H * W;
     const float* xb = x + (size_t)b * 3 * plane;
-
-    {   // x halo tile via cp.async (all loads in flight at once); zero fill outside the image = the conv's zero padding
-        const uint32_t sh = tc::smem_u32(sx);
-        if ((W & 3) == 0) {
-            for (int i = t; i < 3 * SX_H * (SX_W / 4); i += 256) {
-                const int p = i / (SX_W / 4), j = i - p * (SX_W / 4);
-                const int c = p / SX_H, rr = p - c * SX_H;
-                const int yy = y0 - 3 + rr, xx = x0 - 4 + 4 * j;
-                const bool ok = yy >= 0 && yy < H && xx >= 0 && xx < W;
-                tc::cp_async16(sh + (p * SX_W + 4 * j) * 4, xb + (ok ? c * plane + (size_t)yy * W + xx : (size_t)0), ok);
+    // tile + halo completely inside the image (block-uniform): no zero padding, no masks, 128-bit global accesses
+    const bool interior = (W & 3) == 0 && y0 >= 3 && y0 + S_TH + 3 <= H && x0 >= 4 && x0 + S_TW + 4 <= W;
+    {   // x halo tile into row pairs: a task = (channel c, row pair p, 4 columns from x0 - 4 + 4q); thread t < 252 owns
+        // (p = t / 18 < 14, q = t % 18) in all three channels, row pair 14 goes to threads 0..53 (c = t / 18); all of a
+        // thread's loads are in flight before its first store; zeros outside the image are the conv's zero padding
+        constexpr int NQ = (SX_W + 2 + 3) / 4;  // columns x0-4 .. x0+67 (the outer two unused)
+        static_assert(NQ * (SX_RP - 1) <= 256 && NQ * 3 <= 256, "x tile task mapping");
+        const int q = t % NQ, pt = t / NQ;
+        const int gx = x0 - 4 + 4 * q;
+        float4 v0[4], v1[4];
+        if (interior) {
+            const float* g0 = xb + (size_t)(y0 - 3 + 2 * pt) * W + gx;
+            if (pt < SX_RP - 1) {
+#pragma unroll
+                for (int u = 0; u < 3; ++u) {
+                    v0[u] = __ldg(reinterpret_cast<const float4*>(g0 + u * plane));
+                    v1[u] = __ldg(reinterpret_cast<const float4*>(g0 + u * plane + W));
+                }
+            }
+            if (pt < 3) {
+                const float* g3 = xb + pt * plane + (size_t)(y0 - 3 + 2 * (SX_RP - 1)) * W + gx;
+                v0[3] = __ldg(reinterpret_cast<const float4*>(g3));
+                v1[3] = __ldg(reinterpret_cast<const float4*>(g3 + W));
             }
         } else {
-            for (int i = t; i < 3 * SX_H * SX_W; i += 256) {
-                const int p = i / SX_W, cc = i - p * SX_W;
-                const int c = p / SX_H, rr = p - c * SX_H;
-                const int yy = y0 - 3 + rr, xx = x0 - 4 + cc;
-                const bool ok = yy >= 0 && yy < H && xx >= 0 && xx < W;
-                tc::cp_async4(sh + i * 4, xb + (ok ? c * plane + (size_t)yy * W + xx : (size_t)0), ok);
+            const bool vec = (W & 3) == 0;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int c = u < 3 ? u : pt, p = u < 3 ? pt : SX_RP - 1;
+                const bool active = u < 3 ? pt < SX_RP - 1 : pt < 3;
+                v0[u] = v1[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!active) continue;
+                const int r0 = y0 - 3 + 2 * p;
+                const float* g0 = xb + ((long long)c * (long long)plane + (long long)r0 * W + gx);
+                const bool in0 = r0 >= 0 && r0 < H, in1 = r0 + 1 >= 0 && r0 + 1 < H;
+                if (vec) {
+                    if (gx >= 0 && gx < W) {
+                        if (in0) v0[u] = __ldg(reinterpret_cast<const float4*>(g0));
+                        if (in1) v1[u] = __ldg(reinterpret_cast<const float4*>(g0 + W));
+                    }
+                } else {
+                    float e0[4] = {0.f, 0.f, 0.f, 0.f}, e1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (gx + e >= 0 && gx + e < W) {
+                            if (in0) e0[e] = __ldg(g0 + e);
+                            if (in1) e1[e] = __ldg(g0 + W + e);
+                        }
+                    v0[u] = make_float4(e0[0], e0[1], e0[2], e0[3]);
+                    v1[u] = make_float4(e1[0], e1[1], e1[2], e1[3]);
+                }
             }
         }
-        tc::cp_async_commit();
-        tc::cp_async_wait<0>();
-    }
-    __syncthreads();
-    // fea1 = relu(conv(x)) on 28 x 36; zero outside the image (that is the next conv's zero padding)
-    int gi, cc;
-    if (sci_item<S1_G, S1_W>(t, gi, cc)) {
-        const int yy = y0 - 2 + 4 * gi, xx = x0 - 2 + cc;
-        float2 o[3][2];
-        conv3_quad_rowmajor<SX_W, SX_H * SX_W>(sx + (4 * gi) * SX_W + cc + 1, wt.w1, wt.b1, o);
-        const bool xin = xx >= 0 && xx < W;
-        const bool in0 = xin && yy >= 0 && yy < H, in1 = xin && yy + 1 >= 0 && yy + 1 < H;
-        const bool in2 = xin && yy + 2 >= 0 && yy + 2 < H, in3 = xin && yy + 3 >= 0 && yy + 3 < H;
+        float2* dst = sx + pt * SX_W + 4 * q - 1;  // plane column k <-> image column x0 - 3 + k
+        if (pt < SX_RP - 1) {
 #pragma unroll
-        for (int c = 0; c < 3; ++c)
-            store_quad<S1_W>(s1a + c * S1_RP * S1_W, s1b + c * S1_RP * S1_W, gi, cc, in0 ? fmaxf(o[c][0].x, 0.f) : 0.f,
-                             in1 ? fmaxf(o[c][0].y, 0.f) : 0.f, in2 ? fmaxf(o[c][1].x, 0.f) : 0.f,
-                             in3 ? fmaxf(o[c][1].y, 0.f) : 0.f);
-    }
-    __syncthreads();
-    // fea2 = fea1 + relu(bn(conv(fea1))) on 28 x 34 (rows y0-1 ..; the last two rows feed nothing)
-    if (sci_item<S2_G, S2_W>(t, gi, cc)) {
-        const int yy = y0 - 1 + 4 * gi, xx = x0 - 1 + cc;
-        float2 o[3][2];
-        conv3_quad<S1_W, S1_RP * S1_W>(s1a + (2 * gi) * S1_W + cc, s1b + (2 * gi) * S1_W + cc, wt.w2, wt.b2, o);
-        const bool xin = xx >= 0 && xx < W;
-        const bool in0 = xin && yy >= 0 && yy < H, in1 = xin && yy + 1 >= 0 && yy + 1 < H;
-        const bool in2 = xin && yy + 2 >= 0 && yy + 2 < H, in3 = xin && yy + 3 >= 0 && yy + 3 < H;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            // residual: fea1 at the same position = fea1 rows 4gi+1 .. 4gi+4, column cc+1: copy B pair rows 2gi, 2gi+1
-            const float2 ra = s1b[(c * S1_RP + 2 * gi) * S1_W + cc + 1], rb = s1b[(c * S1_RP + 2 * gi + 1) * S1_W + cc + 1];
-            store_quad<S2_W>(s2a + c * S2_RP * S2_W, s2b + c * S2_RP * S2_W, gi, cc,
-                             in0 ? ra.x + fmaxf(o[c][0].x, 0.f) : 0.f, in1 ? ra.y + fmaxf(o[c][0].y, 0.f) : 0.f,
-                             in2 ? rb.x + fmaxf(o[c][1].x, 0.f) : 0.f, in3 ? rb.y + fmaxf(o[c][1].y, 0.f) : 0.f);
+            for (int u = 0; u < 3; ++u) {
+                float2* d = dst + u * SX_RP * SX_W;
+                if (q > 0) d[0] = make_float2(v0[u].x, v1[u].x);
+                *reinterpret_cast<float4*>(d + 1) = make_float4(v0[u].y, v1[u].y, v0[u].z, v1[u].z);
+                if (q < NQ - 1) d[3] = make_float2(v0[u].w, v1[u].w);
+            }
+        }
+        if (pt < 3) {
+            float2* d = sx + (pt * SX_RP + SX_RP - 1) * SX_W + 4 * q - 1;
+            if (q > 0) d[0] = make_float2(v0[3].x, v1[3].x);
+            *reinterpret_cast<float4*>(d + 1) = make_float4(v0[3].y, v1[3].y, v0[3].z, v1[3].z);
+            if (q < NQ - 1) d[3] = make_float2(v0[3].w, v1[3].w);
         }
     }
     __syncthreads();
-    if (sci_item<S3_G, S_TW>(t, gi, cc)) {
-        const int xx = x0 + cc;
+    int gi, ip;
+    // fea1 = relu(conv(x)) on 28 x 68
+    if (sci_item<S1_G, S1_W / 2>(t, gi, ip)) {
+        const int j = 2 * ip, yy = y0 - 2 + 4 * gi, xx = x0 - 2 + j;
+        float2 o[2][3][2];
+        conv3_item<SX_W, SX_RP * SX_W, false>(sx + (2 * gi) * SX_W + j, wt.w[0], o, o);
+        if (interior) {
+            sci_store_item<S1_W, S1_RP, false, false>(s1, gi, j, o, o, yy, xx, H, W);
+        } else {
+            sci_store_item<S1_W, S1_RP, false, true>(s1, gi, j, o, o, yy, xx, H, W);
+        }
+    }
+    __syncthreads();
+    // fea2 = fea1 + relu(bn(conv(fea1))) on 28 x 66 (rows y0-1 ..; the last two rows feed nothing)
+    if (sci_item<S2_G, S2_W / 2>(t, gi, ip)) {
+        const int j = 2 * ip, yy = y0 - 1 + 4 * gi, xx = x0 - 1 + j;
+        float2 o[2][3][2], res[2][3][2];
+        conv3_item<S1_W, S1_RP * S1_W, true>(s1 + (2 * gi) * S1_W + j, wt.w[1], o, res);
+        if (interior) {
+            sci_store_item<S2_W, S2_RP, true, false>(s2, gi, j, o, res, yy, xx, H, W);
+        } else {
+            sci_store_item<S2_W, S2_RP, true, true>(s2, gi, j, o, res, yy, xx, H, W);
+        }
+    }
+    __syncthreads();
+    if (sci_item<S3_G, S_TW / 2>(t, gi, ip)) {
+        const int j = 2 * ip, xx = x0 + j;
         if (xx < W) {
-            float2 o[3][2];
-            conv3_quad<S2_W, S2_RP * S2_W>(s2a + (2 * gi) * S2_W + cc, s2b + (2 * gi) * S2_W + cc, wt.w3, wt.b3, o);
+            const bool pairs = (W & 1) == 0;  // then xx + 1 < W and every (row, xx) is 8-byte aligned
+            // the x values under this thread's outputs: cp.async into the thread's own slots of the (dead) fea1 region,
+            // in flight under the conv; slot k of thread t at [k][t]: conflict-free
+            float2* xs = s1 + t;
+            if (pairs) {
+                const uint32_t sh = tc::smem_u32(xs);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int yy = y0 + 4 * gi + q;
-                if (yy >= H) continue;
+                for (int c = 0; c < 3; ++c)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int yy = y0 + 4 * gi + q;
+                        if (yy < H) tc::cp_async8(sh + (c * 4 + q) * 32 * S3_G * 8, xb + c * plane + (size_t)yy * W + xx);
+                    }
+                tc::cp_async_commit();
+            }
+            float2 o[2][3][2];
+            conv3_item<S2_W, S2_RP * S2_W, false>(s2 + (2 * gi) * S2_W + j, wt.w[2], o, o);
+            if (pairs) {
+                tc::cp_async_wait<0>();
+                const size_t off0 = (size_t)b * 3 * plane + (size_t)(y0 + 4 * gi) * W + xx;
+                float* ip = illu ? illu + off0 : nullptr;
+                float* rp = r + off0;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    const float xin = __ldg(xb + c * plane + (size_t)yy * W + xx);
-                    const float ov = (q & 1) ? o[c][q >> 1].y : o[c][q >> 1].x;
-                    // sigmoid and x / illu on the SFU (ex2.approx / rcp.approx, ~2 ulp): the IEEE-rounded forms cost as
-                    // many FMA-pipe instructions per pixel as a whole conv layer; the contract is 1e-3
-                    const float sg = __fdividef(1.f, 1.f + __expf(-ov));
-                    const float il = fminf(fmaxf(sg + xin, 0.0001f), 1.f);
-                    const float rv = fminf(fmaxf(__fdividef(xin, il), 0.f), 1.f);
-                    const size_t off = ((size_t)(b * 3 + c)) * plane + (size_t)yy * W + xx;
-                    if (illu) illu[off] = il;
-                    r[off] = rv;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (y0 + 4 * gi + q >= H) continue;
+                        const float2 xv = xs[(c * 4 + q) * 32 * S3_G];
+                        const float xin[2] = {xv.x, xv.y};
+                        float il[2], rv[2];
+#pragma unroll
+                        for (int col = 0; col < 2; ++col) {
+                            const float ov = (q & 1) ? o[col][c][q >> 1].y : o[col][c][q >> 1].x;
+                            const float sg = sfu_rcp(1.f + sfu_ex2(ov * -1.4426950408889634f));  // 1 / (1 + e^-ov)
+                            il[col] = fminf(fmaxf(sg + xin[col], 0.0001f), 1.f);
+                            rv[col] = fminf(fmaxf(xin[col] * sfu_rcp(il[col]), 0.f), 1.f);
+                        }
+                        if (ip) *reinterpret_cast<float2*>(ip + c * plane + (size_t)q * W) = make_float2(il[0], il[1]);
+                        *reinterpret_cast<float2*>(rp + c * plane + (size_t)q * W) = make_float2(rv[0], rv[1]);
+                    }
+                }
+            } else {  // odd widths: scalar accesses
+#pragma unroll 1
+                for (int c = 0; c < 3; ++c) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int yy = y0 + 4 * gi + q;
+                        if (yy >= H) continue;
+                        const size_t off = ((size_t)(b * 3 + c)) * plane + (size_t)yy * W + xx;
+#pragma unroll
+                        for (int col = 0; col < 2; ++col) {
+                            if (xx + col >= W) continue;
+                            const float xin = __ldg(x + off + col);
+                            const float ov = c == 0 ? ((q & 1) ? o[col][0][q >> 1].y : o[col][0][q >> 1].x)
+                                           : c == 1 ? ((q & 1) ? o[col][1][q >> 1].y : o[col][1][q >> 1].x)
+                                                    : ((q & 1) ? o[col][2][q >> 1].y : o[col][2][q >> 1].x);
+                            const float sg = sfu_rcp(1.f + sfu_ex2(ov * -1.4426950408889634f));
+                            const float il = fminf(fmaxf(sg + xin, 0.0001f), 1.f);
+                            if (illu) illu[off + col] = il;
+                            r[off + col] = fminf(fmaxf(xin * sfu_rcp(il), 0.f), 1.f);
+                        }
+                    }
                 }
             }
         }
@@ -251,8 +378,19 @@ extern "C" int b200_sci_forward(const float* x, const float* packed_host, float*
     if (B <= 0 || H <= 0 || W <= 0) return B200_ERR_BAD_SHAPE;
     if (B > 65535) return B200_ERR_UNSUPPORTED;
     if (!b200::aligned16(x) || !b200::aligned16(r) || (illu && !b200::aligned16(illu))) return B200_ERR_MISALIGNED;
-    b200::SciWeights wt;
-    memcpy(&wt, packed_host, sizeof(wt));
+    b200::SciWeights pk;
+    memcpy(&pk, packed_host, sizeof(pk));
+    b200::SciKernelWeights wt{};  // OIHW -> [ci][kx][co][ky], the order the kernel's loop consumes
+    const float* src_w[3] = {pk.w1, pk.w2, pk.w3};
+    const float* src_b[3] = {pk.b1, pk.b2, pk.b3};
+    for (int l = 0; l < 3; ++l) {
+        for (int co = 0; co < 3; ++co)
+            for (int ci = 0; ci < 3; ++ci)
+                for (int ky = 0; ky < 3; ++ky)
+                    for (int kx = 0; kx < 3; ++kx)
+                        wt.w[l][ci * b200::SCI_WCI + (kx * 3 + co) * 3 + ky] = src_w[l][((co * 3 + ci) * 3 + ky) * 3 + kx];
+        for (int co = 0; co < 3; ++co) wt.w[l][3 * b200::SCI_WCI + co] = src_b[l][co];
+    }
     dim3 grid((W + b200::S_TW - 1) / b200::S_TW, (H + b200::S_TH - 1) / b200::S_TH, B);
     if (cudaFuncSetAttribute(b200::sci_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, b200::SCI_SMEM) !=
         cudaSuccess) {

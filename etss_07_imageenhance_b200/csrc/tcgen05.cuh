@@ -261,6 +261,9 @@ __device__ __forceinline__ void cp_async4(uint32_t smem_dst, const void* gsrc, b
     const uint32_t n = valid ? 4u : 0u;
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_dst), "l"(gsrc), "r"(n) : "memory");
 }
+__device__ __forceinline__ void cp_async8(uint32_t smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
