@@ -42,6 +42,12 @@ struct __align__(16) SciKernelWeights {
     float w[3][SCI_WL];
 };
 
+#ifndef SCI_UNROLL_L1
+#define SCI_UNROLL_L1 true
+#endif
+#ifndef SCI_UNROLL_L3
+#define SCI_UNROLL_L3 true
+#endif
 constexpr int S_TH = 24, S_TW = 64;
 constexpr int SX_RP = 15, SX_W = S_TW + 6;  // x:    rows y0-3 .. y0+26 as 15 row pairs, columns x0-3 .. x0+66
 constexpr int S1_RP = 15, S1_W = S_TW + 4;  // fea1: rows y0-2 .. y0+25 (+ one pair never written, read by the two
@@ -60,7 +66,7 @@ static_assert(SCI_SX_BYTES % 16 == 0 && SCI_S1_BYTES % 16 == 0 && (SX_W * 8) % 1
 // W_IN / PLANE in float2 units.  out[col][co][pair].  The loop over the input channel stays ROLLED: the body (144 FMA
 // instructions) then lives in the instruction cache -- fully unrolled, the three layers are 50 KB of straight-line code
 // and a fifth of all issue slots went to instruction fetch.
-template <int W_IN, int PLANE, bool RESIDUAL>
+template <int W_IN, int PLANE, bool RESIDUAL, bool UNROLL>
 __device__ __forceinline__ void conv3_item(const float2* __restrict__ in, const float* __restrict__ w, float2 out[2][3][2],
                                            float2 res[2][3][2]) {
 #pragma unroll
@@ -69,7 +75,7 @@ __device__ __forceinline__ void conv3_item(const float2* __restrict__ in, const 
         for (int co = 0; co < 3; ++co) out[col][co][0] = out[col][co][1] = make_float2(w[3 * SCI_WCI + co], w[3 * SCI_WCI + co]);
     // RESIDUAL (layer 2 only): unrolled, so that res[col][ci][pair] = the input at the output's own position (rows b+1 ..
     // b+4, columns j+1, j+2) is taken from the registers of iteration ci
-#pragma unroll(RESIDUAL ? 3 : 1)
+#pragma unroll(UNROLL ? 3 : 1)
     for (int ci = 0; ci < 3; ++ci) {
         float2 a[3][4];  // a[t][k] = rows (b+2t, b+2t+1) at column j+k
 #pragma unroll
@@ -258,7 +264,7 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
     if (sci_item<S1_G, S1_W / 2>(t, gi, ip)) {
         const int j = 2 * ip, yy = y0 - 2 + 4 * gi, xx = x0 - 2 + j;
         float2 o[2][3][2];
-        conv3_item<SX_W, SX_RP * SX_W, false>(sx + (2 * gi) * SX_W + j, wt.w[0], o, o);
+        conv3_item<SX_W, SX_RP * SX_W, false, SCI_UNROLL_L1>(sx + (2 * gi) * SX_W + j, wt.w[0], o, o);
         if (interior) {
             sci_store_item<S1_W, S1_RP, false, false>(s1, gi, j, o, o, yy, xx, H, W);
         } else {
@@ -270,7 +276,7 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
     if (sci_item<S2_G, S2_W / 2>(t, gi, ip)) {
         const int j = 2 * ip, yy = y0 - 1 + 4 * gi, xx = x0 - 1 + j;
         float2 o[2][3][2], res[2][3][2];
-        conv3_item<S1_W, S1_RP * S1_W, true>(s1 + (2 * gi) * S1_W + j, wt.w[1], o, res);
+        conv3_item<S1_W, S1_RP * S1_W, true, true>(s1 + (2 * gi) * S1_W + j, wt.w[1], o, res);
         if (interior) {
             sci_store_item<S2_W, S2_RP, true, false>(s2, gi, j, o, res, yy, xx, H, W);
         } else {
@@ -297,7 +303,7 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
                 tc::cp_async_commit();
             }
             float2 o[2][3][2];
-            conv3_item<S2_W, S2_RP * S2_W, false>(s2 + (2 * gi) * S2_W + j, wt.w[2], o, o);
+            conv3_item<S2_W, S2_RP * S2_W, false, SCI_UNROLL_L3>(s2 + (2 * gi) * S2_W + j, wt.w[2], o, o);
             if (pairs) {
                 tc::cp_async_wait<0>();
                 const size_t off0 = (size_t)b * 3 * plane + (size_t)(y0 + 4 * gi) * W + xx;
