@@ -2,25 +2,27 @@
 // EnhanceNetwork.forward :36-45, layers=1, channels=3, BatchNorm2d eval) as ONE fused pass:
 //   fea1 = relu(conv3x3(x));  fea2 = fea1 + relu(bn(conv3x3(fea1)));  fea3 = sigmoid(conv3x3(fea2));
 //   illu = clamp(fea3 + x, 1e-4, 1);  r = clamp(x / illu, 0, 1)
-// CTA tile 24x64 output pixels; the three stacked 3x3 layers are evaluated on shrinking halo regions held in
-// shared memory (x: 30x70, fea1: 28x68, fea2: 28x66), so x is read once from HBM and illu / r written once.
+// CTA tile 32x60 output pixels, 9 warps; the three stacked 3x3 layers are evaluated on shrinking halo regions held in
+// shared memory (x: 38x66, fea1: 36x64, fea2: 36x62), so x is read once from HBM and illu / r written once.
 //
-// The work is 3 x 81 MAC per position on the fp32 pipe (~560 FLOP per output pixel with the halo recompute): the
-// kernel is bound by the packed-FMA pipe and by instruction issue, not by HBM, so the inner loop is built to be
-// (almost) nothing but FFMA2, with as few other instructions per FFMA2 as the data flow allows:
+// The work is 3 x 81 MAC per position on the fp32 pipe (~550 FLOP per output pixel with the halo recompute): the
+// kernel is bound by the FMA pipe and by instruction issue (both ~65 % busy), not by HBM, so the inner loop is built
+// to be (almost) nothing but FMAs, with as few other instructions per FMA as the data flow allows:
 //   * all three planes (x, fea1, fea2) are stored ROW-PAIR INTERLEAVED: element [pair row p][column] is the float2
 //     (row 2p, row 2p+1), so a vertical pair of inputs is one aligned 64-bit operand of an FFMA2 and two adjacent
-//     columns are one 128-bit shared access;
-//   * a thread computes an item of FOUR rows x TWO columns x 3 output channels (324 FFMA2 per layer): per input
-//     channel six 128-bit loads bring the 6 x 4 input window; the pairs that start on an odd row (r+1, r+2) are put
-//     together in registers (two moves each -- a second, odd-aligned copy of the planes would save the moves and cost
-//     twice the shared memory, i.e. half the resident warps);
-//   * every FFMA2 carries one weight as a scalar broadcast from a uniform register; the 252 weights travel as a by-value
-//     kernel parameter in the constant bank, reordered on the host to the order the loop consumes them so that they
-//     arrive as 128-bit uniform loads;
-//   * item counts per layer (7 x 34, 7 x 33, 6 x 32) are just under the 256 threads: one round per layer, a warp per
-//     row group (its 128-bit shared accesses are consecutive: conflict free), the last warp takes the two / one
-//     left-over column pairs of every group.
+//     columns are one 128-bit shared access (a warp's accesses are consecutive: conflict free);
+//   * a thread computes an item of FOUR rows x TWO columns x 3 output channels: per input channel six 128-bit loads
+//     bring the 6 x 4 input window; the taps ky = 0 / 2 read aligned row pairs (FFMA2), the tap ky = 1 reads the pair
+//     (r+1, r+2) that straddles two row pairs: two scalar FFMAs on the halves -- the same FMA-lane cycles as one
+//     FFMA2 and no register moves (ptxas rebuilt the odd pairs with ~3.5 moves per FFMA2 saved; a second, odd-aligned
+//     copy of the planes would double shared memory and its traffic);
+//   * every FMA carries one weight as a scalar broadcast from a uniform register; the 252 weights travel as a by-value
+//     kernel parameter in the constant bank, reordered on the host to the order the loop consumes them;
+//   * tile width 60: with two halo columns per side layer 1 is exactly 32 column pairs = one warp per row group, no
+//     left-over columns; 9 / 9 / 8 row groups of 4 rows = 9 warps, one round per layer;
+//   * sigmoid and the division on the SFU in their flush-to-zero forms (see sfu_ex2); tiles whose halo lies inside
+//     the image take a path without masks; the x values for the epilogue come by cp.async under the last conv.
+// History of the measurements (16 x 1080p): profiles/r02_summary.md section 6.
 #include <math.h>
 
 #include "common.cuh"
@@ -36,7 +38,7 @@ struct SciWeights {
 };
 static_assert(sizeof(SciWeights) == B200_SCI_PACKED_FLOATS * sizeof(float), "packed size");
 // the kernel parameter: each layer's weights as [ci][kx][co][ky] (the order the loop consumes them), every input
-// channel's 27 padded to 28 floats so that the loop over ci can stay rolled with 128-bit uniform loads
+// channel's 27 padded to 28 floats (16-byte blocks; lets the loop over ci be rolled, see SCI_UNROLL_*)
 constexpr int SCI_WCI = 28, SCI_WL = 3 * SCI_WCI + 4;  // per layer: 3 x 28 weights, 3 biases (+1)
 struct __align__(16) SciKernelWeights {
     float w[3][SCI_WL];
@@ -48,14 +50,16 @@ struct __align__(16) SciKernelWeights {
 #ifndef SCI_UNROLL_L3
 #define SCI_UNROLL_L3 true
 #endif
-constexpr int S_TH = 24, S_TW = 64;
-constexpr int SX_RP = 15, SX_W = S_TW + 6;  // x:    rows y0-3 .. y0+26 as 15 row pairs, columns x0-3 .. x0+66
-constexpr int S1_RP = 15, S1_W = S_TW + 4;  // fea1: rows y0-2 .. y0+25 (+ one pair never written, read by the two
-                                            //       fea2 rows that feed nothing), columns x0-2 .. x0+65
-constexpr int S2_RP = 14, S2_W = S_TW + 2;  // fea2: rows y0-1 .. y0+26, columns x0-1 .. x0+64
-constexpr int S1_G = 7, S2_G = 7, S3_G = S_TH / 4;  // row groups (4 rows) per layer
+constexpr int S_TH = 32, S_TW = 60;           // with the two halo columns per side layer 1 is exactly 32 column pairs wide
+constexpr int SCI_NT = 32 * (S_TH / 4 + 1);   // one warp per row group of the tallest layer (9 groups of 4 rows)
+constexpr int S1_G = S_TH / 4 + 1, S2_G = S_TH / 4 + 1, S3_G = S_TH / 4;  // row groups (4 rows) per layer
+constexpr int SX_RP = 2 * S1_G + 1, SX_W = S_TW + 6;  // x:    rows y0-3 .. y0+34 as 19 row pairs, columns x0-3 .. x0+62
+constexpr int S1_RP = 2 * S2_G + 1, S1_W = S_TW + 4;  // fea1: rows y0-2 .. y0+33 (+ one pair never written, read by the
+                                                      //       two fea2 rows that feed nothing), columns x0-2 .. x0+61
+constexpr int S2_RP = 2 * S2_G, S2_W = S_TW + 2;      // fea2: rows y0-1 .. y0+34, columns x0-1 .. x0+60
+static_assert(S1_W / 2 <= 32 && S_TW % 4 == 0, "a warp covers a row group; tiles start on 16-byte boundaries");
 constexpr int SCI_SX_BYTES = 8 * 3 * SX_RP * SX_W, SCI_S1_BYTES = 8 * 3 * S1_RP * S1_W, SCI_S2_BYTES = 8 * 3 * S2_RP * S2_W;
-// fea2 reuses the x planes' bytes (x is only read by layer 1); 50 KB: four CTAs per SM.  During layer 3 the dead fea1
+// fea2 reuses the x planes' bytes (x is only read by layer 1); 58 KB: three CTAs per SM.  During layer 3 the dead fea1
 // region holds each thread's own x values for the epilogue (fetched by cp.async under the conv)
 constexpr int SCI_SMEM = (SCI_SX_BYTES > SCI_S2_BYTES ? SCI_SX_BYTES : SCI_S2_BYTES) + SCI_S1_BYTES;
 static_assert(12 * 32 * S3_G * 8 <= SCI_S1_BYTES, "layer 3's x slots fit the fea1 region");
@@ -63,9 +67,9 @@ static_assert(SCI_SX_BYTES % 16 == 0 && SCI_S1_BYTES % 16 == 0 && (SX_W * 8) % 1
 
 // One item: output rows b .. b+3 (two row pairs) x columns j, j+1 x 3 channels from a row-pair plane whose origin lies
 // one row above and one column left of the output's origin.  `in` points at (pair row b/2, column j) of channel 0;
-// W_IN / PLANE in float2 units.  out[col][co][pair].  The loop over the input channel stays ROLLED: the body (144 FMA
-// instructions) then lives in the instruction cache -- fully unrolled, the three layers are 50 KB of straight-line code
-// and a fifth of all issue slots went to instruction fetch.
+// W_IN / PLANE in float2 units.  out[col][co][pair].  UNROLL: the loop over the input channel unrolled (default for
+// all layers; rolled it is 1/3 of the code -- that mattered while the epilogue was 4x its present size and a fifth of
+// all issue slots went to instruction fetch; with the lean epilogue unrolled is 7 % faster).
 template <int W_IN, int PLANE, bool RESIDUAL, bool UNROLL>
 __device__ __forceinline__ void conv3_item(const float2* __restrict__ in, const float* __restrict__ w, float2 out[2][3][2],
                                            float2 res[2][3][2]) {
@@ -134,19 +138,12 @@ __device__ __forceinline__ float sfu_rcp(float v) {
     return r;
 }
 
-// item (row group gi, column pair ci2) of thread t for a layer with G row groups of NP >= 32 column pairs: warp gi takes
-// pairs 0..31 of its group, the last warp takes the NP - 32 left-over pairs of every group
+// item (row group gi, column pair) of thread t for a layer with G row groups of NP <= 32 column pairs: warp gi, lane pair
 template <int G, int NP>
 __device__ __forceinline__ bool sci_item(int t, int& gi, int& ci2) {
-    static_assert(G <= 7 && NP >= 32 && (NP - 32) * G <= 32, "one round of 8 warps");
-    const int warp = t >> 5, lane = t & 31;
-    if (warp < G) {
-        gi = warp, ci2 = lane;
-        return true;
-    }
-    if (NP == 32 || warp != 7 || lane >= (NP - 32) * G) return false;
-    gi = lane / (NP - 32 > 0 ? NP - 32 : 1), ci2 = 32 + lane % (NP - 32 > 0 ? NP - 32 : 1);
-    return true;
+    static_assert(G * 32 <= SCI_NT && NP <= 32, "one round");
+    gi = t >> 5, ci2 = t & 31;
+    return gi < G && ci2 < NP;
 }
 
 // relu / optional residual / (MASKED: zero outside the image = the next conv's zero padding), then the two row pairs of
@@ -176,7 +173,7 @@ __device__ __forceinline__ void sci_store_item(float2* __restrict__ plane, int g
         }
 }
 
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(SCI_NT, 3)
 sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* __restrict__ r,
                  const __grid_constant__ SciKernelWeights wt, int H, int W) {
     extern __shared__ __align__(16) float2 sci_smem[];
@@ -190,73 +187,58 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
     const float* xb = x + (size_t)b * 3 * plane;
     // tile + halo completely inside the image (block-uniform): no zero padding, no masks, 128-bit global accesses
     const bool interior = (W & 3) == 0 && y0 >= 3 && y0 + S_TH + 3 <= H && x0 >= 4 && x0 + S_TW + 4 <= W;
-    {   // x halo tile into row pairs: a task = (channel c, row pair p, 4 columns from x0 - 4 + 4q); thread t < 252 owns
-        // (p = t / 18 < 14, q = t % 18) in all three channels, row pair 14 goes to threads 0..53 (c = t / 18); all of a
-        // thread's loads are in flight before its first store; zeros outside the image are the conv's zero padding
-        constexpr int NQ = (SX_W + 2 + 3) / 4;  // columns x0-4 .. x0+67 (the outer two unused)
-        static_assert(NQ * (SX_RP - 1) <= 256 && NQ * 3 <= 256, "x tile task mapping");
-        const int q = t % NQ, pt = t / NQ;
-        const int gx = x0 - 4 + 4 * q;
-        float4 v0[4], v1[4];
-        if (interior) {
-            const float* g0 = xb + (size_t)(y0 - 3 + 2 * pt) * W + gx;
-            if (pt < SX_RP - 1) {
+    {   // x halo tile into row pairs: a task = (row pair p, 4 columns from x0 - 4 + 4q) in all three channels; the loads
+        // of a task are in flight together; zeros outside the image are the conv's zero padding
+        constexpr int NQ = (SX_W + 2 + 3) / 4;  // columns x0-4 .. (the outer two unused)
+        constexpr int NPQ = SX_RP * NQ;
+        static_assert(NPQ <= 2 * SCI_NT, "two rounds of tasks");
+        auto xtask = [&](int pq) {
+            const int p = pq / NQ, q = pq - p * NQ;
+            const int gx = x0 - 4 + 4 * q, r0 = y0 - 3 + 2 * p;
+            float4 v0[3], v1[3];
+            if (interior) {
+                const float* g0 = xb + (size_t)r0 * W + gx;
 #pragma unroll
                 for (int u = 0; u < 3; ++u) {
                     v0[u] = __ldg(reinterpret_cast<const float4*>(g0 + u * plane));
                     v1[u] = __ldg(reinterpret_cast<const float4*>(g0 + u * plane + W));
                 }
-            }
-            if (pt < 3) {
-                const float* g3 = xb + pt * plane + (size_t)(y0 - 3 + 2 * (SX_RP - 1)) * W + gx;
-                v0[3] = __ldg(reinterpret_cast<const float4*>(g3));
-                v1[3] = __ldg(reinterpret_cast<const float4*>(g3 + W));
-            }
-        } else {
-            const bool vec = (W & 3) == 0;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int c = u < 3 ? u : pt, p = u < 3 ? pt : SX_RP - 1;
-                const bool active = u < 3 ? pt < SX_RP - 1 : pt < 3;
-                v0[u] = v1[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (!active) continue;
-                const int r0 = y0 - 3 + 2 * p;
-                const float* g0 = xb + ((long long)c * (long long)plane + (long long)r0 * W + gx);
+            } else {
+                const bool vec = (W & 3) == 0;
                 const bool in0 = r0 >= 0 && r0 < H, in1 = r0 + 1 >= 0 && r0 + 1 < H;
-                if (vec) {
-                    if (gx >= 0 && gx < W) {
-                        if (in0) v0[u] = __ldg(reinterpret_cast<const float4*>(g0));
-                        if (in1) v1[u] = __ldg(reinterpret_cast<const float4*>(g0 + W));
-                    }
-                } else {
-                    float e0[4] = {0.f, 0.f, 0.f, 0.f}, e1[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        if (gx + e >= 0 && gx + e < W) {
-                            if (in0) e0[e] = __ldg(g0 + e);
-                            if (in1) e1[e] = __ldg(g0 + W + e);
+                for (int u = 0; u < 3; ++u) {
+                    v0[u] = v1[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float* g0 = xb + ((long long)u * (long long)plane + (long long)r0 * W + gx);
+                    if (vec) {
+                        if (gx >= 0 && gx < W) {
+                            if (in0) v0[u] = __ldg(reinterpret_cast<const float4*>(g0));
+                            if (in1) v1[u] = __ldg(reinterpret_cast<const float4*>(g0 + W));
                         }
-                    v0[u] = make_float4(e0[0], e0[1], e0[2], e0[3]);
-                    v1[u] = make_float4(e1[0], e1[1], e1[2], e1[3]);
+                    } else {
+                        float e0[4] = {0.f, 0.f, 0.f, 0.f}, e1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            if (gx + e >= 0 && gx + e < W) {
+                                if (in0) e0[e] = __ldg(g0 + e);
+                                if (in1) e1[e] = __ldg(g0 + W + e);
+                            }
+                        v0[u] = make_float4(e0[0], e0[1], e0[2], e0[3]);
+                        v1[u] = make_float4(e1[0], e1[1], e1[2], e1[3]);
+                    }
                 }
             }
-        }
-        float2* dst = sx + pt * SX_W + 4 * q - 1;  // plane column k <-> image column x0 - 3 + k
-        if (pt < SX_RP - 1) {
+            float2* dst = sx + p * SX_W + 4 * q - 1;  // plane column k <-> image column x0 - 3 + k
 #pragma unroll
             for (int u = 0; u < 3; ++u) {
                 float2* d = dst + u * SX_RP * SX_W;
                 if (q > 0) d[0] = make_float2(v0[u].x, v1[u].x);
                 *reinterpret_cast<float4*>(d + 1) = make_float4(v0[u].y, v1[u].y, v0[u].z, v1[u].z);
-                if (q < NQ - 1) d[3] = make_float2(v0[u].w, v1[u].w);
+                if (4 * q + 2 < SX_W) d[3] = make_float2(v0[u].w, v1[u].w);
             }
-        }
-        if (pt < 3) {
-            float2* d = sx + (pt * SX_RP + SX_RP - 1) * SX_W + 4 * q - 1;
-            if (q > 0) d[0] = make_float2(v0[3].x, v1[3].x);
-            *reinterpret_cast<float4*>(d + 1) = make_float4(v0[3].y, v1[3].y, v0[3].z, v1[3].z);
-            if (q < NQ - 1) d[3] = make_float2(v0[3].w, v1[3].w);
-        }
+        };
+        xtask(t);
+        if (t < NPQ - SCI_NT) xtask(SCI_NT + t);
     }
     __syncthreads();
     int gi, ip;
@@ -286,29 +268,28 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
     __syncthreads();
     if (sci_item<S3_G, S_TW / 2>(t, gi, ip)) {
         const int j = 2 * ip, xx = x0 + j;
-        if (xx < W) {
+        if (xx < W && y0 + 4 * gi < H) {
             const bool pairs = (W & 1) == 0;  // then xx + 1 < W and every (row, xx) is 8-byte aligned
             // the x values under this thread's outputs: cp.async into the thread's own slots of the (dead) fea1 region,
             // in flight under the conv; slot k of thread t at [k][t]: conflict-free
             float2* xs = s1 + t;
+            // 32-bit element offsets inside the frame (the host checks 3 * H * W < 2^31): one IMAD.WIDE per address
+            const int hw = H * W, off0 = (y0 + 4 * gi) * W + xx;
             if (pairs) {
                 const uint32_t sh = tc::smem_u32(xs);
 #pragma unroll
                 for (int c = 0; c < 3; ++c)
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const int yy = y0 + 4 * gi + q;
-                        if (yy < H) tc::cp_async8(sh + (c * 4 + q) * 32 * S3_G * 8, xb + c * plane + (size_t)yy * W + xx);
-                    }
+                    for (int q = 0; q < 4; ++q)
+                        if (y0 + 4 * gi + q < H) tc::cp_async8(sh + (c * 4 + q) * 32 * S3_G * 8, xb + (off0 + c * hw + q * W));
                 tc::cp_async_commit();
             }
             float2 o[2][3][2];
             conv3_item<S2_W, S2_RP * S2_W, false, SCI_UNROLL_L3>(s2 + (2 * gi) * S2_W + j, wt.w[2], o, o);
             if (pairs) {
                 tc::cp_async_wait<0>();
-                const size_t off0 = (size_t)b * 3 * plane + (size_t)(y0 + 4 * gi) * W + xx;
-                float* ip = illu ? illu + off0 : nullptr;
-                float* rp = r + off0;
+                float* ip = illu ? illu + (size_t)b * 3 * plane : nullptr;
+                float* rp = r + (size_t)b * 3 * plane;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
 #pragma unroll
@@ -324,8 +305,8 @@ sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* _
                             il[col] = fminf(fmaxf(sg + xin[col], 0.0001f), 1.f);
                             rv[col] = fminf(fmaxf(xin[col] * sfu_rcp(il[col]), 0.f), 1.f);
                         }
-                        if (ip) *reinterpret_cast<float2*>(ip + c * plane + (size_t)q * W) = make_float2(il[0], il[1]);
-                        *reinterpret_cast<float2*>(rp + c * plane + (size_t)q * W) = make_float2(rv[0], rv[1]);
+                        if (ip) *reinterpret_cast<float2*>(ip + (off0 + c * hw + q * W)) = make_float2(il[0], il[1]);
+                        *reinterpret_cast<float2*>(rp + (off0 + c * hw + q * W)) = make_float2(rv[0], rv[1]);
                     }
                 }
             } else {  // odd widths: scalar accesses
@@ -382,7 +363,7 @@ extern "C" int b200_sci_forward(const float* x, const float* packed_host, float*
                                 void* stream) {
     if (!x || !packed_host || !r) return B200_ERR_NULL;
     if (B <= 0 || H <= 0 || W <= 0) return B200_ERR_BAD_SHAPE;
-    if (B > 65535) return B200_ERR_UNSUPPORTED;
+    if (B > 65535 || 3LL * H * W + W >= (1LL << 31)) return B200_ERR_UNSUPPORTED;  // grid.z; 32-bit offsets inside a frame
     if (!b200::aligned16(x) || !b200::aligned16(r) || (illu && !b200::aligned16(illu))) return B200_ERR_MISALIGNED;
     b200::SciWeights pk;
     memcpy(&pk, packed_host, sizeof(pk));
@@ -403,6 +384,6 @@ extern "C" int b200_sci_forward(const float* x, const float* packed_host, float*
         (void)cudaGetLastError();
         return B200_ERR_LAUNCH;
     }
-    b200::sci_fused_kernel<<<grid, 256, b200::SCI_SMEM, (cudaStream_t)stream>>>(x, illu, r, wt, H, W);
+    b200::sci_fused_kernel<<<grid, b200::SCI_NT, b200::SCI_SMEM, (cudaStream_t)stream>>>(x, illu, r, wt, H, W);
     return b200::launch_status();
 }
