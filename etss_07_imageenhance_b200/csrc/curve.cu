@@ -107,6 +107,74 @@ static int launch_curve(const float* x, const float* a, float* y, int B, int C, 
     return launch_status();
 }
 
+// ---- GCENet's curve loop with the brightness attention map (gcenet.py:469-484) ------------------------------------
+//   bam = (1 - V)^gamma, V = max(R, G, B)                       (nn/modules/prior/image.py:269-272; kornia's HSV value)
+//   iters times:  bright = e * (1 - bam);  dark = e * bam;  e = bright + dark + a * (dark^2 - dark)
+// with ONE 3-channel map `a` for all iterations.  Same rounding sequence as the ATen ops (no contraction); the only
+// operation that is not correctly rounded on either side is the pow.
+struct GceOut {
+    float* enhanced;
+    float* bam;     // [B,1,H,W] or nullptr
+    float* bright;  // [B,3,H,W] or nullptr: the last iteration's
+    float* dark;    // [B,3,H,W] or nullptr
+};
+
+__device__ __forceinline__ void gce_step(float& e, float a, float bam, float one_minus_bam, float& bright, float& dark) {
+    bright = __fmul_rn(e, one_minus_bam);
+    dark = __fmul_rn(e, bam);
+    e = __fadd_rn(__fadd_rn(bright, dark), __fmul_rn(a, __fsub_rn(__fmul_rn(dark, dark), dark)));
+}
+
+// VEC: one item = 4 consecutive pixels of one frame in all three channels (H*W % 4 == 0, 16-byte aligned bases)
+template <bool VEC>
+__global__ void __launch_bounds__(256) gce_curve_kernel(const float* __restrict__ image, const float* __restrict__ adjust,
+                                                        GceOut out, long long frames, long long hw, int iters,
+                                                        float gamma) {
+    constexpr int V = VEC ? 4 : 1;
+    const long long per = hw / V, total = frames * per;
+    for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < total;
+         it += (long long)gridDim.x * blockDim.x) {
+        const long long f = it / per, p = (it - f * per) * V;
+        const long long o = f * 3 * hw + p;
+        float e[3][4], a[3][4], br[3][4], dk[3][4], bam[4];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            if (VEC) {
+                const float4 ev = ld_stream4(image + o + c * hw), av = ld_stream4(adjust + o + c * hw);
+                e[c][0] = ev.x, e[c][1] = ev.y, e[c][2] = ev.z, e[c][3] = ev.w;
+                a[c][0] = av.x, a[c][1] = av.y, a[c][2] = av.z, a[c][3] = av.w;
+            } else {
+                e[c][0] = image[o + c * hw];
+                a[c][0] = adjust[o + c * hw];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            bam[k] = powf(__fsub_rn(1.f, fmaxf(fmaxf(e[0][k], e[1][k]), e[2][k])), gamma);
+            const float omb = __fsub_rn(1.f, bam[k]);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                br[c][k] = dk[c][k] = 0.f;
+                for (int i = 0; i < iters; ++i) gce_step(e[c][k], a[c][k], bam[k], omb, br[c][k], dk[c][k]);
+            }
+        }
+        auto put = [&](float* base, const float* v, long long off) {
+            if (VEC) {
+                st_stream4(base + off, make_float4(v[0], v[1], v[2], v[3]));
+            } else {
+                base[off] = v[0];
+            }
+        };
+        if (out.bam) put(out.bam, bam, f * hw + p);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            put(out.enhanced, e[c], o + c * hw);
+            if (out.bright) put(out.bright, br[c], o + c * hw);
+            if (out.dark) put(out.dark, dk[c], o + c * hw);
+        }
+    }
+}
+
 // ---- u8 HWC <-> fp32 NCHW (C = 3) ------------------------------------------------
 // to_image_tensor(normalize=True) -> normalize_image_by_range (core/image/photometry.py:262-263):
 //   image = (image - 0.0) * ratio + 0.0   with ratio = 1/255 (a Python double) applied to an fp32 tensor,
@@ -244,6 +312,32 @@ extern "C" int b200_curve_shared(const float* x, const float* a, float* y, int B
 extern "C" int b200_curve_per_iter(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters,
                                    void* stream) {
     return b200::launch_curve<true>(x, a, y, B, C, H, W, iters, stream);
+}
+
+extern "C" int b200_gce_curve(const float* image, const float* adjust, float* enhanced, float* bam, float* bright,
+                              float* dark, int B, int H, int W, int iters, float gamma, void* stream) {
+    if (!image || !adjust || !enhanced) return B200_ERR_NULL;
+    if (B <= 0 || H <= 0 || W <= 0 || iters < 0) return B200_ERR_BAD_SHAPE;
+    // gcenet.py:470-475: without a gamma the loop is the plain shared-map curve and there is no map to return
+    if (gamma == 0.f) return b200::launch_curve<false>(image, adjust, enhanced, B, 3, H, W, iters, stream);
+    const float* in[2] = {image, adjust};
+    float* outs[4] = {enhanced, bam, bright, dark};
+    bool al = true;
+    for (const float* q : in) al = al && b200::aligned16(q);
+    for (float* q : outs) al = al && (!q || b200::aligned16(q));
+    if (!al) return B200_ERR_MISALIGNED;
+    const long long hw = (long long)H * W;
+    const bool vec = hw % 4 == 0;
+    const long long total = (long long)B * (vec ? hw / 4 : hw);
+    long long blocks = (total + 255) / 256;
+    const long long cap = (long long)B200_NUM_SMS * 16;
+    if (blocks > cap) blocks = cap;
+    const b200::GceOut o{enhanced, bam, bright, dark};
+    if (vec)
+        b200::gce_curve_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(image, adjust, o, B, hw, iters, gamma);
+    else
+        b200::gce_curve_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(image, adjust, o, B, hw, iters, gamma);
+    return b200::launch_status();
 }
 
 extern "C" int b200_u8hwc_to_f32nchw(const uint8_t* src, float* dst, int B, int H, int W, void* stream) {

@@ -8,6 +8,7 @@ infrastructure).  Inference-only: no autograd formula is registered.
 Replaces the ATen op sequence of
   src/mon/vision/enhance/llie/zero_dce/zero_dce.py:176-188      (dce_forward)
   src/mon/vision/enhance/llie/zero_dce/zero_dcepp.py:186-203    (dcepp_forward, curve_shared)
+  src/mon/vision/enhance/llie/gcenet/gcenet.py:469-484          (gce_curve)
   src/mon_extra/vision/enhance/llie/sci/model.py:36-45,155-159  (sci_forward)
   src/mon_extra/vision/enhance/llie/ruas/model.py:46-149,202-206  (ruas_forward)
 """
@@ -22,7 +23,7 @@ from . import _lib
 from ._lib import PRECISIONS, check, lib, ptr_array
 
 __all__ = [
-    "curve_shared", "curve_per_iter", "dcepp_pack", "dcepp_forward", "dcepp_lowres", "dcepp_apply",
+    "curve_shared", "curve_per_iter", "gce_curve", "dcepp_pack", "dcepp_forward", "dcepp_lowres", "dcepp_apply",
     "dce_pack", "dce_forward", "dcev_pack", "dcev_core", "sci_pack", "sci_forward", "ruas_pack", "ruas_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
     "current_stream_ptr", "require_device",
 ]
@@ -77,6 +78,39 @@ def curve_shared(x: Tensor, a: Tensor, iters: int) -> Tensor:
 @curve_shared.register_fake
 def _(x, a, iters):
     return torch.empty_like(x)
+
+
+@torch.library.custom_op("b200dce::gce_curve", mutates_args=(), device_types="cuda")
+def gce_curve(image: Tensor, adjust: Tensor, iters: int, gamma: float, debug: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """GCENet's enhancement loop (gcenet.py:469-484): (enhanced, bam, bright, dark).  `enhanced` is the loop's result
+    before the guided filter; bam [B,1,H,W] = (1 - max(R,G,B))^gamma (prior/image.py:269-272) and the last iteration's
+    bright / dark [B,3,H,W] are returned when `debug` (the reference's debug dict) and gamma != 0, else empty [0]
+    tensors (the reference returns None for them when `bam_gamma in [None, 0.0]`)."""
+    image, adjust = _img(image, "image"), _img(adjust, "adjust")
+    if adjust.shape != image.shape:
+        raise ValueError(f"b200dce::gce_curve: adjust {tuple(adjust.shape)} must match image {tuple(image.shape)}")
+    B, _, H, W = image.shape
+    enhanced = torch.empty_like(image)
+    extra = debug and gamma != 0.0
+    bam = image.new_empty(B, 1, H, W) if extra else image.new_empty(0)
+    bright = torch.empty_like(image) if extra else image.new_empty(0)
+    dark = torch.empty_like(image) if extra else image.new_empty(0)
+    if image.numel():
+        with torch.cuda.device(image.device):
+            check(lib().b200_gce_curve(image.data_ptr(), adjust.data_ptr(), enhanced.data_ptr(),
+                                       bam.data_ptr() if extra else None, bright.data_ptr() if extra else None,
+                                       dark.data_ptr() if extra else None, B, H, W, iters, float(gamma),
+                                       current_stream_ptr()), "b200_gce_curve")
+    return enhanced, bam, bright, dark
+
+
+@gce_curve.register_fake
+def _(image, adjust, iters, gamma, debug):
+    B, _, H, W = image.shape
+    extra = debug and gamma != 0.0
+    e = image.new_empty(0)
+    return (torch.empty_like(image), image.new_empty(B, 1, H, W) if extra else e,
+            torch.empty_like(image) if extra else e, torch.empty_like(image) if extra else e)
 
 
 @torch.library.custom_op("b200dce::curve_per_iter", mutates_args=(), device_types="cuda")

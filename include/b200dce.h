@@ -61,6 +61,17 @@ int b200_check_device(void);
  * Bit-exact against ATen on CPU (mul, sub, mul, add with no contraction). */
 int b200_curve_shared(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream);
 
+/* GCENet's enhancement loop with the brightness attention map: bam = (1 - max(R,G,B))^gamma, then `iters` times
+ *   bright = e*(1 - bam); dark = e*bam; e = bright + dark + adjust*(dark*dark - dark)
+ * with one map `adjust` [B,3,H,W] for every iteration; `enhanced` [B,3,H,W] is the loop's result BEFORE the guided
+ * filter.  Replaces src/mon/vision/enhance/llie/gcenet/gcenet.py:469-484 and
+ * src/mon/nn/modules/prior/image.py:269-272 (BrightnessAttentionMap without the optional median blur).
+ * gamma == 0 selects the reference's plain branch (gcenet.py:470-475 = b200_curve_shared); bam / bright / dark are
+ * then not written.  bam [B,1,H,W], bright / dark [B,3,H,W] (the last iteration's; the reference's debug outputs)
+ * may be NULL.  All arithmetic but the pow is rounded as ATen rounds it; 16-byte aligned bases. */
+int b200_gce_curve(const float* image, const float* adjust, float* enhanced, float* bam, float* bright, float* dark,
+                   int B, int H, int W, int iters, float gamma, void* stream);
+
 /* Per-iteration maps: `a` is [B, C*iters, H, W]; iteration i uses channels
  * [i*C, (i+1)*C).  Replaces zero_dce.py:183-188 (torch.split + loop). */
 int b200_curve_per_iter(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream);

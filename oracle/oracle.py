@@ -195,6 +195,26 @@ def curve_per_iter(x: torch.Tensor, a: torch.Tensor, num_iters: int = 8) -> torc
 
 
 @torch.no_grad()
+def gce_curve_loop(image: torch.Tensor, adjust: torch.Tensor, num_iters: int, bam_gamma: float) -> dict:
+    """GCENet.forward's enhancement loop, src/mon/vision/enhance/llie/gcenet/gcenet.py:469-484, with the brightness
+    attention map of src/mon/nn/modules/prior/image.py:269-272 (tensor branch, denoise_ksize=None): V is kornia's HSV
+    value = the channel maximum.  `enhanced` is the value BEFORE the guided filter (gcenet.py:485)."""
+    if bam_gamma in [None, 0.0]:
+        enhanced, bam, bright, dark = image, None, None, None
+        for _ in range(num_iters):
+            enhanced = enhanced + adjust * (torch.pow(enhanced, 2) - enhanced)
+    else:
+        v = image.max(dim=-3, keepdim=True)[0]
+        bam = torch.pow((1 - v), bam_gamma)
+        enhanced, bright, dark = image, None, None
+        for _ in range(num_iters):
+            bright = enhanced * (1 - bam)
+            dark = enhanced * bam
+            enhanced = bright + dark + adjust * (torch.pow(dark, 2) - dark)
+    return {"enhanced": enhanced, "bam": bam, "bright": bright, "dark": dark}
+
+
+@torch.no_grad()
 def zero_dce_forward(x: torch.Tensor, sd: dict, num_iters: int = 8) -> dict:
     """ZeroDCE_RE.forward (zero_dce.py:173-191).  Returns the reference's dict
     (adjust_0.., adjust, enhanced — in that insertion order)."""

@@ -224,6 +224,43 @@ def load_reference_zero_dce_v():
     return zv.ZeroDCEV
 
 
+def load_reference_gce_loop(iutils):
+    """The reference's own statements for GCENet's enhancement loop, run here without the rest of the class:
+      * `BrightnessAttentionMap` from src/mon/nn/modules/prior/image.py, the file loaded unmodified under the stub
+        `mon` with `core.get_image_channel` = the reference's own (core/image/utils.py:180) and a stand-in `kornia`
+        (not installed here) whose `color.rgb_to_hsv` returns (0, 0, V), V = the channel maximum -- kornia's
+        definition of the value channel, the only one the map reads;
+      * the `if self.bam_gamma in [None, 0.0]: ... else: ...` statement of `GCENet.forward`
+        (src/mon/vision/enhance/llie/gcenet/gcenet.py:469-484), cut out of the parsed file by its AST node and compiled
+        into `loop(self, image, adjust)`; nothing is retyped, the EnhanceNet / guided filter around it are not run."""
+    import ast
+    core = sys.modules["mon.core"]
+    core.get_image_channel = iutils.get_image_channel
+    if "kornia" not in sys.modules:
+        kornia = types.ModuleType("kornia")
+        kornia.color = types.ModuleType("kornia.color")
+        kornia.filters = types.ModuleType("kornia.filters")
+
+        def rgb_to_hsv(image, eps=1e-8):
+            v = image.max(dim=-3, keepdim=True)[0]
+            return torch.cat([torch.zeros_like(v), torch.zeros_like(v), v], dim=-3)
+        kornia.color.rgb_to_hsv = rgb_to_hsv
+        sys.modules["kornia"], sys.modules["kornia.color"], sys.modules["kornia.filters"] = kornia, kornia.color, kornia.filters
+    prior = _load_file("ref_prior_image", REF / "src/mon/nn/modules/prior/image.py")
+    src = (REF / "src/mon/vision/enhance/llie/gcenet/gcenet.py").read_text()
+    tree = ast.parse(src)
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "GCENet")
+    fwd = next(n for n in cls.body if isinstance(n, ast.FunctionDef) and n.name == "forward")
+    node = next(n for n in fwd.body if isinstance(n, ast.If) and "bam_gamma" in ast.unparse(n.test))
+    assert (node.lineno, node.end_lineno) == (469, 484), (node.lineno, node.end_lineno)
+    fn = ast.parse("def loop(self, image, adjust):\n    pass\n    return enhanced, bam, bright, dark")
+    fn.body[0].body[0] = node
+    ast.fix_missing_locations(fn)
+    ns = {"torch": torch}
+    exec(compile(fn, "gcenet.py:469-484", "exec"), ns)
+    return ns["loop"], prior.BrightnessAttentionMap
+
+
 def to_upstream_keys(sd: dict) -> dict:
     return {k.replace("dw_conv", "depth_conv").replace("pw_conv", "point_conv"): v for k, v in sd.items()}
 
@@ -422,6 +459,31 @@ def main():
                         u8=ref_u.numpy())
     report.append(f"u8 wire: oracle == reference to_image_tensor(normalize=True) / to_image_nparray(denormalize=True); "
                   f"multiply by fl32(1/255) differs from /255.0 for {nb} of the 256 byte values ({n_div} elements of the fixture)")
+
+    # ---------------- GCENet's curve loop with the brightness attention map (partial) ----------------
+    gce_loop, BAM = load_reference_gce_loop(iutils)
+    g = torch.Generator().manual_seed(777)
+    gimg = O.synthetic_lowlight(2, 37, 52, seed=702)
+    gimg[0, :, 0, :3] = torch.tensor([0.0, 1.0, 0.25]).view(1, 3)       # V = 0 (bam 1), V = 1 (bam 0)
+    gadj = torch.rand(2, 3, 37, 52, generator=g) * 2 - 1                # GCENet's EnhanceNet ends in tanh
+    arrs = {"image": gimg.numpy(), "adjust": gadj.numpy()}
+    for gamma, iters in ((2.5, 8), (1.0, 4), (0.0, 8)):
+        self_ = types.SimpleNamespace(bam_gamma=gamma, num_iters=iters, bam=BAM(gamma=gamma, denoise_ksize=None))
+        with torch.no_grad():
+            re, rb, rbr, rdk = gce_loop(self_, gimg, gadj)
+        got = O.gce_curve_loop(gimg, gadj, iters, gamma)
+        eq(got["enhanced"], re, f"gce/{gamma}/enhanced")
+        tag = f"g{gamma}_i{iters}"
+        arrs[f"{tag}:enhanced"] = re.numpy()
+        if gamma:
+            for k, r_ in (("bam", rb), ("bright", rbr), ("dark", rdk)):
+                eq(got[k], r_, f"gce/{gamma}/{k}")
+                arrs[f"{tag}:{k}"] = r_.numpy()
+        else:
+            assert rb is None and rbr is None and rdk is None and got["bam"] is None
+    np.savez_compressed(GOLD / "gce_curve.npz", **arrs)
+    report.append("gce curve loop: oracle == the reference's own statements (gcenet.py:469-484 cut out by AST, "
+                  "prior/image.py BrightnessAttentionMap with kornia's V = channel maximum) for gamma 2.5 / 1.0 / 0.0")
 
     (GOLD / "PIN_REPORT.txt").write_text(
         f"generated by oracle/pin_against_reference.py with torch {torch.__version__} (CPU, fp32)\n" +

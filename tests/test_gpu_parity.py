@@ -698,3 +698,36 @@ def test_zero_dce_v_core_shapes_vs_oracle(cuda_dev, B, H, W, S):
     assert torch.equal(out["image_v"].cpu(), ref["image_v"]) and torch.equal(out["image_v_lr"].cpu(), ref["image_v_lr"])
     assert out["adjust"].shape == (B, 15, S, S)
     assert maxerr(out["adjust"], ref["adjust"]) <= TIGHT and maxerr(out["image_v_fixed_lr"], ref["image_v_fixed_lr"]) <= TIGHT
+
+
+# ------------------------------------------------------------------ GCENet's curve loop (partial)
+GCE_TOL = 2e-6   # everything but the pow is rounded as ATen rounds it; powf (2 ulp) vs ATen's pow on values in [0, 1]
+
+
+def test_gce_curve_golden(cuda_dev):
+    """b200dce::gce_curve against the reference's own loop statements (tests/golden/gce_curve.npz)."""
+    z = np.load(GOLDEN_DIR / "gce_curve.npz")
+    image, adjust = torch.from_numpy(z["image"]).to(cuda_dev), torch.from_numpy(z["adjust"]).to(cuda_dev)
+    for gamma, iters in ((2.5, 8), (1.0, 4), (0.0, 8)):
+        tag = f"g{gamma}_i{iters}"
+        enh, bam, bright, dark = torch.ops.b200dce.gce_curve(image, adjust, iters, gamma, True)
+        if gamma == 0.0:   # the plain branch: bit-exact, and nothing else is returned
+            assert torch.equal(enh.cpu(), torch.from_numpy(z[f"{tag}:enhanced"]))
+            assert bam.numel() == bright.numel() == dark.numel() == 0
+            continue
+        for got, k in ((enh, "enhanced"), (bam, "bam"), (bright, "bright"), (dark, "dark")):
+            assert maxerr(got, torch.from_numpy(z[f"{tag}:{k}"])) <= GCE_TOL, (gamma, k)
+        only = torch.ops.b200dce.gce_curve(image, adjust, iters, gamma, False)
+        assert torch.equal(only[0], enh) and only[1].numel() == 0
+
+
+@pytest.mark.parametrize("B,H,W", [(1, 1, 1), (2, 37, 45), (1, 1080, 1920), (3, 30, 50)])
+def test_gce_curve_shapes_vs_oracle(cuda_dev, B, H, W):
+    g = torch.Generator().manual_seed(B * 100 + W)
+    image = O.synthetic_lowlight(B, H, W, seed=B + H)
+    adjust = torch.rand(B, 3, H, W, generator=g) * 2 - 1
+    ref = O.gce_curve_loop(image, adjust, 8, 2.5)
+    enh, bam, bright, dark = torch.ops.b200dce.gce_curve(image.to(cuda_dev), adjust.to(cuda_dev), 8, 2.5, True)
+    assert bam.shape == (B, 1, H, W)
+    for got, k in ((enh, "enhanced"), (bam, "bam"), (bright, "bright"), (dark, "dark")):
+        assert maxerr(got, ref[k]) <= GCE_TOL, k

@@ -4,7 +4,11 @@ import numpy as np
 import pytest
 import torch
 
+from pathlib import Path
+
 from oracle import oracle as O
+
+GOLDEN_DIR = Path(__file__).resolve().parent / "golden"
 
 CASES_DCEPP = [("dcepp_sf1", 1), ("dcepp_sf2", 2), ("dcepp_sf12", 12)]
 
@@ -124,3 +128,19 @@ def test_oracle_zero_dce_v_core_matches_reference_golden(golden, regime):
     assert list(got.keys()) == ["image_v", "image_v_lr", "adjust", "image_v_fixed_lr"]
     for k in got:
         assert torch.equal(got[k], outs[k]), k
+
+
+def test_oracle_gce_curve_loop_matches_reference_golden():
+    """tests/golden/gce_curve.npz = GCENet.forward's own loop statements (gcenet.py:469-484) and the reference's
+    BrightnessAttentionMap, run by oracle/pin_against_reference.py."""
+    z = np.load(GOLDEN_DIR / "gce_curve.npz")
+    image, adjust = torch.from_numpy(z["image"]), torch.from_numpy(z["adjust"])
+    for gamma, iters in ((2.5, 8), (1.0, 4), (0.0, 8)):
+        got = O.gce_curve_loop(image, adjust, iters, gamma)
+        tag = f"g{gamma}_i{iters}"
+        assert torch.equal(got["enhanced"], torch.from_numpy(z[f"{tag}:enhanced"]))
+        for k in ("bam", "bright", "dark"):
+            if gamma:
+                assert torch.equal(got[k], torch.from_numpy(z[f"{tag}:{k}"])), k
+            else:
+                assert got[k] is None
