@@ -16,7 +16,7 @@ LIB_PATH = PKG / "lib" / "libb200dce.so"
 # error codes (include/b200dce.h)
 OK = 0
 ERR_NULL, ERR_BAD_SHAPE, ERR_MISALIGNED, ERR_UNSUPPORTED = -1, -2, -3, -4
-ERR_WORKSPACE, ERR_LAUNCH, ERR_NO_DEVICE = -5, -6, -7
+ERR_WORKSPACE, ERR_LAUNCH, ERR_NO_DEVICE, ERR_TOO_LARGE = -5, -6, -7, -8
 PREC_FP32, PREC_BF16, PREC_BF16X3, PREC_BF16X3_MMA = 0, 1, 2, 3
 # "fp32" is the reference's contract (fp32 in / out, max-abs <= 1e-3 against its forward), served by the 3-term
 # split-bf16 tcgen05 kernels (measured <= 2.5e-4, typically 1e-5); "fp32_exact" keeps every product in fp32 on the CUDA
@@ -42,6 +42,9 @@ _SIGNATURES = {
                                    c_void_p, c_size_t, c_void_p]),
     "b200_dcepp_forward_marked": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                           c_void_p, c_size_t, c_void_p, c_void_p]),
+    "b200_dcepp_static_scratch_bytes": (c_size_t, []),
+    "b200_dcepp_forward_static": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                          c_void_p]),
     "b200_dcepp_lowres": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_size_t,
                                   c_void_p]),
     "b200_dcepp_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,

@@ -13,6 +13,7 @@ extern "C" const char* b200_strerror(int code) {
         case B200_ERR_WORKSPACE: return "workspace too small";
         case B200_ERR_LAUNCH: return "CUDA launch failed";
         case B200_ERR_NO_DEVICE: return "no sm_100 (B200) CUDA device is current";
+        case B200_ERR_TOO_LARGE: return "problem too large for the built-in scratch array of this *_static entry point (use the variant that takes a workspace)";
         default: return "unknown b200dce error";
     }
 }

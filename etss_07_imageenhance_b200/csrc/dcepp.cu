@@ -11,6 +11,8 @@
 //       `adjust` once each.  Persistent CTAs, grid = multiple of the SM count.
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "dcepp_mma.cuh"
 
@@ -582,4 +584,54 @@ extern "C" int b200_dcepp_forward_marked(const float* x, const float* packed, fl
                                          void* stream, void* mid_event) {
     return dcepp_forward(x, packed, enhanced, adjust, B, H, W, sf, iters, workspace, workspace_bytes, stream,
                          (cudaEvent_t)mid_event);
+}
+
+// ------------------------------------------------------------------------------------------------
+// b200_dcepp_forward_static: the same forward with its scratch (feature maps, low-res curve map, tile flags) in a
+// file-scope device array instead of a caller-provided workspace -- for callers that cannot call cudaMalloc (CUDA graph
+// capture, tight serving loops).  Every GPU that loads the library holds the array until the process exits.
+// `g_dcepp_static_scratch` names a device symbol: in host code it is only a handle for cudaGetSymbolAddress, never
+// an address to hand to a kernel.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_dcepp_static_scratch[B200_DCEPP_STATIC_SCRATCH_BYTES];
+
+// device address of the array on the CURRENT device, looked up once per device (with that device current)
+static int dcepp_static_scratch_ptr(void** out) {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static void* ptrs[MAX_DEV] = {};
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+        (void)cudaGetLastError();
+        return B200_ERR_NO_DEVICE;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        if (cudaGetSymbolAddress(&p, g_dcepp_static_scratch) != cudaSuccess || !p) {
+            (void)cudaGetLastError();
+            return B200_ERR_LAUNCH;
+        }
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return B200_OK;
+}
+
+extern "C" size_t b200_dcepp_static_scratch_bytes(void) { return (size_t)B200_DCEPP_STATIC_SCRATCH_BYTES; }
+
+extern "C" int b200_dcepp_forward_static(const float* x, const float* packed, float* enhanced, float* adjust, int B,
+                                         int H, int W, int sf, int iters, void* stream) {
+    if (!x || !packed || !enhanced) return B200_ERR_NULL;
+    if (B <= 0 || H <= 0 || W <= 0 || sf <= 0 || iters < 0) return B200_ERR_BAD_SHAPE;
+    if (H % sf != 0 || W % sf != 0) return B200_ERR_BAD_SHAPE;
+    const size_t need = b200_dcepp_workspace_bytes(B, H, W, sf);
+    if (need > (size_t)B200_DCEPP_STATIC_SCRATCH_BYTES) return B200_ERR_TOO_LARGE;
+    void* scratch = nullptr;
+    const int rc = dcepp_static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    // Nothing in the array has to start at zero from the caller's side: the layer-1 launch of every forward clears the
+    // tile counters and dependency flags it is going to use before the persistent launch reads them; feature maps and
+    // the curve map are fully written before they are read.  (`need`, not the array size: no debug trace area.)
+    return dcepp_forward(x, packed, enhanced, adjust, B, H, W, sf, iters, scratch, need, stream, nullptr);
 }

@@ -39,6 +39,7 @@ extern "C" {
 #define B200_ERR_WORKSPACE (-5)   /* workspace too small (see *_workspace_bytes) */
 #define B200_ERR_LAUNCH (-6)      /* CUDA launch error */
 #define B200_ERR_NO_DEVICE (-7)   /* no sm_100 CUDA device is current */
+#define B200_ERR_TOO_LARGE (-8)   /* the problem needs more scratch than a *_static entry point's built-in array holds */
 
 /* precision selector for the Zero-DCE conv stack */
 #define B200_PREC_FP32 0   /* fp32 CUDA-core direct convolution (FFMA2), fp32 accumulate            */
@@ -116,6 +117,24 @@ int b200_dcepp_forward(const float* x, const float* packed, float* enhanced, flo
 int b200_dcepp_forward_marked(const float* x, const float* packed, float* enhanced, float* adjust_or_null, int B, int H,
                               int W, int scale_factor, int iters, void* workspace, size_t workspace_bytes, void* stream,
                               void* mid_event);
+
+/* b200_dcepp_forward WITHOUT a workspace argument and without any allocation: the scratch (feature maps, low-resolution
+ * curve map, tile flags) lives in a file-scope `static __device__` array of B200_DCEPP_STATIC_SCRATCH_BYTES inside the
+ * library, which every GPU that loads the library holds until the process exits.  This entry point has NO counterpart
+ * in the reference; it was added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  It calls no cudaMalloc / cudaFree and no
+ * allocating library routine; inputs and outputs are the caller's.  Same results as b200_dcepp_forward bit for bit.
+ *   - Limit: b200_dcepp_workspace_bytes(B, H, W, scale_factor) must be <= B200_DCEPP_STATIC_SCRATCH_BYTES (16 MiB:
+ *     one 1080p frame at scale_factor 12 needs 9.0 MiB, one 4K frame at 12 needs 35.8 MiB and does not fit); beyond
+ *     that it returns B200_ERR_TOO_LARGE and launches nothing -- use b200_dcepp_forward with a workspace.
+ *   - The array is shared by every call in the process (per GPU) and keeps the previous call's contents; each call
+ *     clears the counters and flags it uses itself.  Calls that can overlap on the GPU (different streams, or
+ *     several host threads on different streams) RACE on it: keep all calls of this entry point on one stream, or
+ *     order them with events. */
+#define B200_DCEPP_STATIC_SCRATCH_BYTES (16u << 20)
+size_t b200_dcepp_static_scratch_bytes(void);
+int b200_dcepp_forward_static(const float* x, const float* packed, float* enhanced, float* adjust_or_null, int B, int H,
+                              int W, int scale_factor, int iters, void* stream);
 
 /* Only the low-resolution curve-estimation net (stages a3+a4): writes a_lr
  * [B,3,H/sf,W/sf].  Exposed for tests and for callers that cache the map. */
