@@ -2,8 +2,8 @@
 // EnhanceNetwork.forward :36-45, layers=1, channels=3, BatchNorm2d eval) as ONE fused pass:
 //   fea1 = relu(conv3x3(x));  fea2 = fea1 + relu(bn(conv3x3(fea1)));  fea3 = sigmoid(conv3x3(fea2));
 //   illu = clamp(fea3 + x, 1e-4, 1);  r = clamp(x / illu, 0, 1)
-// CTA tile 32x60 output pixels, 9 warps; the three stacked 3x3 layers are evaluated on shrinking halo regions held in
-// shared memory (x: 38x66, fea1: 36x64, fea2: 36x62), so x is read once from HBM and illu / r written once.
+// CTA tile 28x60 output pixels, 8 warps; the three stacked 3x3 layers are evaluated on shrinking halo regions held in
+// shared memory (x: 34x66, fea1: 32x64, fea2: 32x62), so x is read once from HBM and illu / r written once.
 //
 // The work is 3 x 81 MAC per position on the fp32 pipe (~550 FLOP per output pixel with the halo recompute): the
 // kernel is bound by the FMA pipe and by instruction issue (both ~65 % busy), not by HBM, so the inner loop is built
@@ -19,7 +19,8 @@
 //   * every FMA carries one weight as a scalar broadcast from a uniform register; the 252 weights travel as a by-value
 //     kernel parameter in the constant bank, reordered on the host to the order the loop consumes them;
 //   * tile width 60: with two halo columns per side layer 1 is exactly 32 column pairs = one warp per row group, no
-//     left-over columns; 9 / 9 / 8 row groups of 4 rows = 9 warps, one round per layer;
+//     left-over columns; 8 / 8 / 7 row groups of 4 rows = 8 warps (two per scheduler), one round per layer; 1080p is
+//     39 x 32 tiles per frame = 45.0 waves of 3 CTAs per SM for 16 frames;
 //   * sigmoid and the division on the SFU in their flush-to-zero forms (see sfu_ex2); tiles whose halo lies inside
 //     the image take a path without masks; the x values for the epilogue come by cp.async under the last conv.
 // History of the measurements (16 x 1080p): profiles/r02_summary.md section 6.
@@ -50,13 +51,19 @@ struct __align__(16) SciKernelWeights {
 #ifndef SCI_UNROLL_L3
 #define SCI_UNROLL_L3 true
 #endif
-constexpr int S_TH = 32, S_TW = 60;           // with the two halo columns per side layer 1 is exactly 32 column pairs wide
-constexpr int SCI_NT = 32 * (S_TH / 4 + 1);   // one warp per row group of the tallest layer (9 groups of 4 rows)
+#ifndef SCI_TH
+#define SCI_TH 28
+#endif
+#ifndef SCI_CTAS
+#define SCI_CTAS 3
+#endif
+constexpr int S_TH = SCI_TH, S_TW = 60;           // with the two halo columns per side layer 1 is exactly 32 column pairs wide
+constexpr int SCI_NT = 32 * (S_TH / 4 + 1);   // one warp per row group of the tallest layer (S_TH / 4 + 1 groups of 4 rows)
 constexpr int S1_G = S_TH / 4 + 1, S2_G = S_TH / 4 + 1, S3_G = S_TH / 4;  // row groups (4 rows) per layer
-constexpr int SX_RP = 2 * S1_G + 1, SX_W = S_TW + 6;  // x:    rows y0-3 .. y0+34 as 19 row pairs, columns x0-3 .. x0+62
-constexpr int S1_RP = 2 * S2_G + 1, S1_W = S_TW + 4;  // fea1: rows y0-2 .. y0+33 (+ one pair never written, read by the
+constexpr int SX_RP = 2 * S1_G + 1, SX_W = S_TW + 6;  // x:    rows y0-3 .. y0+S_TH+2 as 2*S1_G+1 row pairs, columns x0-3 .. x0+62
+constexpr int S1_RP = 2 * S2_G + 1, S1_W = S_TW + 4;  // fea1: rows y0-2 .. y0+S_TH+1 (+ one pair never written, read by the
                                                       //       two fea2 rows that feed nothing), columns x0-2 .. x0+61
-constexpr int S2_RP = 2 * S2_G, S2_W = S_TW + 2;      // fea2: rows y0-1 .. y0+34, columns x0-1 .. x0+60
+constexpr int S2_RP = 2 * S2_G, S2_W = S_TW + 2;      // fea2: rows y0-1 .. y0+S_TH+2, columns x0-1 .. x0+60
 static_assert(S1_W / 2 <= 32 && S_TW % 4 == 0, "a warp covers a row group; tiles start on 16-byte boundaries");
 constexpr int SCI_SX_BYTES = 8 * 3 * SX_RP * SX_W, SCI_S1_BYTES = 8 * 3 * S1_RP * S1_W, SCI_S2_BYTES = 8 * 3 * S2_RP * S2_W;
 // fea2 reuses the x planes' bytes (x is only read by layer 1); 58 KB: three CTAs per SM.  During layer 3 the dead fea1
@@ -173,7 +180,7 @@ __device__ __forceinline__ void sci_store_item(float2* __restrict__ plane, int g
         }
 }
 
-__global__ void __launch_bounds__(SCI_NT, 3)
+__global__ void __launch_bounds__(SCI_NT, SCI_CTAS)
 sci_fused_kernel(const float* __restrict__ x, float* __restrict__ illu, float* __restrict__ r,
                  const __grid_constant__ SciKernelWeights wt, int H, int W) {
     extern __shared__ __align__(16) float2 sci_smem[];
