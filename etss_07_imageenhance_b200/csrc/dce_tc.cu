@@ -770,7 +770,8 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
             const int nA = nB + 2;
             const int px = x0 - 1 + m;  // image column of this lane's pixel
             const bool px_ok = px >= 0 && px < W;
-            for (int j = (int)((ga ^ (uint32_t)par) & 1); j < nA + 2; j += TP_EPG) {  // this group's rows: g % 2 == par
+            // TP_EPG == 2: this group's rows are those with g % 2 == par (one group: every row)
+            for (int j = TP_EPG == 2 ? (int)((ga ^ (uint32_t)par) & 1) : 0; j < nA + 2; j += TP_EPG) {
                 const uint32_t g = ga + j;
                 const int p = TP_NB - 1 - (int)(g & (TP_NB - 1));
                 mbar_wait_guard(&accA_full[p], (g >> NB_SH) & 1);
@@ -822,7 +823,7 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             int b, y0, x0, nB;
             item_geom(item, b, y0, x0, nB);
-            for (int j = (int)((gb ^ (uint32_t)par) & 1); j < nB + 2; j += TP_EPG) {
+            for (int j = TP_EPG == 2 ? (int)((gb ^ (uint32_t)par) & 1) : 0; j < nB + 2; j += TP_EPG) {
                 const uint32_t g = gb + j;
                 const int p = TP_NB - 1 - (int)(g & (TP_NB - 1));
                 mbar_wait_guard(&accB_full[p], (g >> NB_SH) & 1);

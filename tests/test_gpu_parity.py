@@ -264,7 +264,8 @@ def test_dce_bf16_ragged_shapes_vs_oracle(cuda_dev, H, W, B, iters):
     assert O.psnr(out["enhanced"].cpu(), ref["enhanced"]) >= 50.0   # the contract (BASELINE.json north_star)
 
 
-@pytest.mark.parametrize("H,W,B", [(83, 256, 3), (120, 380, 1), (37, 252, 2), (3, 4, 1), (200, 1000, 1)])
+@pytest.mark.parametrize("H,W,B", [(83, 256, 3), (120, 380, 1), (37, 252, 2), (3, 4, 1), (200, 1000, 1),
+                                   (43, 1920, 12), (81, 636, 40)])  # > 148 items with odd row counts per item
 def test_dce_bf16_fused_launches_equal_per_layer_launches(cuda_dev, monkeypatch, H, W, B):
     # e_conv1 + e_conv2 and e_conv4 + e_conv5 as fused launches (126-pixel strips, rows handed over on chip) against
     # the seven per-layer launches: the same MMAs in the same order per pixel -> bit-identical
