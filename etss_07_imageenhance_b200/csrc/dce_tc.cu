@@ -100,6 +100,16 @@ __host__ __device__ constexpr int tc_layer_offset(int l, bool x3 = false) {
 }
 constexpr int TC_PACKED_BYTES = tc_layer_offset(7), TC_PACKED_BYTES_X3 = tc_layer_offset(7, true);
 
+// bias + ReLU + round-to-nearest bf16 of a channel pair (low half = first channel): one packed add and one conversion
+// with the ReLU built in -- the same values as fmaxf(v + b, 0) rounded by __floats2bfloat162_rn, in 2 instructions
+// instead of 5 (the epilogue warps of the fused kernels are instruction-bound)
+__device__ __forceinline__ uint32_t bias_relu_bf16x2(uint32_t v0, uint32_t v1, float b0, float b1) {
+    const float2 t = __fadd2_rn(make_float2(__uint_as_float(v0), __uint_as_float(v1)), make_float2(b0, b1));
+    uint32_t r;
+    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(t.y), "f"(t.x));
+    return r;
+}
+
 struct TcPackArgs {
     const float* w[7];
     const float* b[7];
@@ -313,11 +323,14 @@ dce_tc_layer_kernel(const TcArgs args, const __grid_constant__ TcMaps tm) {
                     uint32_t pk[16], pl[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        const float a0 = fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f);
-                        const float a1 = fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f);
-                        __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
-                        pk[i] = *reinterpret_cast<uint32_t*>(&h);
-                        if (X3) {  // lo = bf16(v - hi): the next layer multiplies (hi + lo)
+                        if constexpr (!X3) {
+                            pk[i] = bias_relu_bf16x2(v[2 * i], v[2 * i + 1], bias[2 * i], bias[2 * i + 1]);
+                        } else {
+                            const float a0 = fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f);
+                            const float a1 = fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f);
+                            __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
+                            pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                            // lo = bf16(v - hi): the next layer multiplies (hi + lo)
                             __nv_bfloat162 l2 = __floats2bfloat162_rn(a0 - __low2float(h), a1 - __high2float(h));
                             pl[i] = *reinterpret_cast<uint32_t*>(&l2);
                         }
@@ -651,9 +664,16 @@ constexpr int TP_NB = 8;            // accumulator blocks per layer
 constexpr int TP_WA = 3 * 2 * 3072, TP_WB = 3 * 4 * 3072;
 constexpr int TP_EPG = 1;            // epilogue groups of 4 warps per layer (2 = alternating rows: measured slower)
 constexpr int TP_THREADS = (8 * TP_EPG + 3) * 32;  // epilogue A, epilogue B, two MMA issuers, TMA producer
+#ifndef TP_NOUT_N
+#define TP_NOUT_N 4
+#endif
+constexpr int TP_NOUT = TP_NOUT_N;   // staging tiles of epilogue B: the tile written in row r was stored in row r - TP_NOUT; the
+                                     // issuing thread waits for the read of the store of row r - TP_NOUT + 1 before row r's
+                                     // barrier, so TP_NOUT - 2 stores stay in flight (with 2 tiles the group spent a third
+                                     // of its time waiting for the previous row's store to read its tile)
 constexpr int TP_BAR_BYTES = 1024;
 constexpr int TP_HEAD = TP_WA + TP_WB + 256 + TP_BAR_BYTES + 16;
-constexpr int TP_SMEM = TP_HEAD + 1024 + TP_EPG * TC_NOUT * TC_OUT_BYTES + (TP_NM + TP_NST) * TC_SRC_STRIDE;
+constexpr int TP_SMEM = TP_HEAD + 1024 + TP_EPG * TP_NOUT * TC_OUT_BYTES + (TP_NM + TP_NST) * TC_SRC_STRIDE;
 static_assert(TP_SMEM <= 227 * 1024, "shared memory budget");
 
 struct TpArgs {
@@ -686,7 +706,7 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + TP_WA + TP_WB + 256 + TP_BAR_BYTES);
     const uint32_t out_u32 = (smem_u32(smem_raw + TP_HEAD) + 1023u) & ~1023u;  // swizzle phase = address bits 7-8
     uint8_t* s_out = smem_raw + (out_u32 - smem_u32(smem_raw));
-    const uint32_t mid_u32 = out_u32 + TP_EPG * TC_NOUT * TC_OUT_BYTES;
+    const uint32_t mid_u32 = out_u32 + TP_EPG * TP_NOUT * TC_OUT_BYTES;
     uint8_t* s_mid = smem_raw + (mid_u32 - smem_u32(smem_raw));
     const uint32_t stage_u32 = mid_u32 + TP_NM * TC_SRC_STRIDE;
 
@@ -792,10 +812,7 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    const float a0 = ok ? fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f) : 0.f;
-                    const float a1 = ok ? fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f) : 0.f;
-                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
-                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                    pk[i] = ok ? bias_relu_bf16x2(v[2 * i], v[2 * i + 1], bias[2 * i], bias[2 * i + 1]) : 0u;
                 }
                 const uint32_t gm = gb + j;
                 const int ms = (int)(gm % TP_NM);
@@ -842,12 +859,9 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    const float a0 = fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f);
-                    const float a1 = fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f);
-                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
-                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                    pk[i] = bias_relu_bf16x2(v[2 * i], v[2 * i + 1], bias[2 * i], bias[2 * i + 1]);
                 }
-                const uint32_t ob = (uint32_t)(par * TC_NOUT + (int)obuf) * TC_OUT_BYTES;
+                const uint32_t ob = (uint32_t)(par * TP_NOUT + (int)obuf) * TC_OUT_BYTES;
                 uint8_t* op = s_out + ob + m * 64;
                 const int sw = (m >> 1) & 3;
                 *reinterpret_cast<uint4*>(op + ((0 ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
@@ -855,13 +869,13 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
                 *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
                 *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
                 fence_proxy_async_smem();
-                if (q == 0 && lane == 0) tma_store_wait_read<0>();  // the previous row's store (see the per-layer kernel)
+                if (q == 0 && lane == 0) tma_store_wait_read<TP_NOUT - 2>();  // the previous row's store (see the per-layer kernel)
                 named_bar_sync(1 + par, 128);
                 if (q == 0 && lane == 0) {  // the box is TP_VALID pixels: pixels 126 / 127 of the tile are not results
                     tma_store_4d(&tmo, out_u32 + ob, 0, x0, y0 + j, b);
                     tma_store_commit();
                 }
-                if (++obuf == TC_NOUT) obuf = 0;
+                if (++obuf == TP_NOUT) obuf = 0;
             }
             gb += nB + 2;
         }
@@ -1047,14 +1061,44 @@ dce_tc_pair_kernel(const TpArgs args, const __grid_constant__ CUtensorMap tma, c
 constexpr int TF_XPX = 132;                       // pixels per x row box
 constexpr int TF_XBYTES = 3 * TF_XPX * 4;         // bytes per x row box (3 planes)
 constexpr int TF_XROW = (TF_XBYTES + 127) / 128 * 128;  // x ring slot pitch (bulk tensor copies land 128-byte aligned)
-constexpr int TF_NX = 8, TF_NA = 8, TF_NM = 4, TF_NB = 8;  // x rows, A tiles, layer-A output rows, accumulator blocks
+#ifndef TF_STQ_N
+#define TF_STQ_N 3
+#endif
+#ifndef TF_NM_N
+#define TF_NM_N 8
+#endif
+constexpr int TF_STQ = TF_STQ_N;  // x1 row stores in flight (a slot stays taken until its store has read it)
+constexpr int TF_NX = 8, TF_NA = 8, TF_NM = TF_NM_N, TF_NB = 8;  // x rows, A tiles, layer-A output rows, accumulator blocks
+static_assert(TF_STQ < TF_NM, "epilogue A must be able to run ahead of the stores");
 constexpr int TF_WA = 3072, TF_WB = 3 * 2 * 3072;
-constexpr int TF_THREADS = 16 * 32;  // epilogue A (0-3), epilogue B (4-7), converters (8-11), issuers A / B, TMA, x1 store
+#ifndef TF_EPG_N
+#define TF_EPG_N 1
+#endif
+constexpr int TF_EPG = TF_EPG_N;  // epilogue groups of 4 warps per layer: the kernel is bound by its epilogues (7 MMAs per row)
+constexpr int TF_THREADS = (8 * TF_EPG + 9) * 32;  // epilogue A, epilogue B, 4 converters, issuers A / B, TMA, x1 store, x2 store
+#ifndef TF_NOUT_N
+#define TF_NOUT_N 4
+#endif
+constexpr int TF_NOUT = TF_NOUT_N;   // staging tiles per epilogue-B group, handed to the x2 store warp through mbarriers
+constexpr int TF_STQ2 = 2;           // x2 row stores in flight
+static_assert(TF_STQ2 < TF_NOUT, "epilogue B must be able to run ahead of the stores");
 constexpr int TF_BAR_BYTES = 1024;
 constexpr int TF_HEAD = TF_WA + TF_WB + 256 + TF_BAR_BYTES + 16;
 constexpr int TF_XRING = (TF_NX * TF_XROW + 1023) / 1024 * 1024;
-constexpr int TF_SMEM = TF_HEAD + 1024 + TC_NOUT * TC_OUT_BYTES + TF_NM * TC_SRC_STRIDE + TF_NA * TC_A1_BYTES + TF_XRING;
+constexpr int TF_SMEM = TF_HEAD + 1024 + TF_EPG * TF_NOUT * TC_OUT_BYTES + TF_NM * TC_SRC_STRIDE + TF_NA * TC_A1_BYTES + TF_XRING;
 static_assert(TF_SMEM <= 227 * 1024, "shared memory budget");
+
+// biases: in registers with one epilogue group per layer; with two (768 threads, 80 registers) read from shared memory
+// where they are used (warp-uniform addresses: broadcasts)
+#if TF_EPG_N == 1
+#define TF_BIAS_DECL(src)  \
+    float bias[32];        \
+    _Pragma("unroll") for (int i_ = 0; i_ < 32; ++i_) bias[i_] = (src)[i_];
+#define TF_BIAS(src, i) bias[i]
+#else
+#define TF_BIAS_DECL(src)
+#define TF_BIAS(src, i) (src)[i]
+#endif
 
 struct TfArgs {
     __nv_bfloat16* x1;      // e_conv1 output, NHWC bf16 [B,H,W,32] (strip 0 is written with plain stores)
@@ -1068,7 +1112,8 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                          const __grid_constant__ CUtensorMap tm2) {
     constexpr int NB_SH = 3;
     constexpr int TILE = 3072;
-    constexpr int W_EPB = 4, W_CONV = 8, W_MMA_A = 12, W_MMA_B = 13, W_TMA = 14;  // warp 15: x1 store
+    constexpr int W_EPB = 4 * TF_EPG, W_CONV = 8 * TF_EPG, W_MMA_A = W_CONV + 4, W_MMA_B = W_MMA_A + 1, W_TMA = W_MMA_A + 2;
+    // warp W_TMA + 1: x1 store, warp W_TMA + 2: x2 store
     extern __shared__ uint8_t smem_raw[];
     uint8_t* s_wA = smem_raw;
     uint8_t* s_wB = smem_raw + TF_WA;
@@ -1085,11 +1130,13 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
     uint64_t* accB_empty = accB_full + TF_NB;   // [NB] epilogue B (128)
     uint64_t* mid_full = accB_empty + TF_NB;    // [NM] epilogue A (128)
     uint64_t* mid_empty = mid_full + TF_NM;     // [NM] issuer B commit + the x1 store warp (2)
-    static_assert((2 * TF_NX + 2 * TF_NA + 4 * TF_NB + 2 * TF_NM) * 8 <= TF_BAR_BYTES, "mbarrier area");
+    uint64_t* out_full = mid_empty + TF_NM;     // [EPG * NOUT] epilogue B group (128)
+    uint64_t* out_empty = out_full + TF_EPG * TF_NOUT;  // [EPG * NOUT] the x2 store warp (1)
+    static_assert((2 * TF_NX + 2 * TF_NA + 4 * TF_NB + 2 * TF_NM + 2 * TF_EPG * TF_NOUT) * 8 <= TF_BAR_BYTES, "mbarrier area");
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + TF_WA + TF_WB + 256 + TF_BAR_BYTES);
     const uint32_t out_u32 = (smem_u32(smem_raw + TF_HEAD) + 1023u) & ~1023u;  // swizzle phase = address bits 7-8
     uint8_t* s_out = smem_raw + (out_u32 - smem_u32(smem_raw));
-    const uint32_t mid_u32 = out_u32 + TC_NOUT * TC_OUT_BYTES;
+    const uint32_t mid_u32 = out_u32 + TF_EPG * TF_NOUT * TC_OUT_BYTES;
     uint8_t* s_mid = smem_raw + (mid_u32 - smem_u32(smem_raw));
     const uint32_t at_u32 = mid_u32 + TF_NM * TC_SRC_STRIDE;  // A tiles (no swizzle, core matrices)
     uint8_t* s_at = smem_raw + (at_u32 - smem_u32(smem_raw));
@@ -1132,6 +1179,10 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 mbar_init(&mid_full[i], 128);
                 mbar_init(&mid_empty[i], 2);
             }
+            for (int i = 0; i < TF_EPG * TF_NOUT; ++i) {
+                mbar_init(&out_full[i], 128);
+                mbar_init(&out_empty[i], 1);
+            }
             mbar_fence_init();
         }
         __syncwarp();
@@ -1168,11 +1219,9 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
 
     if (warp < W_EPB) {
         // =========================== EPILOGUE A: accumulator ring A -> on-chip row slots ===========================
-        const int q = warp, m = q * 32 + lane;
+        const int q = warp & 3, par = warp >> 2, m = q * 32 + lane;
         const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
-        float bias[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) bias[i] = s_biasA[i];
+        TF_BIAS_DECL(s_biasA)
         uint32_t ga = 0, gb = 0;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             int b, y0, x0, nB;
@@ -1180,7 +1229,8 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
             const int nA = nB + 2;
             const int px = x0 - 1 + m;  // image column of this lane's pixel
             const bool px_ok = px >= 0 && px < W;
-            for (int j = 0; j < nA + 2; ++j) {
+            // TF_EPG == 2: this group's rows are those with g % 2 == par
+            for (int j = TF_EPG == 2 ? (int)((ga ^ (uint32_t)par) & 1) : 0; j < nA + 2; j += TF_EPG) {
                 const uint32_t g = ga + j;
                 const int p = TF_NB - 1 - (int)(g & (TF_NB - 1));
                 mbar_wait_guard(&accA_full[p], (g >> NB_SH) & 1);
@@ -1201,10 +1251,7 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    const float a0 = ok ? fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f) : 0.f;
-                    const float a1 = ok ? fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f) : 0.f;
-                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
-                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                    pk[i] = ok ? bias_relu_bf16x2(v[2 * i], v[2 * i + 1], TF_BIAS(s_biasA, 2 * i), TF_BIAS(s_biasA, 2 * i + 1)) : 0u;
                 }
                 const uint32_t gm = gb + j;
                 const int ms = (int)(gm % TF_NM);
@@ -1230,16 +1277,14 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
         }
     } else if (warp < W_CONV) {
         // =========================== EPILOGUE B: accumulator ring B -> x2 ===========================
-        const int q = warp & 3, m = q * 32 + lane;
+        const int q = warp & 3, par = (warp - W_EPB) >> 2, m = q * 32 + lane;
         const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16) + TF_NB * 32;
-        float bias[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) bias[i] = s_biasB[i];
-        uint32_t gb = 0, obuf = 0;
+        TF_BIAS_DECL(s_biasB)
+        uint32_t gb = 0, nuse = 0;  // nuse: rows this group has staged so far
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             int b, y0, x0, nB;
             item_geom(item, b, y0, x0, nB);
-            for (int j = 0; j < nB + 2; ++j) {
+            for (int j = TF_EPG == 2 ? (int)((gb ^ (uint32_t)par) & 1) : 0; j < nB + 2; j += TF_EPG) {
                 const uint32_t g = gb + j;
                 const int p = TF_NB - 1 - (int)(g & (TF_NB - 1));
                 mbar_wait_guard(&accB_full[p], (g >> NB_SH) & 1);
@@ -1258,26 +1303,21 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    const float a0 = fmaxf(__uint_as_float(v[2 * i]) + bias[2 * i], 0.f);
-                    const float a1 = fmaxf(__uint_as_float(v[2 * i + 1]) + bias[2 * i + 1], 0.f);
-                    __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
-                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                    pk[i] = bias_relu_bf16x2(v[2 * i], v[2 * i + 1], TF_BIAS(s_biasB, 2 * i), TF_BIAS(s_biasB, 2 * i + 1));
                 }
-                const uint32_t ob = obuf * TC_OUT_BYTES;
-                uint8_t* op = s_out + ob + m * 64;
+                // staging tile -> the x2 store warp (no CTA-level barrier, nobody in this group issues the store: with an
+                // elected thread doing it, the other three warps spent a third of their time waiting for that thread)
+                const uint32_t buf = (uint32_t)par * TF_NOUT + nuse % TF_NOUT;
+                if (nuse >= TF_NOUT) mbar_wait_guard(&out_empty[buf], ((nuse / TF_NOUT) - 1) & 1);
+                ++nuse;
+                uint8_t* op = s_out + buf * TC_OUT_BYTES + m * 64;
                 const int sw = (m >> 1) & 3;
                 *reinterpret_cast<uint4*>(op + ((0 ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 *reinterpret_cast<uint4*>(op + ((1 ^ sw) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
                 *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
                 fence_proxy_async_smem();
-                if (q == 0 && lane == 0) tma_store_wait_read<0>();  // the previous row's store (see the per-layer kernel)
-                named_bar_sync(1, 128);
-                if (q == 0 && lane == 0) {  // the box is TP_VALID pixels: pixels 126 / 127 of the tile are not results
-                    tma_store_4d(&tm2, out_u32 + ob, 0, x0, y0 + j, b);
-                    tma_store_commit();
-                }
-                if (++obuf == TC_NOUT) obuf = 0;
+                mbar_arrive(&out_full[buf]);
             }
             gb += nB + 2;
         }
@@ -1360,47 +1400,76 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
         }
     } else if (warp == W_MMA_B) {
         // =========================== MMA ISSUER B (e_conv1 rows on chip -> e_conv2) ===========================
+        // This one warp's instruction stream paces the kernel (it waits on barriers 17 % of its time), so the row loop
+        // is unrolled over the 8 positions of the slot / accumulator rings: slot, block, descriptor offsets and barrier
+        // addresses of position k = g % 8 are compile-time constants, the phase parity flips once per 8 rows.
+        static_assert(TF_NM == 8 && TF_NB == 8, "issuer B is unrolled over rings of 8");
         constexpr uint32_t IDESC0 = idesc_bf16_f32(TC_M, 0);
-        constexpr uint32_t IDESC_FULL = IDESC0 | ((uint32_t)(96 >> 3) << 17);
         const uint64_t bdesc0 = smem_desc_kmajor(smem_u32(s_wB), 128, 256);
         const uint64_t mdesc0 = smem_desc_sw64(mid_u32);
         const bool leader = elect_one();
-        uint32_t g = 0;
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int seg = (item / args.nstrip) % args.nseg;
-            const int nout = min(R, H - seg * R);  // layer-B output rows
-            const int nin = nout + 2;
-            for (int ri = 0; ri < nin; ++ri, ++g) {
-                const uint32_t ms = g % TF_NM;
-                const int pn = TF_NB - 1 - (int)(g & (TF_NB - 1));
-                mbar_wait_guard(&mid_full[ms], (g / TF_NM) & 1);
-                if (g >= TF_NB) mbar_wait_guard(&accB_empty[pn], ((g >> NB_SH) & 1) ^ 1);
+        int item = blockIdx.x;
+        bool live = item < n_items;
+        int nout = 0, ri = 0;  // layer-B output rows of the item (it has nout + 2 input rows); input row in the item
+        if (live) nout = min(R, H - ((item / args.nstrip) % args.nseg) * R);
+        uint32_t par = 0;      // (g >> 3) & 1
+        bool lap0 = true;      // g < 8: the accumulator blocks have not been used yet
+        // N = 32 * cnt output rows starting at tap row dy into blocks p0 .., from slot `ms`
+        // the (address >> 4) field is the low 14 bits of a descriptor and cannot carry (window < 256 KB)
+        const uint32_t m_lo = (uint32_t)mdesc0, m_hi = (uint32_t)(mdesc0 >> 32);
+        const uint32_t b_lo = (uint32_t)bdesc0, b_hi = (uint32_t)(bdesc0 >> 32);
+        auto taps = [&](int ms, int p0, int dy, int cnt) {
+            const uint32_t idesc = IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17);
+            const uint32_t d = tbase + (TF_NB + p0) * 32;
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx)
+#pragma unroll
+                for (int kc = 0; kc < 2; ++kc)
+                    mma_ss_lohi(d, m_lo + (uint32_t)((ms * TC_SRC_STRIDE + dx * 64 + kc * 32) >> 4), m_hi,
+                                b_lo + (uint32_t)((dy * 1024 + (dx * 2 + kc) * TILE) >> 4), b_hi, idesc);
+        };
+        while (live) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                if (!live) break;
+                constexpr int NBm = TF_NB - 1;
+                const int pn = NBm - k;  // block opened by this input row (dy = 0); compile-time after unrolling
+                mbar_wait_guard(&mid_full[k], par);
+                if (!lap0) mbar_wait_guard(&accB_empty[pn], par ^ 1);
                 tc_fence_after();
                 // layer-B pixel m = image column x0 + m reads slot row m + dx (slot row 0 = x0 - 1)
-                const uint64_t mdesc = mdesc0 + (uint64_t)((ms * TC_SRC_STRIDE) >> 4);
                 if (leader) {
-                    int dy = max(0, ri - (nout - 1));
-                    const int dy_hi = min(2, ri);
-                    while (dy <= dy_hi) {
-                        const int p0 = (pn + dy) & (TF_NB - 1);
-                        const int cnt = min(dy_hi - dy + 1, TF_NB - p0);
-                        const uint32_t idesc = cnt == 3 ? IDESC_FULL : (IDESC0 | ((uint32_t)(cnt * 32 >> 3) << 17));
-                        const uint32_t d = tbase + (TF_NB + p0) * 32;
-                        const uint64_t bd = bdesc0 + (uint64_t)((dy * 1024) >> 4);
-#pragma unroll
-                        for (int dx = 0; dx < 3; ++dx)
-#pragma unroll
-                            for (int kc = 0; kc < 2; ++kc)
-                                mma_ss(d, mdesc + (uint64_t)((dx * 64 + kc * 32) >> 4),
-                                       bd + (uint64_t)(((dx * 2 + kc) * TILE) >> 4), idesc, 1u);
-                        dy += cnt;
+                    if (ri >= 2 && ri < nout) {  // interior row: all three tap rows
+                        if (pn + 3 <= TF_NB) {
+                            taps(k, pn, 0, 3);
+                        } else {  // the ring wraps inside the three blocks
+                            taps(k, pn, 0, TF_NB - pn);
+                            taps(k, 0, TF_NB - pn, 3 - (TF_NB - pn));
+                        }
+                    } else {  // segment borders: output row ri - dy must lie in [0, nout)
+                        int dy = max(0, ri - (nout - 1));
+                        const int dy_hi = min(2, ri);
+                        while (dy <= dy_hi) {
+                            const int p0 = (pn + dy) & NBm;
+                            const int cnt = min(dy_hi - dy + 1, TF_NB - p0);
+                            taps(k, p0, dy, cnt);
+                            dy += cnt;
+                        }
                     }
-                    tc_commit(&mid_empty[ms]);
-                    if (ri >= 2) tc_commit(&accB_full[(pn + 2) & (TF_NB - 1)]);
-                    if (ri >= nout) tc_commit(&accB_full[pn]);
+                    tc_commit(&mid_empty[k]);
+                    if (ri >= 2) tc_commit(&accB_full[(pn + 2) & NBm]);
+                    if (ri >= nout) tc_commit(&accB_full[pn]);  // block unused this lap: complete its phase
                 }
                 __syncwarp();
+                if (++ri == nout + 2) {
+                    ri = 0;
+                    item += gridDim.x;
+                    live = item < n_items;
+                    if (live) nout = min(R, H - ((item / args.nstrip) % args.nseg) * R);
+                }
             }
+            par ^= 1;
+            lap0 = false;
         }
     } else if (warp == W_TMA) {
         // =========================== TMA PRODUCER (rows of x, fp32 planes) ===========================
@@ -1420,6 +1489,34 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 __syncwarp();
             }
         }
+    } else if (warp == W_TMA + 2) {
+        // =========================== x2 STORE (staging tiles of epilogue B -> HBM) ===========================
+        const bool leader = elect_one();
+        uint32_t gb = 0, n = 0;                 // running layer-B row counter (as in epilogue B); rows stored so far
+        uint32_t used[2] = {0, 0};              // rows staged per epilogue-B group
+        uint32_t hist[TF_STQ2 + 1];             // staging tiles of the newest stores
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            int b, y0, x0, nB;
+            item_geom(item, b, y0, x0, nB);
+            for (int j = 0; j < nB; ++j, ++n) {
+                const uint32_t par = TF_EPG == 2 ? ((gb + j) & 1) : 0;
+                const uint32_t u = used[par]++;
+                const uint32_t buf = par * TF_NOUT + u % TF_NOUT;
+                mbar_wait_guard(&out_full[buf], (u / TF_NOUT) & 1);
+                if (leader) {  // the box is TP_VALID pixels: pixels 126 / 127 of the tile are not results
+#ifndef TF_DBG_NO_X2
+                    tma_store_4d(&tm2, out_u32 + buf * TC_OUT_BYTES, 0, x0, y0 + j, b);
+#endif
+                    tma_store_commit();
+                    tma_store_wait_read<TF_STQ2>();
+                    if (n >= TF_STQ2) mbar_arrive(&out_empty[hist[(n - TF_STQ2) % (TF_STQ2 + 1)]]);
+                }
+                hist[n % (TF_STQ2 + 1)] = buf;
+                __syncwarp();
+            }
+            gb += nB + 2;
+        }
+        if (leader) tma_store_wait<0>();  // shared memory outlives the stores
     } else {
         // =========================== x1 STORE (slot rows the item owns -> HBM) ===========================
         const bool leader = elect_one();
@@ -1434,21 +1531,23 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 if (leader) {
                     // rows 0 / nA - 1 are the halo rows: the neighbouring segments own them; a bulk tensor STORE that starts
                     // at a negative coordinate is an illegal instruction (loads may): strip 0 is stored by epilogue A
-                    if (j >= 1 && j < nA - 1 && x0 > 0) {
+#ifndef TF_DBG_NO_X1
+                    if (j >= 1 && j < nA - 1 && x0 > 0)
                         tma_store_4d(&tm1, mid_u32 + ms * TC_SRC_STRIDE, 0, x0 - 1, y0 - 1 + j, b);
-                        tma_store_commit();
-                        tma_store_wait_read<0>();
-                    }
-                    mbar_arrive(&mid_empty[ms]);
+#endif
+                    // one bulk group per row (empty for the rows without a store): up to TF_STQ stores stay in flight,
+                    // row g - TF_STQ's slot is released when its store has read the slot
+                    tma_store_commit();
+                    tma_store_wait_read<TF_STQ>();
+                    if (g >= TF_STQ) mbar_arrive(&mid_empty[(g - TF_STQ) % TF_NM]);
                 }
                 __syncwarp();
             }
         }
-        if (leader) tma_store_wait<0>();  // shared memory outlives the stores
+        if (leader) tma_store_wait<0>();  // shared memory outlives the stores (the last slots are not needed again)
     }
 
     // ---- teardown ----
-    if (warp == W_EPB && lane == 0) tma_store_wait<0>();
     tc_fence_before();
     __syncthreads();
     if (warp == W_MMA_A) {
@@ -1633,6 +1732,7 @@ static int dce_tc_forward_t(const float* x, const void* packed, float* adjust, f
         if ((rc = tc_launch_first_pair(a, (__nv_bfloat16*)x1.hi, (__nv_bfloat16*)x2.hi, pk + tc_layer_offset(0),
                                        pk + tc_layer_offset(1), s)))
             return rc;
+        if (fe && fe[0] == 'o') return B200_OK;  // "only": timing aid, the forward stops behind this launch
     } else {
         layer(0, x1);
         if ((rc = tc_launch<1, true, false, X3>(a, none, none, x1, s))) return rc;

@@ -143,6 +143,21 @@ __device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_
         : "memory");
 }
 
+// Same with the descriptors as {low word, high word}: only the low word (start address field) differs between the taps
+// of a row, so a tap costs one 32-bit add of a compile-time constant per descriptor
+__device__ __forceinline__ void mma_ss_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                            uint32_t idesc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, 1, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, {%6, %6, %6, %6}, p;\n\t}"
+        :
+        : "r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(0u)
+        : "memory");
+}
+
 // Same, guarded by a per-thread predicate INSIDE the instruction stream: the call site stays in warp-uniform control
 // flow (no branch around the MMA), so descriptors and addresses can live in uniform registers.
 __device__ __forceinline__ void mma_ss_pred(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
