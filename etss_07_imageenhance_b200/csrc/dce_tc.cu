@@ -1125,12 +1125,12 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
     uint64_t* a_full = x_empty + TF_NX;         // [NA] the converter warp of the row (1)
     uint64_t* a_empty = a_full + TF_NA;         // [NA] issuer A commit
     uint64_t* accA_full = a_empty + TF_NA;      // [NB] issuer A commit
-    uint64_t* accA_empty = accA_full + TF_NB;   // [NB] epilogue A (128)
+    uint64_t* accA_empty = accA_full + TF_NB;   // [NB] epilogue A (one arrival per warp: 4)
     uint64_t* accB_full = accA_empty + TF_NB;   // [NB] issuer B commit
-    uint64_t* accB_empty = accB_full + TF_NB;   // [NB] epilogue B (128)
-    uint64_t* mid_full = accB_empty + TF_NB;    // [NM] epilogue A (128)
+    uint64_t* accB_empty = accB_full + TF_NB;   // [NB] epilogue B (4)
+    uint64_t* mid_full = accB_empty + TF_NB;    // [NM] epilogue A (4)
     uint64_t* mid_empty = mid_full + TF_NM;     // [NM] issuer B commit + the x1 store warp (2)
-    uint64_t* out_full = mid_empty + TF_NM;     // [EPG * NOUT] epilogue B group (128)
+    uint64_t* out_full = mid_empty + TF_NM;     // [EPG * NOUT] epilogue B group (4)
     uint64_t* out_empty = out_full + TF_EPG * TF_NOUT;  // [EPG * NOUT] the x2 store warp (1)
     static_assert((2 * TF_NX + 2 * TF_NA + 4 * TF_NB + 2 * TF_NM + 2 * TF_EPG * TF_NOUT) * 8 <= TF_BAR_BYTES, "mbarrier area");
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem_raw + TF_WA + TF_WB + 256 + TF_BAR_BYTES);
@@ -1171,16 +1171,16 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
             }
             for (int i = 0; i < TF_NB; ++i) {
                 mbar_init(&accA_full[i], 1);
-                mbar_init(&accA_empty[i], 128);
+                mbar_init(&accA_empty[i], 4);
                 mbar_init(&accB_full[i], 1);
-                mbar_init(&accB_empty[i], 128);
+                mbar_init(&accB_empty[i], 4);
             }
             for (int i = 0; i < TF_NM; ++i) {
-                mbar_init(&mid_full[i], 128);
+                mbar_init(&mid_full[i], 4);
                 mbar_init(&mid_empty[i], 2);
             }
             for (int i = 0; i < TF_EPG * TF_NOUT; ++i) {
-                mbar_init(&out_full[i], 128);
+                mbar_init(&out_full[i], 4);
                 mbar_init(&out_empty[i], 1);
             }
             mbar_fence_init();
@@ -1235,7 +1235,7 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 const int p = TF_NB - 1 - (int)(g & (TF_NB - 1));
                 mbar_wait_guard(&accA_full[p], (g >> NB_SH) & 1);
                 if (j >= nA) {
-                    mbar_arrive(&accA_empty[p]);
+                    warp_arrive(&accA_empty[p], lane);
                     continue;
                 }
                 tc_fence_after();
@@ -1245,7 +1245,7 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 tmem_zero32(tlane + p * 32);
                 tc_wait_st();
                 tc_fence_before();
-                mbar_arrive(&accA_empty[p]);
+                warp_arrive(&accA_empty[p], lane);
                 const int y = y0 - 1 + j;  // image row of this layer-A output row
                 const bool ok = px_ok && y >= 0 && y < H;
                 uint32_t pk[16];
@@ -1263,7 +1263,7 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
                 *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
                 fence_proxy_async_smem();  // read by issuer B's MMAs and the x1 store through the async proxy
-                mbar_arrive(&mid_full[ms]);
+                warp_arrive(&mid_full[ms], lane);
                 if (x0 == 0 && j >= 1 && j < nA - 1 && px_ok) {  // strip 0: slot row 0 is column -1, see the x1 store warp
                     uint4* gp = reinterpret_cast<uint4*>(args.x1 + (((size_t)b * H + y) * W + px) * 32);
                     gp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
@@ -1289,7 +1289,7 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 const int p = TF_NB - 1 - (int)(g & (TF_NB - 1));
                 mbar_wait_guard(&accB_full[p], (g >> NB_SH) & 1);
                 if (j >= nB) {
-                    mbar_arrive(&accB_empty[p]);
+                    warp_arrive(&accB_empty[p], lane);
                     continue;
                 }
                 tc_fence_after();
@@ -1299,7 +1299,7 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 tmem_zero32(tlane + p * 32);
                 tc_wait_st();
                 tc_fence_before();
-                mbar_arrive(&accB_empty[p]);
+                warp_arrive(&accB_empty[p], lane);
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
@@ -1317,7 +1317,7 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 *reinterpret_cast<uint4*>(op + ((2 ^ sw) << 4)) = make_uint4(pk[8], pk[9], pk[10], pk[11]);
                 *reinterpret_cast<uint4*>(op + ((3 ^ sw) << 4)) = make_uint4(pk[12], pk[13], pk[14], pk[15]);
                 fence_proxy_async_smem();
-                mbar_arrive(&out_full[buf]);
+                warp_arrive(&out_full[buf], lane);
             }
             gb += nB + 2;
         }
@@ -1504,9 +1504,7 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 const uint32_t buf = par * TF_NOUT + u % TF_NOUT;
                 mbar_wait_guard(&out_full[buf], (u / TF_NOUT) & 1);
                 if (leader) {  // the box is TP_VALID pixels: pixels 126 / 127 of the tile are not results
-#ifndef TF_DBG_NO_X2
                     tma_store_4d(&tm2, out_u32 + buf * TC_OUT_BYTES, 0, x0, y0 + j, b);
-#endif
                     tma_store_commit();
                     tma_store_wait_read<TF_STQ2>();
                     if (n >= TF_STQ2) mbar_arrive(&out_empty[hist[(n - TF_STQ2) % (TF_STQ2 + 1)]]);
@@ -1531,10 +1529,8 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
                 if (leader) {
                     // rows 0 / nA - 1 are the halo rows: the neighbouring segments own them; a bulk tensor STORE that starts
                     // at a negative coordinate is an illegal instruction (loads may): strip 0 is stored by epilogue A
-#ifndef TF_DBG_NO_X1
                     if (j >= 1 && j < nA - 1 && x0 > 0)
                         tma_store_4d(&tm1, mid_u32 + ms * TC_SRC_STRIDE, 0, x0 - 1, y0 - 1 + j, b);
-#endif
                     // one bulk group per row (empty for the rows without a store): up to TF_STQ stores stay in flight,
                     // row g - TF_STQ's slot is released when its store has read the slot
                     tma_store_commit();

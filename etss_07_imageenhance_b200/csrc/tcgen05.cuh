@@ -69,11 +69,25 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
         : "memory");
     return ok != 0;
 }
+// One arrival per WARP: every lane has done its part (its shared-memory writes + fence.proxy.async, or the warp-wide
+// tcgen05.wait + fence), __syncwarp orders them before lane 0's arrive (release).  128 single-thread arrivals on one
+// barrier are 128 serialised shared-memory atomics per row and barrier.
+__device__ __forceinline__ void warp_arrive(uint64_t* bar, int lane) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar);
+}
 __device__ __forceinline__ void mbar_wait_guard(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     uint32_t n = 0;
-    while (!mbar_try_wait_hint(bar, parity, 20000u)) {
+#ifndef B200_MBAR_HINT_NS
+#define B200_MBAR_HINT_NS 20000u
+#endif
+#if B200_MBAR_HINT_NS == 0
+    while (!mbar_try_wait(bar, parity)) {
+#else
+    while (!mbar_try_wait_hint(bar, parity, B200_MBAR_HINT_NS)) {
+#endif
 #ifdef B200_MBAR_DEBUG  // deadlock hunting: name the barrier and run on (the results are garbage, the launch ends)
         if ((++n & 63u) == 0 && clock64() - t0 > 100000000LL) {
             printf("mbar timeout: block %d warp %d barrier word %u parity %u\n", (int)blockIdx.x, (int)(threadIdx.x >> 5),
