@@ -1557,6 +1557,24 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
 // ------------------------------------------------------------------------------------------------
 static size_t tc_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// Rows per segment for a fused pair launch: an item (frame, segment, strip) costs R + 4 row steps for R output rows
+// (layer A is recomputed on the two halo rows of each side), the launch costs ceil(items / CTAs) items on its busiest
+// CTA: pick the number of segments per frame that minimises the product (the per-layer kernels keep 40 rows: their
+// recompute is 2 rows and they are HBM-bound).  Any R gives the same values.
+static int tc_pair_rows(int B, int H, int nstrip, int halo) {
+    long long best = -1;
+    int best_r = H < 40 ? H : 40;
+    for (int k = 1; k <= (H + 7) / 8; ++k) {
+        const int r = (H + k - 1) / k;
+        const int segs = (H + r - 1) / r;
+        const long long items = (long long)B * segs * nstrip;
+        const long long rounds = (items + B200_NUM_SMS - 1) / B200_NUM_SMS;
+        const long long cost = rounds * (r + halo);
+        if (best < 0 || cost < best) best = cost, best_r = r;
+    }
+    return best_r;
+}
+
 // NHWC bf16 [B,H,W,32] as a 4-D tensor (c, x, y, b); box = 32 channels x 130 pixels of one row; 64-byte swizzle;
 // coordinates outside the image (x = -1, x >= W, y = -1, y >= H) are zero-filled = the conv's zero padding.
 static int tc_make_map(CUtensorMap* m, const void* base, int B, int H, int W, int box_px = TC_SPX) {
@@ -1626,8 +1644,10 @@ static int tc_launch_pair(const TcArgs& a, const void* src, __nv_bfloat16* dst, 
     t.dst = dst;
     t.wpackA = wA;
     t.wpackB = wB;
-    t.B = a.B, t.H = a.H, t.W = a.W, t.R = a.R, t.nseg = a.nseg;
+    t.B = a.B, t.H = a.H, t.W = a.W;
     t.nstrip = (a.W + TP_VALID - 1) / TP_VALID;
+    t.R = tc_pair_rows(a.B, a.H, t.nstrip, 4);
+    t.nseg = (a.H + t.R - 1) / t.R;
     const long long items = (long long)t.B * t.nseg * t.nstrip;
     const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
     kern<<<grid, TP_THREADS, TP_SMEM, s>>>(t, mi, mo);
@@ -1665,8 +1685,10 @@ static int tc_launch_first_pair(const TcArgs& a, __nv_bfloat16* x1, __nv_bfloat1
     t.x1 = x1;
     t.wpackA = wA;
     t.wpackB = wB;
-    t.B = a.B, t.H = a.H, t.W = a.W, t.R = a.R, t.nseg = a.nseg;
+    t.B = a.B, t.H = a.H, t.W = a.W;
     t.nstrip = (a.W + TP_VALID - 1) / TP_VALID;
+    t.R = tc_pair_rows(a.B, a.H, t.nstrip, 4);
+    t.nseg = (a.H + t.R - 1) / t.R;
     const long long items = (long long)t.B * t.nseg * t.nstrip;
     const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
     kern<<<grid, TF_THREADS, TF_SMEM, s>>>(t, mx, m1, m2);
