@@ -1557,18 +1557,17 @@ dce_tc_first_pair_kernel(const TfArgs args, const __grid_constant__ CUtensorMap 
 // ------------------------------------------------------------------------------------------------
 static size_t tc_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// Rows per segment for a fused pair launch: an item (frame, segment, strip) costs R + 4 row steps for R output rows
-// (layer A is recomputed on the two halo rows of each side), the launch costs ceil(items / CTAs) items on its busiest
-// CTA: pick the number of segments per frame that minimises the product (the per-layer kernels keep 40 rows: their
-// recompute is 2 rows and they are HBM-bound).  Any R gives the same values.
-static int tc_pair_rows(int B, int H, int nstrip, int halo) {
+// Rows per segment: an item (frame, segment, strip) costs R + halo row steps for R output rows (the per-layer kernels
+// re-read 2 halo rows, the fused pairs recompute layer A on 2 more), a launch costs ceil(items / CTAs) items on its
+// busiest CTA: pick the number of segments per frame that minimises the product.  Any R gives the same values.
+static int tc_pick_rows(int B, int H, int nstrip, int halo, int ctas) {
     long long best = -1;
     int best_r = H < 40 ? H : 40;
     for (int k = 1; k <= (H + 7) / 8; ++k) {
         const int r = (H + k - 1) / k;
         const int segs = (H + r - 1) / r;
         const long long items = (long long)B * segs * nstrip;
-        const long long rounds = (items + B200_NUM_SMS - 1) / B200_NUM_SMS;
+        const long long rounds = (items + ctas - 1) / ctas;
         const long long cost = rounds * (r + halo);
         if (best < 0 || cost < best) best = cost, best_r = r;
     }
@@ -1646,7 +1645,7 @@ static int tc_launch_pair(const TcArgs& a, const void* src, __nv_bfloat16* dst, 
     t.wpackB = wB;
     t.B = a.B, t.H = a.H, t.W = a.W;
     t.nstrip = (a.W + TP_VALID - 1) / TP_VALID;
-    t.R = tc_pair_rows(a.B, a.H, t.nstrip, 4);
+    t.R = tc_pick_rows(a.B, a.H, t.nstrip, 4, B200_NUM_SMS);
     t.nseg = (a.H + t.R - 1) / t.R;
     const long long items = (long long)t.B * t.nseg * t.nstrip;
     const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
@@ -1687,7 +1686,7 @@ static int tc_launch_first_pair(const TcArgs& a, __nv_bfloat16* x1, __nv_bfloat1
     t.wpackB = wB;
     t.B = a.B, t.H = a.H, t.W = a.W;
     t.nstrip = (a.W + TP_VALID - 1) / TP_VALID;
-    t.R = tc_pair_rows(a.B, a.H, t.nstrip, 4);
+    t.R = tc_pick_rows(a.B, a.H, t.nstrip, 4, B200_NUM_SMS);
     t.nseg = (a.H + t.R - 1) / t.R;
     const long long items = (long long)t.B * t.nseg * t.nstrip;
     const int grid = (int)(items < B200_NUM_SMS ? items : B200_NUM_SMS);
@@ -1736,9 +1735,13 @@ static int dce_tc_forward_t(const float* x, const void* packed, float* adjust, f
     a.H = H;
     a.W = W;
     a.iters = iters;
-    a.R = H < 40 ? H : 40;
-    a.nseg = (H + a.R - 1) / a.R;
     a.nstrip = (W + TC_M - 1) / TC_M;
+    a.R = tc_pick_rows(B, H, a.nstrip, 2, B200_NUM_SMS * (X3 ? 1 : 2));  // X3: one CTA per SM in every layer
+    if (const char* re = getenv("B200DCE_DCE_ROWS")) {  // tuning / A-B aid: fixed rows per segment for the per-layer launches
+        const int r = atoi(re);
+        if (r > 0) a.R = r < H ? r : H;
+    }
+    a.nseg = (H + a.R - 1) / a.R;
     int rc;
     auto layer = [&](int l, TcPair dst) {
         a.dst = (__nv_bfloat16*)dst.hi;
