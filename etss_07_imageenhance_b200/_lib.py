@@ -57,6 +57,8 @@ _SIGNATURES = {
     "b200_dcev_packed_floats": (c_size_t, []),
     "b200_dcev_pack_weights": (c_int, [_PP, _PP, c_void_p, c_int, c_void_p]),
     "b200_dcev_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "b200_dcev_tail_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "b200_dcev_tail": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "b200_dcev_core": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                c_int, c_void_p, c_size_t, c_void_p]),
     "b200_sci_pack_weights_host": (c_int, [c_void_p] * 8 + [c_float, c_void_p, c_void_p, c_void_p]),

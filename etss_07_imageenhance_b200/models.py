@@ -309,11 +309,11 @@ class ZeroDCE_RE(_EnhancementModel):
 # --------------------------------------------------------------------------------------------- ZeroDCE-V (core)
 @MODELS.register(name="zero_dce_v", arch="zero_dce")
 class ZeroDCEV(_EnhancementModel):
-    """ZeroDCE-V (zero_dce_v.py:92-218), PARTIAL: constructor, attribute names and state_dict layout of
-    the reference class, and `forward_core` = its forward up to `image_v_fixed_lr` (:172-193: V channel, nearest resize
-    to `down_size`, DCE-Net with in_channels=1, `num_iters` curve steps on V) on the fp32 kernels.  The rest of the
-    reference forward -- `FastGuidedFilter` upsample (:194), HSV recomposition through kornia and the division by the
-    global maximum (:195-197) -- is not built; `forward` says so instead of returning something else."""
+    """ZeroDCE-V (zero_dce_v.py:92-230): constructor, attribute names and state_dict layout of the
+    reference class.  `forward_core` = its forward up to `image_v_fixed_lr` (:172-193: V channel, nearest resize to
+    `down_size`, DCE-Net with in_channels=1, `num_iters` curve steps on V) on the fp32 kernels; `forward` adds the
+    `FastGuidedFilter` upsample (:194), the HSV recomposition (kornia's formulas) and the division by the frame maximum
+    (:195-197) and returns the reference's six outputs."""
 
     arch = "zero_dce"
     schemes: list = ["unsupervised", "zero_reference", "instance"]
@@ -365,11 +365,18 @@ class ZeroDCEV(_EnhancementModel):
                                                              self.num_iters)
         return {"image_v": v, "image_v_lr": v_lr, "adjust": adjust, "image_v_fixed_lr": fixed}
 
+    @torch.no_grad()
     def forward(self, datapoint: dict, *args, **kwargs) -> dict:
-        raise NotImplementedError(
-            "ZeroDCEV: only the core of the forward is built on the B200 path (forward_core: image_v, image_v_lr, "
-            "adjust, image_v_fixed_lr); the guided-filter upsample and the HSV recomposition of zero_dce_v.py:194-197 "
-            "are not")
+        """All six entries of the reference's output dict (zero_dce_v.py:198-205), same keys and order.  The reference
+        only runs with batch 1 (`replace_v_component`, :221-230); a batch here is a loop of batch-1 calls, i.e. `enhanced`
+        is divided by each frame's own maximum.  `enhanced` goes through kornia's HSV conversions, restated from their
+        published form (kornia is not installed where this was built: that output is not pinned to the reference)."""
+        out = self.forward_core(datapoint)
+        x = self._image(datapoint)
+        v_fixed, enhanced = torch.ops.b200dce.dcev_tail(x, out["image_v"], out["image_v_lr"], out["image_v_fixed_lr"])
+        out["image_v_fixed"] = v_fixed
+        out["enhanced"] = enhanced
+        return out
 
 
 # --------------------------------------------------------------------------------------------- Zero-DCE++

@@ -24,7 +24,7 @@ from ._lib import PRECISIONS, check, lib, ptr_array
 
 __all__ = [
     "curve_shared", "curve_per_iter", "gce_curve", "dcepp_pack", "dcepp_forward", "dcepp_lowres", "dcepp_apply",
-    "dce_pack", "dce_forward", "dcev_pack", "dcev_core", "sci_pack", "sci_forward", "ruas_pack", "ruas_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
+    "dce_pack", "dce_forward", "dcev_pack", "dcev_core", "dcev_tail", "sci_pack", "sci_forward", "ruas_pack", "ruas_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
     "current_stream_ptr", "require_device",
 ]
 
@@ -362,6 +362,36 @@ def _(image, packed, down_size, iters):
     S = int(down_size)
     return (image.new_empty(B, 1, H, W), image.new_empty(B, 1, S, S), image.new_empty(B, iters, S, S),
             image.new_empty(B, 1, S, S))
+
+
+@torch.library.custom_op("b200dce::dcev_tail", mutates_args=(), device_types="cuda")
+def dcev_tail(image: Tensor, image_v: Tensor, image_v_lr: Tensor, image_v_fixed_lr: Tensor) -> Tuple[Tensor, Tensor]:
+    """(image_v_fixed [B,1,H,W], enhanced [B,3,H,W]): the tail of ZeroDCEV.forward (zero_dce_v.py:193-197):
+    FastGuidedFilter(radius=1) upsample of the corrected low-resolution V (guided_filter.py:171-203), clip, V replaced
+    in kornia's HSV, back to RGB, division by the frame's maximum (each frame = one batch-1 call of the reference)."""
+    image = _img(image, "image")
+    image_v, image_v_lr, image_v_fixed_lr = (_img(t, n, 1) for t, n in ((image_v, "image_v"), (image_v_lr, "image_v_lr"),
+                                                                        (image_v_fixed_lr, "image_v_fixed_lr")))
+    B, _, H, W = image.shape
+    S = image_v_lr.shape[-1]
+    if tuple(image_v.shape) != (B, 1, H, W) or tuple(image_v_lr.shape) != (B, 1, S, S) or image_v_fixed_lr.shape != image_v_lr.shape:
+        raise ValueError("b200dce::dcev_tail: shapes must be [B,3,H,W], [B,1,H,W], [B,1,S,S], [B,1,S,S]")
+    v_fixed = torch.empty_like(image_v)
+    enhanced = torch.empty_like(image)
+    if B:
+        L = lib()
+        ws_bytes = L.b200_dcev_tail_workspace_bytes(B, S)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=image.device)
+        with torch.cuda.device(image.device):
+            check(L.b200_dcev_tail(image.data_ptr(), image_v.data_ptr(), image_v_lr.data_ptr(), image_v_fixed_lr.data_ptr(),
+                                   v_fixed.data_ptr(), enhanced.data_ptr(), B, H, W, S, ws.data_ptr(), ws_bytes,
+                                   current_stream_ptr()), "b200_dcev_tail")
+    return v_fixed, enhanced
+
+
+@dcev_tail.register_fake
+def _(image, image_v, image_v_lr, image_v_fixed_lr):
+    return torch.empty_like(image_v), torch.empty_like(image)
 
 
 # ----------------------------------------------------------------------------- SCI

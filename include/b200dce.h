@@ -228,6 +228,19 @@ int b200_dcev_core(const float* image_rgb, const float* packed, float* image_v, 
                    float* image_v_fixed_lr, int B, int H, int W, int S, int iters, void* workspace,
                    size_t workspace_bytes, void* stream);
 
+/* Tail of ZeroDCEV.forward: image_v_fixed [B,1,H,W] = clip(FastGuidedFilter(radius 1, eps 1e-8)(image_v_lr,
+ * image_v_fixed_lr, image_v), 0, 1) and enhanced [B,3,H,W] = hsv_to_rgb(H, S of image_rgb, V = image_v_fixed) divided
+ * by the frame's maximum.  Replaces src/mon/vision/enhance/llie/zero_dce/zero_dce_v.py:193-197,208-230,
+ * src/mon/vision/filtering/guided_filter.py:171-203 and box_filter.py:26-117 (cumulative-sum box filter: the window
+ * sums are differences of fp32-rounded prefixes accumulated in double, repeated here exactly -- A = cov / (var + eps) is
+ * ill-conditioned in flat windows), bicubic align_corners=True resize of A and b as ATen does it; the HSV conversions
+ * are kornia's (src/mon/core/image/color.py:169-190,262-277 delegate to it) restated from their published form.
+ * The reference runs with batch 1 only: a batch is B batch-1 calls (per-frame maximum).  S > 3. */
+size_t b200_dcev_tail_workspace_bytes(int B, int S);
+int b200_dcev_tail(const float* image_rgb, const float* image_v, const float* image_v_lr, const float* image_v_fixed_lr,
+                   float* image_v_fixed, float* enhanced, int B, int H, int W, int S, void* workspace,
+                   size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * "next" rows: u8 HWC <-> fp32 NCHW frame conversion.
  * Replaces src/mon/core/image/utils.py:801-848 (to_image_tensor(normalize=True)

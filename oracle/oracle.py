@@ -263,6 +263,96 @@ def zero_dce_v_core(x: torch.Tensor, sd: dict, down_size: int = 256, num_iters: 
     return {"image_v": image_v, "image_v_lr": image_v_lr, "adjust": x_r, "image_v_fixed_lr": y}
 
 
+# ----------------------------------------------------------------------------- guided filter / HSV (ZeroDCE-V tail)
+def _gf_diff(t: torch.Tensor, r: int, dim: int) -> torch.Tensor:
+    """diff_x (dim=2) / diff_y (dim=3) of src/mon/vision/filtering/box_filter.py:26-66: window sums from a cumulative sum."""
+    n = t.shape[dim]
+    sl = lambda a, b: t.narrow(dim, a, b - a)  # noqa: E731
+    left = sl(r, 2 * r + 1)
+    middle = sl(2 * r + 1, n) - sl(0, n - 2 * r - 1)
+    right = sl(n - 1, n) - sl(n - 2 * r - 1, n - r - 1)
+    return torch.cat([left, middle, right], dim=dim)
+
+
+def box_filter_cumsum(t: torch.Tensor, r: int) -> torch.Tensor:
+    """box_filter, tensor branch (box_filter.py:69-117): diff_y(diff_x(t.cumsum(2), r).cumsum(3), r).  On the CPU ATen's
+    cumsum accumulates fp32 inputs in double and rounds every prefix to fp32."""
+    return _gf_diff(_gf_diff(t.cumsum(dim=2), r, 2).cumsum(dim=3), r, 3)
+
+
+@torch.no_grad()
+def fast_guided_filter(x_lr: torch.Tensor, y_lr: torch.Tensor, x_hr: torch.Tensor, radius: int = 1,
+                       eps: float = 1e-8, return_coeffs: bool = False):
+    """FastGuidedFilter.forward(x_lr, y_lr, x_hr), src/mon/vision/filtering/guided_filter.py:171-203: the linear model
+    y = A x + b fitted in (2r+1)^2 windows at low resolution, A and b resized bicubically (align_corners=True) to the
+    full resolution and applied to the full-resolution guide."""
+    h, w = x_lr.shape[-2:]
+    n = box_filter_cumsum(x_lr.new_ones(1, 1, h, w), radius)
+    mean_x = box_filter_cumsum(x_lr, radius) / n
+    mean_y = box_filter_cumsum(y_lr, radius) / n
+    cov_xy = box_filter_cumsum(x_lr * y_lr, radius) / n - mean_x * mean_y
+    var_x = box_filter_cumsum(x_lr * x_lr, radius) / n - mean_x * mean_x
+    a = cov_xy / (var_x + eps)
+    b = mean_y - a * mean_x
+    if return_coeffs:
+        return a, b
+    mean_a = F.interpolate(a, x_hr.shape[-2:], mode="bicubic", align_corners=True)
+    mean_b = F.interpolate(b, x_hr.shape[-2:], mode="bicubic", align_corners=True)
+    return mean_a * x_hr + mean_b
+
+
+def rgb_to_hsv_kornia(image: torch.Tensor, eps: float = 1e-8) -> torch.Tensor:
+    """kornia.color.rgb_to_hsv as published (kornia is a dependency of the reference, unpinned in env/*.yaml and absent
+    here: PARITY UNPINNED for this function).  H in [0, 2 pi], S = delta / (max + eps), V = max."""
+    max_rgb, argmax_rgb = image.max(-3)
+    min_rgb = image.min(-3)[0]
+    deltac = max_rgb - min_rgb
+    v = max_rgb
+    s = deltac / (max_rgb + eps)
+    deltac = torch.where(deltac == 0, torch.ones_like(deltac), deltac)
+    rc, gc, bc = torch.unbind(max_rgb.unsqueeze(-3) - image, dim=-3)
+    h1 = bc - gc
+    h2 = (rc - bc) + 2.0 * deltac
+    h3 = (gc - rc) + 4.0 * deltac
+    h = torch.stack((h1, h2, h3), dim=-3) / deltac.unsqueeze(-3)
+    h = torch.gather(h, dim=-3, index=argmax_rgb.unsqueeze(-3)).squeeze(-3)
+    h = (h / 6.0) % 1.0
+    h = 2.0 * math.pi * h
+    return torch.stack((h, s, v), dim=-3)
+
+
+def hsv_to_rgb_kornia(image: torch.Tensor) -> torch.Tensor:
+    """kornia.color.hsv_to_rgb as published (PARITY UNPINNED, see rgb_to_hsv_kornia)."""
+    h = image[..., 0, :, :] / (2 * math.pi)
+    s = image[..., 1, :, :]
+    v = image[..., 2, :, :]
+    hi = torch.floor(h * 6) % 6
+    f = ((h * 6) % 6) - hi
+    one = torch.tensor(1.0)
+    p = v * (one - s)
+    q = v * (one - f * s)
+    t = v * (one - (one - f) * s)
+    hi = hi.long()
+    indices = torch.stack([hi, hi + 6, hi + 12], dim=-3)
+    out = torch.stack((v, q, p, p, t, v, t, v, v, q, p, p, p, p, t, v, v, q), dim=-3)
+    return torch.gather(out, -3, indices)
+
+
+@torch.no_grad()
+def zero_dce_v_forward(x: torch.Tensor, sd: dict, down_size: int = 256, num_iters: int = 15) -> dict:
+    """ZeroDCEV.forward, zero_dce_v.py:172-203, all six outputs.  The reference runs with batch 1 only
+    (`replace_v_component`, :221-230); a batch is treated here as a loop of batch-1 calls, so the final division is by
+    each frame's own maximum.  `image_v_fixed` is pinned against the reference's FastGuidedFilter; `enhanced` goes
+    through the kornia HSV restatements above and is unpinned."""
+    core = zero_dce_v_core(x, sd, down_size, num_iters)
+    v_fixed = torch.clip(fast_guided_filter(core["image_v_lr"], core["image_v_fixed_lr"], core["image_v"], radius=1), 0, 1)
+    hsv = rgb_to_hsv_kornia(x)
+    hsv = torch.cat([hsv[:, :2], v_fixed], dim=1)
+    rgb = hsv_to_rgb_kornia(hsv)
+    rgb = rgb / rgb.amax(dim=(1, 2, 3), keepdim=True)
+    return {**core, "image_v_fixed": v_fixed, "enhanced": rgb}
+
+
 @torch.no_grad()
 def zero_dce_forward_bf16_operands(x: torch.Tensor, sd: dict, num_iters: int = 8) -> dict:
     """`zero_dce_forward` with the OPERAND rounding of the tensor-core mode: every conv input and every

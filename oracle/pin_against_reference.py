@@ -261,6 +261,47 @@ def load_reference_gce_loop(iutils):
     return ns["loop"], prior.BrightnessAttentionMap
 
 
+def load_reference_guided_filter():
+    """src/mon/vision/filtering/{box_filter,guided_filter}.py, unmodified, under the stub `mon`.  Stand-ins for what is
+    not installed here and not on the path being pinned: `plum.dispatch` (overloads told apart by their number of
+    positional arguments -- FastGuidedFilter.forward has a 3- and a 2-tensor form), `cv2.ximgproc` (numpy branch only),
+    `mon.nn.functional` / `mon.nn.init` = torch's."""
+    import cv2
+    if not hasattr(cv2, "ximgproc"):
+        cv2.ximgproc = types.ModuleType("cv2.ximgproc")
+        sys.modules["cv2.ximgproc"] = cv2.ximgproc
+    if "plum" not in sys.modules:
+        plum = types.ModuleType("plum")
+        registry = {}
+
+        def dispatch(fn):
+            import inspect
+            n = len([p_ for p_ in inspect.signature(fn).parameters.values() if p_.name != "self"])
+            registry.setdefault(fn.__qualname__, {})[n] = fn
+
+            def call(self, *args):
+                return registry[fn.__qualname__][len(args)](self, *args)
+            return call
+        plum.dispatch = dispatch
+        sys.modules["plum"] = plum
+    nn = sys.modules["mon.nn"]
+    nn.functional = torch.nn.functional
+    nn.init = torch.nn.init
+    if not hasattr(nn, "AdaptiveBatchNorm2d"):  # a default argument of DeepGuidedFilter (not on the pinned path)
+        nn.AdaptiveBatchNorm2d = torch.nn.BatchNorm2d
+    sys.modules["mon.nn.functional"] = torch.nn.functional
+    sys.modules["mon.nn.init"] = torch.nn.init
+    vision = sys.modules["mon.vision"]
+    filtering = types.ModuleType("mon.vision.filtering")
+    vision.filtering = filtering
+    sys.modules["mon.vision.filtering"] = filtering
+    d = REF / "src/mon/vision/filtering"
+    box = _load_file("mon.vision.filtering.box_filter", d / "box_filter.py")
+    filtering.box_filter = box
+    gf = _load_file("mon.vision.filtering.guided_filter", d / "guided_filter.py")
+    return gf, box
+
+
 def to_upstream_keys(sd: dict) -> dict:
     return {k.replace("dw_conv", "depth_conv").replace("pw_conv", "point_conv"): v for k, v in sd.items()}
 
@@ -484,6 +525,31 @@ def main():
     np.savez_compressed(GOLD / "gce_curve.npz", **arrs)
     report.append("gce curve loop: oracle == the reference's own statements (gcenet.py:469-484 cut out by AST, "
                   "prior/image.py BrightnessAttentionMap with kornia's V = channel maximum) for gamma 2.5 / 1.0 / 0.0")
+
+    # ---------------- FastGuidedFilter of the ZeroDCE-V tail ----------------
+    gfmod, boxmod = load_reference_guided_filter()
+    ZV = load_reference_zero_dce_v.__globals__["sys"].modules["ref_zero_dce_v"].ZeroDCEV
+    garrs = {}
+    for regime in ("init", "stress"):
+        x = O.synthetic_lowlight(2, 70, 90, seed=601)
+        sd = O.make_dce_state_dict(19, regime, num_iters=15, in_channels=1)
+        core_out = O.zero_dce_v_core(x, sd, down_size=48, num_iters=15)
+        with torch.no_grad():
+            # the reference's own static method (zero_dce_v.py:208-219) on top of its own FastGuidedFilter; the stubbed
+            # `filtering` the class saw at import time is replaced by the real module for this call
+            sys.modules["ref_zero_dce_v"].filtering = types.SimpleNamespace(FastGuidedFilter=gfmod.FastGuidedFilter)
+            ref_v = ZV.filter_up(core_out["image_v_lr"], core_out["image_v_fixed_lr"], core_out["image_v"])
+            ref_box = boxmod.BoxFilter(radius=1)(core_out["image_v_lr"])
+        got = O.zero_dce_v_forward(x, sd, down_size=48, num_iters=15)
+        eq(O.box_filter_cumsum(core_out["image_v_lr"], 1), ref_box, f"gf/{regime}/box")
+        eq(got["image_v_fixed"], ref_v, f"gf/{regime}/image_v_fixed")
+        a_, b_ = O.fast_guided_filter(core_out["image_v_lr"], core_out["image_v_fixed_lr"], core_out["image_v"], return_coeffs=True)
+        garrs[f"{regime}:image_v_fixed"] = ref_v.numpy()
+        garrs[f"{regime}:enhanced_unpinned"] = got["enhanced"].numpy()
+        garrs[f"{regime}:A"], garrs[f"{regime}:b"] = a_.numpy(), b_.numpy()
+    np.savez_compressed(GOLD / "dcev_tail.npz", **garrs)
+    report.append("dcev tail: oracle == the reference's ZeroDCEV.filter_up on its own FastGuidedFilter / BoxFilter (bit-exact); "
+                  "`enhanced` (kornia HSV, absent here) is the oracle's restatement: UNPINNED")
 
     (GOLD / "PIN_REPORT.txt").write_text(
         f"generated by oracle/pin_against_reference.py with torch {torch.__version__} (CPU, fp32)\n" +

@@ -732,3 +732,39 @@ def test_gce_curve_shapes_vs_oracle(cuda_dev, B, H, W):
     assert bam.shape == (B, 1, H, W)
     for got, k in ((enh, "enhanced"), (bam, "bam"), (bright, "bright"), (dark, "dark")):
         assert maxerr(got, ref[k]) <= GCE_TOL, k
+
+
+# ------------------------------------------------------------------ ZeroDCE-V tail: guided filter + HSV
+def _gf_close(got, ref, what):
+    """A = cov / (var + 1e-8) amplifies rounding where a 3x3 window is flat: one ulp in the low-resolution pair moves
+    isolated full-resolution pixels by ~1e-3 (CPU study in DESIGN.md).  The low-resolution stage repeats the reference's
+    rounding sequence, the bicubic resize may differ from ATen in the last bits: contract tolerance on every pixel, a
+    tight one on all but a handful."""
+    d = (got.detach().cpu().double() - ref.double()).abs()
+    assert d.max().item() <= TOL, (what, d.max().item())
+    assert (d > TIGHT).double().mean().item() <= 1e-4, (what, (d > TIGHT).double().mean().item())
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_zero_dce_v_forward_golden(cuda_dev, golden, regime):
+    """All six outputs of ZeroDCEV.forward; image_v_fixed against the reference's own FastGuidedFilter output."""
+    x, sd, outs = golden(f"dcev_{regime}")
+    z = np.load(GOLDEN_DIR / "dcev_tail.npz")
+    m = load_into(P.MODELS.build(config={"name": "zero_dce_v", "down_size": 48}), sd).to(cuda_dev)
+    out = m({"image": x.to(cuda_dev)})
+    assert list(out.keys()) == ["image_v", "image_v_lr", "adjust", "image_v_fixed_lr", "image_v_fixed", "enhanced"]
+    _gf_close(out["image_v_fixed"], torch.from_numpy(z[f"{regime}:image_v_fixed"]), "image_v_fixed")
+    _gf_close(out["enhanced"], torch.from_numpy(z[f"{regime}:enhanced_unpinned"]), "enhanced")
+
+
+@pytest.mark.parametrize("B,H,W,S", [(1, 37, 45, 16), (3, 64, 64, 64), (2, 30, 50, 96), (1, 1080, 1920, 256), (1, 5, 7, 4)])
+def test_zero_dce_v_tail_vs_oracle(cuda_dev, B, H, W, S):
+    """The tail alone, fed with the ORACLE's core outputs (isolates the guided filter from the DCE-Net's 1e-5)."""
+    x = O.synthetic_lowlight(B, H, W, seed=190 + S)
+    sd = O.make_dce_state_dict(29, "stress", num_iters=15, in_channels=1)
+    ref = O.zero_dce_v_forward(x, sd, down_size=S, num_iters=15)
+    v_fixed, enh = torch.ops.b200dce.dcev_tail(x.to(cuda_dev), ref["image_v"].to(cuda_dev), ref["image_v_lr"].to(cuda_dev),
+                                               ref["image_v_fixed_lr"].to(cuda_dev))
+    _gf_close(v_fixed, ref["image_v_fixed"], "image_v_fixed")
+    _gf_close(enh, ref["enhanced"], "enhanced")
+    assert enh.amax(dim=(1, 2, 3)).eq(1.0).all()   # divided by the frame's own maximum

@@ -204,8 +204,7 @@ def test_zero_dcepp_state_dict_layout_init_and_file_weights(tmp_path):
 
 
 def test_zero_dce_v_constructor_and_state_dict_layout():
-    """the reference class's registry entry, defaults, attribute names and keys
-    (zero_dce_v.py:87-140); only the core of its forward is built."""
+    """the reference class's registry entry, defaults, attribute names and keys (zero_dce_v.py:87-140)."""
     m = P.MODELS.build(name="zero_dce_v")
     assert isinstance(m, P.ZeroDCEV) and P.MODELS["zero_dce"]["zero_dce_v"] is P.ZeroDCEV
     assert (m.in_channels, m.num_channels, m.num_iters, m.out_channels, m.down_size) == (1, 32, 15, 15, 256)
@@ -213,10 +212,9 @@ def test_zero_dce_v_constructor_and_state_dict_layout():
     assert m.e_conv1.weight.shape == (32, 1, 3, 3) and m.e_conv7.weight.shape == (15, 64, 3, 3)
     m2 = P.ZeroDCEV(weights={"state_dict": m.state_dict(), "num_iters": 15, "down_size": 128})
     assert m2.down_size == 128 and torch.equal(m2.e_conv3.weight, m.e_conv3.weight)
-    with pytest.raises(NotImplementedError, match="forward_core"):
-        m({"image": torch.rand(1, 3, 8, 8)})
-    with pytest.raises(RuntimeError, match="no CPU fallback"):
-        m.forward_core({"image": torch.rand(1, 3, 8, 8)})
+    for call in (m, m.forward_core):  # no CPU fallback for either
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            call({"image": torch.rand(1, 3, 8, 8)})
 
 
 def test_numa_helpers(tmp_path):

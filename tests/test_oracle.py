@@ -144,3 +144,17 @@ def test_oracle_gce_curve_loop_matches_reference_golden():
                 assert torch.equal(got[k], torch.from_numpy(z[f"{tag}:{k}"])), k
             else:
                 assert got[k] is None
+
+
+@pytest.mark.parametrize("regime", ["init", "stress"])
+def test_oracle_zero_dce_v_tail_matches_reference_golden(golden, regime):
+    """tests/golden/dcev_tail.npz: `image_v_fixed` = the reference's ZeroDCEV.filter_up on its own FastGuidedFilter /
+    BoxFilter (bit-exact pin); `enhanced` is the oracle's own kornia-HSV restatement (unpinned: regression value)."""
+    x, sd, _ = golden(f"dcev_{regime}")
+    z = np.load(GOLDEN_DIR / "dcev_tail.npz")
+    got = O.zero_dce_v_forward(x, sd, down_size=48, num_iters=15)
+    assert list(got.keys()) == ["image_v", "image_v_lr", "adjust", "image_v_fixed_lr", "image_v_fixed", "enhanced"]
+    assert torch.equal(got["image_v_fixed"], torch.from_numpy(z[f"{regime}:image_v_fixed"]))
+    assert torch.equal(got["enhanced"], torch.from_numpy(z[f"{regime}:enhanced_unpinned"]))
+    # the conversions are each other's inverse up to rounding
+    assert (O.hsv_to_rgb_kornia(O.rgb_to_hsv_kornia(x)) - x).abs().max() <= 1e-6
