@@ -33,6 +33,9 @@ _SIGNATURES = {
     "b200_strerror": (c_char_p, [c_int]),
     "b200_check_device": (c_int, []),
     "b200_curve_shared": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_guided_filter_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200_guided_filter": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_float,
+                                   c_void_p, c_size_t, c_void_p]),
     "b200_gce_curve": (c_int, [c_void_p] * 6 + [c_int, c_int, c_int, c_int, c_float, c_void_p]),
     "b200_curve_per_iter": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_dcepp_packed_floats": (c_size_t, []),

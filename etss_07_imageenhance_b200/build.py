@@ -15,7 +15,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIBDIR = PKG / "lib"
 LIB = LIBDIR / "libb200dce.so"
-SOURCES = ["abi.cu", "curve.cu", "dcepp.cu", "sci.cu", "ruas.cu", "dce.cu", "dce_tc.cu", "dce_x3.cu", "dcev_tail.cu"]
+SOURCES = ["abi.cu", "curve.cu", "dcepp.cu", "sci.cu", "ruas.cu", "dce.cu", "dce_tc.cu", "dce_x3.cu", "dcev_tail.cu", "guided_filter.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

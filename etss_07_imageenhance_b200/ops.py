@@ -23,7 +23,7 @@ from . import _lib
 from ._lib import PRECISIONS, check, lib, ptr_array
 
 __all__ = [
-    "curve_shared", "curve_per_iter", "gce_curve", "dcepp_pack", "dcepp_forward", "dcepp_lowres", "dcepp_apply",
+    "curve_shared", "curve_per_iter", "gce_curve", "guided_filter", "dcepp_pack", "dcepp_forward", "dcepp_lowres", "dcepp_apply",
     "dce_pack", "dce_forward", "dcev_pack", "dcev_core", "dcev_tail", "sci_pack", "sci_forward", "ruas_pack", "ruas_forward", "u8hwc_to_f32nchw", "f32nchw_to_u8hwc", "resize_bilinear",
     "current_stream_ptr", "require_device",
 ]
@@ -111,6 +111,35 @@ def _(image, adjust, iters, gamma, debug):
     e = image.new_empty(0)
     return (torch.empty_like(image), image.new_empty(B, 1, H, W) if extra else e,
             torch.empty_like(image) if extra else e, torch.empty_like(image) if extra else e)
+
+
+@torch.library.custom_op("b200dce::guided_filter", mutates_args=(), device_types="cuda")
+def guided_filter(image: Tensor, guide: Tensor, radius: int, eps: float) -> Tensor:
+    """filtering.GuidedFilter(radius, eps)(image, guide) (guided_filter.py:99-146), the step GCENet applies after its
+    curve loop (gcenet.py:391,485).  `radius` is the CLASS's argument: it reaches BoxFilter as kernel size, so the window
+    radius is int((radius - 1) / 2) (1 for GCENet's radius 3)."""
+    image, guide = _img(image, "image", None), _img(guide, "guide", None)
+    B, Cx, H, W = image.shape
+    C = guide.shape[1]
+    if guide.shape[0] != B or tuple(guide.shape[2:]) != (H, W) or Cx not in (1, C):
+        raise ValueError(f"b200dce::guided_filter: image {tuple(image.shape)} / guide {tuple(guide.shape)}")
+    if not (H > 2 * radius + 1 and W > 2 * radius + 1):   # the reference's assert (guided_filter.py:126)
+        raise ValueError("b200dce::guided_filter: H and W must exceed 2 * radius + 1")
+    out = torch.empty_like(guide)
+    if out.numel():
+        L = lib()
+        ws_bytes = L.b200_guided_filter_workspace_bytes(B, C, H, W)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=image.device)
+        with torch.cuda.device(image.device):
+            check(L.b200_guided_filter(image.data_ptr(), guide.data_ptr(), out.data_ptr(), B, Cx, C, H, W,
+                                       int((radius - 1) / 2), float(eps), ws.data_ptr(), ws_bytes, current_stream_ptr()),
+                  "b200_guided_filter")
+    return out
+
+
+@guided_filter.register_fake
+def _(image, guide, radius, eps):
+    return torch.empty_like(guide)
 
 
 @torch.library.custom_op("b200dce::curve_per_iter", mutates_args=(), device_types="cuda")

@@ -73,6 +73,17 @@ int b200_curve_shared(const float* x, const float* a, float* y, int B, int C, in
 int b200_gce_curve(const float* image, const float* adjust, float* enhanced, float* bam, float* bright, float* dark,
                    int B, int H, int W, int iters, float gamma, void* stream);
 
+/* GuidedFilter.forward(image = x, guide = y) at full resolution: out [B,C,H,W] = (box(A)/N) * x + box(b)/N with
+ * A = cov(x,y) / (var(x) + eps), b = mean_y - A * mean_x over (2 * box_radius + 1)^2 windows clipped at the borders.
+ * Replaces src/mon/vision/filtering/guided_filter.py:99-146 (box filter: box_filter.py:26-117, whose window sums are
+ * differences of fp32-rounded running sums accumulated in double: repeated here exactly), the step GCENet applies to
+ * the result of its curve loop (gcenet.py:391,485: GuidedFilter(radius=3, eps=1e-4)).  NOTE the reference class passes
+ * its `radius` to BoxFilter positionally, i.e. as KERNEL SIZE: box_radius = (radius - 1) / 2 (1 for GCENet).
+ * x is [B,Cx,H,W] with Cx == C or Cx == 1 (guided_filter.py:124); box_radius >= 1, H, W in [2r+1, 4096]. */
+size_t b200_guided_filter_workspace_bytes(int B, int C, int H, int W);
+int b200_guided_filter(const float* x, const float* y, float* out, int B, int Cx, int C, int H, int W, int box_radius,
+                       float eps, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Per-iteration maps: `a` is [B, C*iters, H, W]; iteration i uses channels
  * [i*C, (i+1)*C).  Replaces zero_dce.py:183-188 (torch.split + loop). */
 int b200_curve_per_iter(const float* x, const float* a, float* y, int B, int C, int H, int W, int iters, void* stream);

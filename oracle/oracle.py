@@ -301,6 +301,26 @@ def fast_guided_filter(x_lr: torch.Tensor, y_lr: torch.Tensor, x_hr: torch.Tenso
     return mean_a * x_hr + mean_b
 
 
+@torch.no_grad()
+def guided_filter(x: torch.Tensor, y: torch.Tensor, radius: int, eps: float = 1e-8) -> torch.Tensor:
+    """GuidedFilter(radius, eps).forward(image=x, guide=y), src/mon/vision/filtering/guided_filter.py:99-146, as GCENet
+    calls it (`self.gf(image, enhanced)`, gcenet.py:485, GuidedFilter(radius=3, eps=1e-4), :391).  The class builds its
+    box filter as `BoxFilter(self.radius)` -- positionally, i.e. as KERNEL SIZE (box_filter.py:161-171) -- so the window
+    radius is int((radius - 1) / 2): 1 for GCENet's radius 3."""
+    r = int((radius - 1) / 2)
+    h, w = x.shape[-2:]
+    n = box_filter_cumsum(x.new_ones(1, 1, h, w), r)
+    mean_x = box_filter_cumsum(x, r) / n
+    mean_y = box_filter_cumsum(y, r) / n
+    cov_xy = box_filter_cumsum(x * y, r) / n - mean_x * mean_y
+    var_x = box_filter_cumsum(x * x, r) / n - mean_x * mean_x
+    a = cov_xy / (var_x + eps)
+    b = mean_y - a * mean_x
+    mean_a = box_filter_cumsum(a, r) / n
+    mean_b = box_filter_cumsum(b, r) / n
+    return mean_a * x + mean_b
+
+
 def rgb_to_hsv_kornia(image: torch.Tensor, eps: float = 1e-8) -> torch.Tensor:
     """kornia.color.rgb_to_hsv as published (kornia is a dependency of the reference, unpinned in env/*.yaml and absent
     here: PARITY UNPINNED for this function).  H in [0, 2 pi], S = delta / (max + eps), V = max."""

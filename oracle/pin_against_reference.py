@@ -547,7 +547,19 @@ def main():
         garrs[f"{regime}:image_v_fixed"] = ref_v.numpy()
         garrs[f"{regime}:enhanced_unpinned"] = got["enhanced"].numpy()
         garrs[f"{regime}:A"], garrs[f"{regime}:b"] = a_.numpy(), b_.numpy()
+    # GCENet's post-network path: curve loop + GuidedFilter(radius=3, eps=1e-4) (gcenet.py:391,469-485)
+    ggen = torch.Generator().manual_seed(778)
+    gx = O.synthetic_lowlight(2, 41, 58, seed=703)
+    gadj2 = torch.rand(2, 3, 41, 58, generator=ggen) * 2 - 1
+    gy = O.gce_curve_loop(gx, gadj2, 15, 2.6)["enhanced"]
+    for rad, eps_ in ((3, 1e-4), (5, 1e-8), (9, 1e-2)):
+        with torch.no_grad():
+            ref_g = gfmod.GuidedFilter(radius=rad, eps=eps_)(gx, gy)
+        eq(O.guided_filter(gx, gy, rad, eps_), ref_g, f"guided_filter/r{rad}")
+        garrs[f"gf_r{rad}:out"] = ref_g.numpy()
+    garrs["gf:x"], garrs["gf:y"] = gx.numpy(), gy.numpy()
     np.savez_compressed(GOLD / "dcev_tail.npz", **garrs)
+    report.append("guided filter: oracle == the reference's GuidedFilter(radius, eps) for (3, 1e-4) [GCENet], (5, 1e-8), (9, 1e-2) (bit-exact)")
     report.append("dcev tail: oracle == the reference's ZeroDCEV.filter_up on its own FastGuidedFilter / BoxFilter (bit-exact); "
                   "`enhanced` (kornia HSV, absent here) is the oracle's restatement: UNPINNED")
 

@@ -768,3 +768,33 @@ def test_zero_dce_v_tail_vs_oracle(cuda_dev, B, H, W, S):
     _gf_close(v_fixed, ref["image_v_fixed"], "image_v_fixed")
     _gf_close(enh, ref["enhanced"], "enhanced")
     assert enh.amax(dim=(1, 2, 3)).eq(1.0).all()   # divided by the frame's own maximum
+
+
+# ------------------------------------------------------------------ GCENet's guided filter
+@pytest.mark.parametrize("radius,eps", [(3, 1e-4), (5, 1e-8), (9, 1e-2)])
+def test_guided_filter_golden(cuda_dev, radius, eps):
+    """b200dce::guided_filter against the reference's own GuidedFilter(radius, eps) (tests/golden/dcev_tail.npz)."""
+    z = np.load(GOLDEN_DIR / "dcev_tail.npz")
+    x, y = torch.from_numpy(z["gf:x"]).to(cuda_dev), torch.from_numpy(z["gf:y"]).to(cuda_dev)
+    out = torch.ops.b200dce.guided_filter(x, y, radius, eps)
+    _gf_close(out, torch.from_numpy(z[f"gf_r{radius}:out"]), f"guided_filter r={radius}")
+
+
+@pytest.mark.parametrize("B,C,Cx,H,W,radius", [(1, 3, 3, 1080, 1920, 3), (2, 3, 1, 67, 131, 3), (1, 1, 1, 17, 300, 7),
+                                               (3, 3, 3, 40, 33, 5)])
+def test_guided_filter_shapes_vs_oracle(cuda_dev, B, C, Cx, H, W, radius):
+    g = torch.Generator().manual_seed(H + W)
+    x = O.synthetic_lowlight(B, H, W, seed=H)[:, :Cx].contiguous()
+    adj = torch.rand(B, 3, H, W, generator=g) * 2 - 1
+    y = O.gce_curve_loop(O.synthetic_lowlight(B, H, W, seed=H), adj, 8, 2.6)["enhanced"][:, :C].contiguous()
+    ref = O.guided_filter(x, y, radius, 1e-4)
+    out = torch.ops.b200dce.guided_filter(x.to(cuda_dev), y.to(cuda_dev), radius, 1e-4)
+    _gf_close(out, ref, "guided_filter")
+
+
+def test_guided_filter_rejects_what_the_reference_asserts(cuda_dev):
+    x = torch.rand(1, 3, 9, 300, device=cuda_dev)
+    with pytest.raises(ValueError, match="2 \\* radius"):   # guided_filter.py:126
+        torch.ops.b200dce.guided_filter(x, x, 7, 1e-4)
+    with pytest.raises(ValueError):                           # c_x == 1 or c_x == c_y (:124)
+        torch.ops.b200dce.guided_filter(x[:, :2].contiguous(), x, 3, 1e-4)

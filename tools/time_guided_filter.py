@@ -1,0 +1,35 @@
+#!/usr/bin/env python
+"""GCENet's post-network path (curve loop + guided filter) timing: python tools/time_guided_filter.py [frames H W]"""
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+import torch  # noqa: E402
+
+import etss_07_imageenhance_b200 as P  # noqa: E402,F401
+
+F, H, W = (int(a) for a in sys.argv[1:4]) if len(sys.argv) >= 4 else (16, 1080, 1920)
+dev = torch.device("cuda:0")
+x = torch.rand(F, 3, H, W, device=dev) * 0.6
+adj = torch.rand(F, 3, H, W, device=dev) * 2 - 1
+
+
+def timed(fn, n=20):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(n):
+        fn()
+    t1.record()
+    torch.cuda.synchronize()
+    return t0.elapsed_time(t1) / n
+
+
+enh = torch.ops.b200dce.gce_curve(x, adj, 15, 2.6, False)[0]
+t_c = timed(lambda: torch.ops.b200dce.gce_curve(x, adj, 15, 2.6, False))
+t_g = timed(lambda: torch.ops.b200dce.guided_filter(x, enh, 3, 1e-4))
+px = F * H * W
+print(f"{F} x {H} x {W}: gce_curve {t_c:.3f} ms ({px * 36 / t_c / 1e6:.0f} GB/s on 36 B/px), guided_filter {t_g:.3f} ms "
+      f"({px * 36 / t_g / 1e6:.0f} GB/s on the algorithmic 36 B/px; six passes move ~500 B/px)")
