@@ -158,3 +158,11 @@ def test_oracle_zero_dce_v_tail_matches_reference_golden(golden, regime):
     assert torch.equal(got["enhanced"], torch.from_numpy(z[f"{regime}:enhanced_unpinned"]))
     # the conversions are each other's inverse up to rounding
     assert (O.hsv_to_rgb_kornia(O.rgb_to_hsv_kornia(x)) - x).abs().max() <= 1e-6
+
+
+@pytest.mark.parametrize("radius,eps", [(3, 1e-4), (5, 1e-8), (9, 1e-2)])
+def test_oracle_guided_filter_matches_reference_golden(radius, eps):
+    """tests/golden/dcev_tail.npz gf_r*: the reference's own GuidedFilter(radius, eps) (GCENet: 3, 1e-4)."""
+    z = np.load(GOLDEN_DIR / "dcev_tail.npz")
+    x, y = torch.from_numpy(z["gf:x"]), torch.from_numpy(z["gf:y"])
+    assert torch.equal(O.guided_filter(x, y, radius, eps), torch.from_numpy(z[f"gf_r{radius}:out"]))
