@@ -9,7 +9,7 @@
 //
 // Six HBM-bound passes over planes of B*C*H*W fp32:
 //   column scan (x, y -> 4 prefix planes) | row scan of diff_x | A, b | column scan (A, b) | row scan | output
-// Column scans: one thread per column (coalesced across the warp), 8 rows of loads in flight.  Row scans: a warp owns
+// Column scans: one thread per column and 72-row chunk (coalesced across the warp), 8 rows of loads in flight.  Row scans: a warp owns
 // 32 rows and moves 32 x 32 blocks through shared memory (coalesced 128-byte rows in and out, conflict-free scan).
 #include <math.h>
 
@@ -27,16 +27,21 @@ __device__ __forceinline__ float gfl_diff(const float* __restrict__ p, int i, in
     return __fsub_rn(hi, lo);
 }
 
-// Column scan.  MODE 0: sources x (plane index px) and y -> maps x, y, x*y, x*x; MODE 1: sources A, b -> maps A, b.
-// grid (ceil(W / 256), planes); out planes [map][plane][H][W]
-template <int MODE>
+// Column scan in chunks of GFL_CH rows (a frame's columns alone are too few threads to hide the latency of 1080
+// dependent steps): pass 1 = every chunk's total, pass 2 = the chunk's running sums on top of the totals above it.
+// Both accumulate in double: the partial sums are exact (see the header), so the chunked order gives the prefixes of
+// ATen's sequential loop.  MODE 0: sources x (plane index px) and y -> maps x, y, x*y, x*x; MODE 1: sources A, b -> A, b.
+// grid (ceil(W / 256), planes, chunks); out planes [map][plane][H][W]; tot [map][plane][chunk][W] doubles
+constexpr int GFL_CH = 72;
+
+template <int MODE, bool TOTALS>
 __global__ void __launch_bounds__(256) gfl_colscan_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
-                                                          float* __restrict__ out, int C, int Cx, int H, int W,
-                                                          size_t map_stride) {
+                                                          float* __restrict__ out, double* __restrict__ tot, int C, int Cx,
+                                                          int H, int W, size_t map_stride) {
     constexpr int NM = MODE == 0 ? 4 : 2;
     const int w = blockIdx.x * 256 + threadIdx.x;
     if (w >= W) return;
-    const int pl = blockIdx.y;  // frame * C + c
+    const int pl = blockIdx.y, ch = blockIdx.z, planes = gridDim.y, nch = gridDim.z;
     const size_t hw = (size_t)H * W;
     const int px = MODE == 0 ? (pl / C) * Cx + (Cx == 1 ? 0 : pl % C) : pl;
     const float* a = s0 + (size_t)px * hw + w;
@@ -45,6 +50,11 @@ __global__ void __launch_bounds__(256) gfl_colscan_kernel(const float* __restric
     double acc[NM];
 #pragma unroll
     for (int m = 0; m < NM; ++m) acc[m] = 0.0;
+    if (!TOTALS) {
+        for (int c = 0; c < ch; ++c)
+#pragma unroll
+            for (int m = 0; m < NM; ++m) acc[m] += tot[(((size_t)m * planes + pl) * nch + c) * W + w];
+    }
     auto step = [&](float av, float bv, size_t off) {
         float v[NM];
         v[0] = av, v[1] = bv;
@@ -52,37 +62,58 @@ __global__ void __launch_bounds__(256) gfl_colscan_kernel(const float* __restric
 #pragma unroll
         for (int m = 0; m < NM; ++m) {
             acc[m] += (double)v[m];
-            o[m * map_stride + off] = (float)acc[m];
+            if (!TOTALS) o[m * map_stride + off] = (float)acc[m];
         }
     };
-    int h = 0;
-    for (; h + 8 <= H; h += 8) {
+    const int h1 = min(H, (ch + 1) * GFL_CH);
+    int h = ch * GFL_CH;
+    for (; h + 8 <= h1; h += 8) {
         float av[8], bv[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) av[k] = a[(size_t)(h + k) * W], bv[k] = b[(size_t)(h + k) * W];
 #pragma unroll
         for (int k = 0; k < 8; ++k) step(av[k], bv[k], (size_t)(h + k) * W);
     }
-    for (; h < H; ++h) step(a[(size_t)h * W], b[(size_t)h * W], (size_t)h * W);
+    for (; h < h1; ++h) step(a[(size_t)h * W], b[(size_t)h * W], (size_t)h * W);
+    if (TOTALS) {
+#pragma unroll
+        for (int m = 0; m < NM; ++m) tot[(((size_t)m * planes + pl) * nch + ch) * W + w] = acc[m];
+    }
 }
 
-// Row scan of diff_x(P1): grid (ceil(H / 256), maps * planes), 8 warps x 32 rows
-__global__ void __launch_bounds__(256) gfl_rowscan_kernel(const float* __restrict__ p1, float* __restrict__ p2, int H, int W,
-                                                          int r, int planes, size_t map_stride) {
+// Row scan of diff_x(P1) in chunks of GFL_CW columns, two passes like the column scan (chunk totals, then the running
+// sums on top of the totals to the left).  grid (ceil(chunks / 8), maps * planes, ceil(H / 32)): the 8 warps of a CTA
+// take 8 adjacent column chunks of the same 32 rows (4 KB contiguous per row and CTA); a warp moves 32 x 32 blocks
+// through shared memory: coalesced 128-byte rows in and out, conflict-free scan along the rows.  Measured 1.5-2.2 TB/s
+// per pass at 16 x 1080p (~29 instructions per 32 elements: address arithmetic, fp32 <-> fp64 conversions, the two
+// shared-memory transposes): the slowest passes of the filter, not tuned further.
+// tot [map * planes][H][chunks] doubles
+constexpr int GFL_CW = 128;
+
+template <bool TOTALS>
+__global__ void __launch_bounds__(256) gfl_rowscan_kernel(const float* __restrict__ p1, float* __restrict__ p2,
+                                                          double* __restrict__ tot, int H, int W, int r, int planes,
+                                                          size_t map_stride, int nch) {
     __shared__ float tile[8][32][33];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t hw = (size_t)H * W;
     const size_t base = (size_t)(blockIdx.y / planes) * map_stride + (size_t)(blockIdx.y % planes) * hw;
     const float* src = p1 + base;
     float* dst = p2 + base;
-    const int r0 = blockIdx.x * 256 + warp * 32;
-    if (r0 >= H) return;
+    const int r0 = blockIdx.z * 32;
+    const int ch = blockIdx.x * 8 + warp;
+    if (ch >= nch) return;
+    const int row = r0 + lane;  // the row this lane scans
+    double* trow = tot + ((size_t)blockIdx.y * H + min(row, H - 1)) * nch;
     double acc = 0.0;
-    for (int c0 = 0; c0 < W; c0 += 32) {
+    if (!TOTALS && row < H)
+        for (int c = 0; c < ch; ++c) acc += trow[c];
+    const int c1 = min(W, (ch + 1) * GFL_CW);
+    for (int c0 = ch * GFL_CW; c0 < c1; c0 += 32) {
         const int w = c0 + lane;
-#pragma unroll 8
+#pragma unroll 16
         for (int k = 0; k < 32; ++k)
-            tile[warp][k][lane] = (r0 + k < H && w < W) ? gfl_diff(src + w, r0 + k, H, r, (size_t)W) : 0.f;
+            tile[warp][k][lane] = (r0 + k < H && w < c1) ? gfl_diff(src + w, r0 + k, H, r, (size_t)W) : 0.f;
         __syncwarp();
         float o[32];
 #pragma unroll
@@ -91,14 +122,17 @@ __global__ void __launch_bounds__(256) gfl_rowscan_kernel(const float* __restric
             o[k] = (float)acc;
         }
         __syncwarp();
+        if (!TOTALS) {
 #pragma unroll
-        for (int k = 0; k < 32; ++k) tile[warp][lane][k] = o[k];
-        __syncwarp();
-#pragma unroll 8
-        for (int k = 0; k < 32; ++k)
-            if (r0 + k < H && w < W) dst[(size_t)(r0 + k) * W + w] = tile[warp][k][lane];
-        __syncwarp();
+            for (int k = 0; k < 32; ++k) tile[warp][lane][k] = o[k];
+            __syncwarp();
+#pragma unroll 16
+            for (int k = 0; k < 32; ++k)
+                if (r0 + k < H && w < c1) dst[(size_t)(r0 + k) * W + w] = tile[warp][k][lane];
+            __syncwarp();
+        }
     }
+    if (TOTALS && row < H) trow[ch] = acc;
 }
 
 __device__ __forceinline__ float gfl_count(int h, int w, int H, int W, int r) {  // box(1): exact
@@ -145,10 +179,13 @@ __global__ void __launch_bounds__(256) gfl_out_kernel(const float* __restrict__ 
 
 }  // namespace b200
 
-// scratch: 4 + 4 prefix planes and A, b, each planes * H * W fp32
+// scratch: 4 + 4 prefix planes and A, b, each planes * H * W fp32, and the chunk totals of the column scans
 extern "C" size_t b200_guided_filter_workspace_bytes(int B, int C, int H, int W) {
     if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return 0;
-    return 10 * b200::gfl_align_up((size_t)B * C * H * W * sizeof(float), 256);
+    const size_t nch = (size_t)(H + b200::GFL_CH - 1) / b200::GFL_CH, ncw = (size_t)(W + b200::GFL_CW - 1) / b200::GFL_CW;
+    const size_t per_plane = nch * W > ncw * H ? nch * W : ncw * H;  // column-scan totals, later row-scan totals
+    return 10 * b200::gfl_align_up((size_t)B * C * H * W * sizeof(float), 256) +
+           b200::gfl_align_up(4 * (size_t)B * C * per_plane * sizeof(double), 256);
 }
 
 extern "C" int b200_guided_filter(const float* x, const float* y, float* out, int B, int Cx, int C, int H, int W,
@@ -160,7 +197,7 @@ extern "C" int b200_guided_filter(const float* x, const float* y, float* out, in
     const int r = box_radius;
     // box_filter's slicing needs 2r + 1 <= size; r = 0 fails in the reference (empty slice), the double-accumulated
     // prefixes are exact for <= 4096 addends
-    if (r < 1 || H < 2 * r + 1 || W < 2 * r + 1 || H > 4096 || W > 4096 || (long long)B * C > 65535) return B200_ERR_UNSUPPORTED;
+    if (r < 1 || H < 2 * r + 1 || W < 2 * r + 1 || H > 4096 || W > 4096 || (long long)B * C * 4 > 65535) return B200_ERR_UNSUPPORTED;  // grid.y / grid.z limits
     if (workspace_bytes < b200_guided_filter_workspace_bytes(B, C, H, W)) return B200_ERR_WORKSPACE;
     if ((reinterpret_cast<uintptr_t>(workspace) & 15u) != 0) return B200_ERR_MISALIGNED;
     cudaStream_t s = (cudaStream_t)stream;
@@ -170,15 +207,22 @@ extern "C" int b200_guided_filter(const float* x, const float* y, float* out, in
     float* p2 = p1 + 4 * plane_set;       // 4 maps
     float* A = p2 + 4 * plane_set;
     float* Bc = A + plane_set;
+    double* tot = (double*)(Bc + plane_set);
+    const int nch = (H + GFL_CH - 1) / GFL_CH;
     const long long total = (long long)planes * H * W;
     long long eb = (total + 255) / 256;
     if (eb > B200_NUM_SMS * 32) eb = B200_NUM_SMS * 32;
-    const dim3 cgrid((W + 255) / 256, planes);
-    gfl_colscan_kernel<0><<<cgrid, 256, 0, s>>>(x, y, p1, C, Cx, H, W, plane_set);
-    gfl_rowscan_kernel<<<dim3((H + 255) / 256, planes * 4), 256, 0, s>>>(p1, p2, H, W, r, planes, plane_set);
+    const dim3 cgrid((W + 255) / 256, planes, nch);
+    gfl_colscan_kernel<0, true><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, plane_set);
+    gfl_colscan_kernel<0, false><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, plane_set);
+    const int ncw = (W + GFL_CW - 1) / GFL_CW;
+    gfl_rowscan_kernel<true><<<dim3((ncw + 7) / 8, planes * 4, (H + 31) / 32), 256, 0, s>>>(p1, p2, tot, H, W, r, planes, plane_set, ncw);
+    gfl_rowscan_kernel<false><<<dim3((ncw + 7) / 8, planes * 4, (H + 31) / 32), 256, 0, s>>>(p1, p2, tot, H, W, r, planes, plane_set, ncw);
     gfl_ab_kernel<<<(unsigned)eb, 256, 0, s>>>(p2, A, Bc, H, W, r, eps, plane_set, total);
-    gfl_colscan_kernel<1><<<cgrid, 256, 0, s>>>(A, Bc, p1, C, C, H, W, plane_set);
-    gfl_rowscan_kernel<<<dim3((H + 255) / 256, planes * 2), 256, 0, s>>>(p1, p2, H, W, r, planes, plane_set);
+    gfl_colscan_kernel<1, true><<<cgrid, 256, 0, s>>>(A, Bc, p1, tot, C, C, H, W, plane_set);
+    gfl_colscan_kernel<1, false><<<cgrid, 256, 0, s>>>(A, Bc, p1, tot, C, C, H, W, plane_set);
+    gfl_rowscan_kernel<true><<<dim3((ncw + 7) / 8, planes * 2, (H + 31) / 32), 256, 0, s>>>(p1, p2, tot, H, W, r, planes, plane_set, ncw);
+    gfl_rowscan_kernel<false><<<dim3((ncw + 7) / 8, planes * 2, (H + 31) / 32), 256, 0, s>>>(p1, p2, tot, H, W, r, planes, plane_set, ncw);
     gfl_out_kernel<<<(unsigned)eb, 256, 0, s>>>(p2, x, out, C, Cx, H, W, r, plane_set, total);
     return launch_status();
 }
