@@ -825,8 +825,11 @@ static int launch_mm_net(const MmNetArgs& a, MmApplyArgs ap, const float* xin, f
         // (measured, 16 x 1080p / 8 x 2160p: ~3.25 tiles per worker and layer is the knee -- smaller groups start the
         // full-resolution pass earlier but stall producers on predecessors and starve the tile phase of parallelism)
         long long g = (13 * 2 * grid + 4 * tpf - 1) / (4 * tpf);
-        if (const char* e = getenv("B200DCE_DCEPP_GROUP")) g = atoi(e);  // tuning aid
-        ap.group = (int)(g < 1 ? 1 : (g > B ? B : g));
+        if (const char* e = getenv("B200DCE_DCEPP_GROUP"))  // tuning aid; an empty / non-positive value means "unset"
+            if (atoi(e) > 0) g = atoi(e);
+        g = g < 1 ? 1 : (g > B ? B : g);
+        const long long ngroups = (B + g - 1) / g;
+        ap.group = (int)((B + ngroups - 1) / ngroups);  // equal groups: 8 frames with g = 5 run as 4 + 4, not 5 + 3
     }
     kern<<<(unsigned)grid, MM_THREADS, MM_NET_SMEM, s>>>(a, ap, m[0], m[1], m[2], m[3], m[4], m[5], m[6], B, h, w, sync);
     return launch_status();
