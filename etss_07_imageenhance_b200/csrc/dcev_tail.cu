@@ -147,10 +147,14 @@ __device__ __forceinline__ CubicTap cubic_tap(int dst, float scale, int in_size)
 
 // kornia.color.rgb_to_hsv / hsv_to_rgb as published (eps = 1e-8), with V replaced in between; fp32 op for op as the
 // oracle's restatement (oracle/oracle.py rgb_to_hsv_kornia / hsv_to_rgb_kornia)
-__device__ __forceinline__ float pymod(float a, float m) {  // Python / torch `%` for m > 0
-    float r = fmodf(a, m);
-    if (r != 0.f && r < 0.f) r = __fadd_rn(r, m);
+// Python / torch `%` on the two ranges that occur (no fmodf: the library routine is ~40 instructions):
+__device__ __forceinline__ float pymod1(float a) {  // a % 1.0 for |a| < 2^23: the fractional part is exact
+    float r = __fsub_rn(a, truncf(a));
+    if (r < 0.f) r = __fadd_rn(r, 1.f);
     return r;
+}
+__device__ __forceinline__ float pymod6(float a) {  // a % 6.0 for 0 <= a < 12: the subtraction is exact
+    return a >= 6.f ? __fsub_rn(a, 6.f) : a;
 }
 __device__ __forceinline__ void recolor(float r, float g, float b, float v_new, float& ro, float& go, float& bo) {
     const float mx = fmaxf(fmaxf(r, g), b), mn = fminf(fminf(r, g), b);
@@ -163,13 +167,13 @@ __device__ __forceinline__ void recolor(float r, float g, float b, float v_new, 
             : arg == 1 ? __fadd_rn(__fsub_rn(rc, bc), __fmul_rn(2.f, delta))
                        : __fadd_rn(__fsub_rn(gc, rc), __fmul_rn(4.f, delta));
     h = __fdiv_rn(h, delta);
-    h = pymod(__fdiv_rn(h, 6.f), 1.f);
+    h = pymod1(__fdiv_rn(h, 6.f));
     h = __fmul_rn(6.2831854820251465f, h);          // 2 * math.pi as the fp32 scalar torch multiplies by
     // hsv_to_rgb
     const float hh = __fdiv_rn(h, 6.2831854820251465f);
     const float h6 = __fmul_rn(hh, 6.f);
-    const float hi = pymod(floorf(h6), 6.f);
-    const float f = __fsub_rn(pymod(h6, 6.f), hi);
+    const float hi = pymod6(floorf(h6));
+    const float f = __fsub_rn(pymod6(h6), hi);
     const float p = __fmul_rn(v_new, __fsub_rn(1.f, s));
     const float q = __fmul_rn(v_new, __fsub_rn(1.f, __fmul_rn(f, s)));
     const float t = __fmul_rn(v_new, __fsub_rn(1.f, __fmul_rn(__fsub_rn(1.f, f), s)));
@@ -183,43 +187,60 @@ __device__ __forceinline__ void recolor(float r, float g, float b, float v_new, 
     }
 }
 
-// Full resolution, one thread per pixel: image_v_fixed = clip(A_up * v + b_up), the recoloured pixel (not yet divided
-// by the frame maximum) and the frame maximum (non-negative floats order like their bit patterns).
+// Full resolution: image_v_fixed = clip(A_up * v + b_up), the recoloured pixel (not yet divided by the frame maximum)
+// and the frame maximum (non-negative floats order like their bit patterns).  Thread = column, CTA = 256 columns x
+// GF_ROWS rows: the column's four x taps are computed once, and the four x-interpolated source rows of A and b are
+// kept while consecutive output rows fall between the same source rows (every ~4 rows change at 256 -> 1080).
+constexpr int GF_ROWS = 32;
 __global__ void __launch_bounds__(256) dcev_gf_apply_kernel(const float* __restrict__ rgb, const float* __restrict__ v,
                                                             const float* __restrict__ A, const float* __restrict__ Bc,
                                                             float* __restrict__ v_fixed, float* __restrict__ out,
                                                             unsigned int* __restrict__ fmax, int H, int W, int S,
                                                             float sh, float sw) {
-    const int f = blockIdx.z, y = blockIdx.y;
+    const int f = blockIdx.z, x = blockIdx.x * 256 + threadIdx.x;
     const size_t hw = (size_t)H * W, ss = (size_t)S * S;
-    const CubicTap ty = cubic_tap(y, sh, S);
     const float* a = A + f * ss;
     const float* b = Bc + f * ss;
     float local_max = 0.f;
-    for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < W; x += gridDim.x * blockDim.x) {
+    if (x < W) {
         const CubicTap tx = cubic_tap(x, sw, S);
-        float ua = 0.f, ub = 0.f;
+        float ra[4], rb[4];
+        int have = -0x7fffffff;  // first source row of the cached window
+        const int y1 = min(H, (blockIdx.y + 1) * GF_ROWS);
+        for (int y = blockIdx.y * GF_ROWS; y < y1; ++y) {
+            const CubicTap ty = cubic_tap(y, sh, S);
+            const int first = (int)floorf(__fmul_rn(sh, (float)y)) - 1;  // unclamped: identifies the window
+            if (first != have) {
+                have = first;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {  // ATen: sum over the rows of (row interpolated along x) * wy
-            float ra = 0.f, rb = 0.f;
+                for (int j = 0; j < 4; ++j) {  // ATen: a row is interpolated along x first
+                    const float* ar = a + (size_t)ty.i[j] * S;
+                    const float* br = b + (size_t)ty.i[j] * S;
+                    ra[j] = __fmul_rn(__ldg(ar + tx.i[0]), tx.w[0]);
+                    rb[j] = __fmul_rn(__ldg(br + tx.i[0]), tx.w[0]);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const size_t o = (size_t)ty.i[j] * S + tx.i[i];
-                ra = i == 0 ? __fmul_rn(__ldg(a + o), tx.w[0]) : __fadd_rn(ra, __fmul_rn(__ldg(a + o), tx.w[i]));
-                rb = i == 0 ? __fmul_rn(__ldg(b + o), tx.w[0]) : __fadd_rn(rb, __fmul_rn(__ldg(b + o), tx.w[i]));
+                    for (int i = 1; i < 4; ++i) {
+                        ra[j] = __fadd_rn(ra[j], __fmul_rn(__ldg(ar + tx.i[i]), tx.w[i]));
+                        rb[j] = __fadd_rn(rb[j], __fmul_rn(__ldg(br + tx.i[i]), tx.w[i]));
+                    }
+                }
             }
-            ua = j == 0 ? __fmul_rn(ra, ty.w[0]) : __fadd_rn(ua, __fmul_rn(ra, ty.w[j]));
-            ub = j == 0 ? __fmul_rn(rb, ty.w[0]) : __fadd_rn(ub, __fmul_rn(rb, ty.w[j]));
+            float ua = __fmul_rn(ra[0], ty.w[0]), ub = __fmul_rn(rb[0], ty.w[0]);
+#pragma unroll
+            for (int j = 1; j < 4; ++j) {
+                ua = __fadd_rn(ua, __fmul_rn(ra[j], ty.w[j]));
+                ub = __fadd_rn(ub, __fmul_rn(rb[j], ty.w[j]));
+            }
+            const size_t p = (size_t)y * W + x;
+            const float vf = fminf(fmaxf(__fadd_rn(__fmul_rn(ua, v[f * hw + p]), ub), 0.f), 1.f);
+            v_fixed[f * hw + p] = vf;
+            float ro, go, bo;
+            recolor(rgb[(f * 3 + 0) * hw + p], rgb[(f * 3 + 1) * hw + p], rgb[(f * 3 + 2) * hw + p], vf, ro, go, bo);
+            out[(f * 3 + 0) * hw + p] = ro;
+            out[(f * 3 + 1) * hw + p] = go;
+            out[(f * 3 + 2) * hw + p] = bo;
+            local_max = fmaxf(local_max, fmaxf(fmaxf(ro, go), bo));
         }
-        const size_t p = (size_t)y * W + x;
-        const float vf = fminf(fmaxf(__fadd_rn(__fmul_rn(ua, v[f * hw + p]), ub), 0.f), 1.f);
-        v_fixed[f * hw + p] = vf;
-        float ro, go, bo;
-        recolor(rgb[(f * 3 + 0) * hw + p], rgb[(f * 3 + 1) * hw + p], rgb[(f * 3 + 2) * hw + p], vf, ro, go, bo);
-        out[(f * 3 + 0) * hw + p] = ro;
-        out[(f * 3 + 1) * hw + p] = go;
-        out[(f * 3 + 2) * hw + p] = bo;
-        local_max = fmaxf(local_max, fmaxf(fmaxf(ro, go), bo));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) local_max = fmaxf(local_max, __shfl_xor_sync(0xffffffffu, local_max, o));
@@ -248,7 +269,7 @@ extern "C" int b200_dcev_tail(const float* image_rgb, const float* image_v, cons
         return B200_ERR_NULL;
     if (B <= 0 || H <= 0 || W <= 0 || S <= 0) return B200_ERR_BAD_SHAPE;
     // FastGuidedFilter asserts h, w > 2 * radius + 1 (guided_filter.py:182)
-    if (S <= 2 * GF_R + 1 || B > 65535 || H > 65535) return B200_ERR_UNSUPPORTED;
+    if (S <= 2 * GF_R + 1 || B > 65535) return B200_ERR_UNSUPPORTED;
     if (workspace_bytes < b200_dcev_tail_workspace_bytes(B, S)) return B200_ERR_WORKSPACE;
     if ((reinterpret_cast<uintptr_t>(workspace) & 15u) != 0) return B200_ERR_MISALIGNED;
     cudaStream_t s = (cudaStream_t)stream;
@@ -268,7 +289,7 @@ extern "C" int b200_dcev_tail(const float* image_rgb, const float* image_v, cons
     // ATen area_pixel_compute_scale<float>(in, out, align_corners=true) = (in - 1) / (out - 1), 0 when out == 1
     const float sh = H > 1 ? (float)(S - 1) / (float)(H - 1) : 0.f;
     const float sw = W > 1 ? (float)(S - 1) / (float)(W - 1) : 0.f;
-    dim3 grid((W + 255) / 256 > 8 ? 8 : (W + 255) / 256, H, B);
+    dim3 grid((W + 255) / 256, (H + GF_ROWS - 1) / GF_ROWS, B);
     dcev_gf_apply_kernel<<<grid, 256, 0, s>>>(image_rgb, image_v, A, Bc, image_v_fixed, enhanced, fmax, H, W, S, sh, sw);
     const long long per = 3LL * H * W, total = per * B;
     long long blocks = (total + 255) / 256;
