@@ -7,11 +7,13 @@
 // kernels below do the same (sums of <= 2^12 fp32 values >= 2^-18 are exact in double in any order), because A is a
 // quotient of two such differences and amplifies their rounding (see dcev_tail.cu / DESIGN.md).
 //
-// Six HBM-bound passes over planes of B*C*H*W fp32:
-//   column scan (x, y -> 4 prefix planes) | row scan of diff_x | A, b | column scan (A, b) | row scan | output
-// Column scans: one thread per column and 72-row chunk (coalesced across the warp), 8 rows of loads in flight.  Row scans: a warp owns
-// 32 rows and moves 32 x 32 blocks through shared memory (coalesced 128-byte rows in and out, conflict-free scan).
+// Passes over planes of B*C*H*W fp32 (default): chunk totals of the columns | column pass: D1 = diff_x(cumsum(2)) from two
+// running prefixes, no prefix plane stored | row pass: cumsum(3) of a row in shared memory, diff_y, and the stage's
+// arithmetic (A, b / the output) | the same three for A, b.  ~80 B per plane pixel instead of the ~250 B of the first
+// version (B200DCE_GF_FUSED=0: column scan, row-scan totals, row scan, A / b, ... as separate HBM round trips; kept
+// for A/B, bit-identical).  16 x 1080p: 2.6 ms (was 7.2), one frame 0.23 ms (was 0.56).
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -177,6 +179,185 @@ __global__ void __launch_bounds__(256) gfl_out_kernel(const float* __restrict__ 
     }
 }
 
+
+// ---- the same arithmetic in four passes instead of six (default; B200DCE_GF_FUSED=0 keeps the six above for A/B) ----
+// Column pass: D1 = diff_x(t.cumsum(2)) without storing the prefixes.  A thread walks its column chunk with TWO exact
+// double running sums, the prefix through row h + r and the prefix through row h - r - 1 (both start from the chunk
+// totals of gfl_colscan_kernel<MODE, true>; the trailing rows are re-read from L1 / L2), rounds each to fp32 as the
+// cumsum does and subtracts.  grid (ceil(W / 256), planes, chunks); out planes [map][plane][H][W]
+template <int MODE>
+__global__ void __launch_bounds__(256) gfl_coldiff_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
+                                                          float* __restrict__ out, const double* __restrict__ tot, int C,
+                                                          int Cx, int H, int W, int r, size_t map_stride) {
+    constexpr int NM = MODE == 0 ? 4 : 2;
+    const int w = blockIdx.x * 256 + threadIdx.x;
+    if (w >= W) return;
+    const int pl = blockIdx.y, ch = blockIdx.z, planes = gridDim.y, nch = gridDim.z;
+    const size_t hw = (size_t)H * W;
+    const int px = MODE == 0 ? (pl / C) * Cx + (Cx == 1 ? 0 : pl % C) : pl;
+    const float* a = s0 + (size_t)px * hw + w;
+    const float* b = s1 + (size_t)pl * hw + w;
+    float* o = out + (size_t)pl * hw + w;
+    double lead[NM], trail[NM];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) lead[m] = 0.0;
+    for (int c = 0; c < ch; ++c)
+#pragma unroll
+        for (int m = 0; m < NM; ++m) lead[m] += tot[(((size_t)m * planes + pl) * nch + c) * W + w];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) trail[m] = lead[m];
+    auto maps = [&](float av, float bv, float (&v)[NM]) {
+        v[0] = av, v[1] = bv;
+        if (MODE == 0) v[2 % NM] = __fmul_rn(av, bv), v[3 % NM] = __fmul_rn(av, av);
+    };
+    const int h0 = ch * GFL_CH, h1 = min(H, h0 + GFL_CH);
+    for (int k = h0; k < min(h0 + r, H); ++k) {  // lead = prefix through row h0 + r - 1
+        float v[NM];
+        maps(a[(size_t)k * W], b[(size_t)k * W], v);
+#pragma unroll
+        for (int m = 0; m < NM; ++m) lead[m] += (double)v[m];
+    }
+    for (int k = max(h0 - r - 1, 0); k < h0; ++k) {  // trail = prefix through row h0 - r - 2 (exact: see the header)
+        float v[NM];
+        maps(a[(size_t)k * W], b[(size_t)k * W], v);
+#pragma unroll
+        for (int m = 0; m < NM; ++m) trail[m] -= (double)v[m];
+    }
+    for (int h = h0; h < h1; h += 4) {
+        float la[4], lb[4], ta[4], tb[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {  // rows past the ends are read clamped and not added
+            const size_t lo = (size_t)min(h + k + r, H - 1) * W, to = (size_t)max(h + k - r - 1, 0) * W;
+            la[k] = a[lo], lb[k] = b[lo], ta[k] = a[to], tb[k] = b[to];
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = h + k;
+            if (i >= h1) break;
+            float v[NM], u[NM];
+            maps(la[k], lb[k], v);
+            maps(ta[k], tb[k], u);
+            const bool add_lead = i + r < H, has_lo = i - r - 1 >= 0;
+#pragma unroll
+            for (int m = 0; m < NM; ++m) {
+                if (add_lead) lead[m] += (double)v[m];
+                if (has_lo) trail[m] += (double)u[m];
+                // box_filter.py:26-45: rows <= r take the prefix itself (hi - 0 is the same value)
+                o[m * map_stride + (size_t)i * W] = __fsub_rn((float)lead[m], has_lo ? (float)trail[m] : 0.f);
+            }
+        }
+    }
+}
+
+// Row pass: one CTA per (image row, plane) runs cumsum(3) of the row's D1 values -- a lane sums its run of E contiguous
+// elements in double, a shuffle scan and eight warp totals give every run its exact base, the rounded prefixes go to
+// shared memory -- then takes diff_y from there and finishes the stage: MODE 0: the four window sums -> A, b;
+// MODE 1: box(A), box(b), x -> out.  No totals pass, no prefix plane in HBM.  grid (H, planes); 8 * 32 * E >= W
+__device__ __forceinline__ double gfl_shfl_up(double v, int o) {
+    return __hiloint2double(__shfl_up_sync(0xffffffffu, __double2hiint(v), o),
+                            __shfl_up_sync(0xffffffffu, __double2loint(v), o));
+}
+template <int MODE, int E>
+__global__ void __launch_bounds__(256) gfl_rowbox_kernel(const float* __restrict__ d1, float* __restrict__ o0,
+                                                         float* __restrict__ o1, const float* __restrict__ x, int C,
+                                                         int Cx, int H, int W, int r, float eps, size_t map_stride) {
+    constexpr int NM = MODE == 0 ? 4 : 2;
+    extern __shared__ __align__(16) unsigned char gfl_smem[];
+    double* wtot = reinterpret_cast<double*>(gfl_smem);   // [NM][8]
+    float* srow = reinterpret_cast<float*>(wtot + NM * 8);  // [NM][Wp]
+    const int Wp = (W + 3) & ~3;
+    const int h = blockIdx.x, pl = blockIdx.y;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t row = ((size_t)pl * H + h) * W;
+    const int w0 = threadIdx.x * E;
+    const bool vec = (W & 3) == 0;
+    float v[NM][E];
+    double excl[NM];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+        const float* src = d1 + m * map_stride + row;
+        double acc = 0.0;
+#pragma unroll
+        for (int j = 0; j < E; j += 4) {
+            float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (vec) {
+                if (w0 + j < W) q = *reinterpret_cast<const float4*>(src + w0 + j);
+            } else {
+                if (w0 + j < W) q.x = src[w0 + j];
+                if (w0 + j + 1 < W) q.y = src[w0 + j + 1];
+                if (w0 + j + 2 < W) q.z = src[w0 + j + 2];
+                if (w0 + j + 3 < W) q.w = src[w0 + j + 3];
+            }
+            v[m][j] = q.x, v[m][j + 1] = q.y, v[m][j + 2] = q.z, v[m][j + 3] = q.w;
+            acc += (double)q.x, acc += (double)q.y, acc += (double)q.z, acc += (double)q.w;
+        }
+        double s = acc;  // inclusive scan over the lanes (exact sums: any order gives the sequential loop's prefixes)
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const double t = gfl_shfl_up(s, o);
+            if (lane >= o) s += t;
+        }
+        excl[m] = s - acc;
+        if (lane == 31) wtot[m * 8 + warp] = s;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+        double acc = excl[m];
+        for (int k = 0; k < warp; ++k) acc += wtot[m * 8 + k];
+        float* dst = srow + m * Wp;
+#pragma unroll
+        for (int j = 0; j < E; j += 4) {
+            float4 q;
+            acc += (double)v[m][j], q.x = (float)acc;
+            acc += (double)v[m][j + 1], q.y = (float)acc;
+            acc += (double)v[m][j + 2], q.z = (float)acc;
+            acc += (double)v[m][j + 3], q.w = (float)acc;
+            if (w0 + j < Wp) *reinterpret_cast<float4*>(dst + w0 + j) = q;
+        }
+    }
+    __syncthreads();
+    const long long hw = (long long)H * W;
+    for (int w = threadIdx.x; w < W; w += 256) {
+        const float n = gfl_count(h, w, H, W, r);
+        float bx[NM];
+#pragma unroll
+        for (int m = 0; m < NM; ++m) bx[m] = gfl_diff(srow + m * Wp, w, W, r, 1);
+        if (MODE == 0) {
+            const float mean_x = __fdiv_rn(bx[0], n), mean_y = __fdiv_rn(bx[1], n);
+            const float cov = __fsub_rn(__fdiv_rn(bx[2 % NM], n), __fmul_rn(mean_x, mean_y));
+            const float var = __fsub_rn(__fdiv_rn(bx[3 % NM], n), __fmul_rn(mean_x, mean_x));
+            const float a = __fdiv_rn(cov, __fadd_rn(var, eps));
+            o0[row + w] = a;
+            o1[row + w] = __fsub_rn(mean_y, __fmul_rn(a, mean_x));
+        } else {
+            const float ma = __fdiv_rn(bx[0], n), mb = __fdiv_rn(bx[1], n);
+            const long long px = (long long)(pl / C) * Cx + (Cx == 1 ? 0 : pl % C);
+            o0[row + w] = __fadd_rn(__fmul_rn(ma, x[px * hw + (long long)h * W + w]), mb);
+        }
+    }
+}
+
+template <int MODE, int E>
+static void gfl_launch_rowbox(const float* d1, float* o0, float* o1, const float* x, int planes, int C, int Cx, int H,
+                              int W, int r, float eps, size_t map_stride, cudaStream_t s) {
+    constexpr int NM = MODE == 0 ? 4 : 2;
+    const size_t smem = NM * 8 * sizeof(double) + (size_t)NM * ((W + 3) & ~3) * sizeof(float);
+    if (smem > 48 * 1024)  // only rows beyond ~3000 pixels; per device, so not cached
+        cudaFuncSetAttribute(gfl_rowbox_kernel<MODE, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    gfl_rowbox_kernel<MODE, E><<<dim3(H, planes), 256, smem, s>>>(d1, o0, o1, x, C, Cx, H, W, r, eps, map_stride);
+}
+template <int MODE>
+static void gfl_rowbox(const float* d1, float* o0, float* o1, const float* x, int planes, int C, int Cx, int H, int W,
+                       int r, float eps, size_t map_stride, cudaStream_t s) {
+    if (W <= 1024)
+        gfl_launch_rowbox<MODE, 4>(d1, o0, o1, x, planes, C, Cx, H, W, r, eps, map_stride, s);
+    else if (W <= 2048)
+        gfl_launch_rowbox<MODE, 8>(d1, o0, o1, x, planes, C, Cx, H, W, r, eps, map_stride, s);
+    else
+        gfl_launch_rowbox<MODE, 16>(d1, o0, o1, x, planes, C, Cx, H, W, r, eps, map_stride, s);
+}
+
 }  // namespace b200
 
 // scratch: 4 + 4 prefix planes and A, b, each planes * H * W fp32, and the chunk totals of the column scans
@@ -213,6 +394,16 @@ extern "C" int b200_guided_filter(const float* x, const float* y, float* out, in
     long long eb = (total + 255) / 256;
     if (eb > B200_NUM_SMS * 32) eb = B200_NUM_SMS * 32;
     const dim3 cgrid((W + 255) / 256, planes, nch);
+    const char* fused = getenv("B200DCE_GF_FUSED");
+    if (!fused || fused[0] != '0') {  // four passes + two totals passes; (grid.x = H, grid.y = planes)
+        gfl_colscan_kernel<0, true><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, plane_set);
+        gfl_coldiff_kernel<0><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, r, plane_set);
+        gfl_rowbox<0>(p1, A, Bc, nullptr, planes, C, Cx, H, W, r, eps, plane_set, s);
+        gfl_colscan_kernel<1, true><<<cgrid, 256, 0, s>>>(A, Bc, p1, tot, C, C, H, W, plane_set);
+        gfl_coldiff_kernel<1><<<cgrid, 256, 0, s>>>(A, Bc, p1, tot, C, C, H, W, r, plane_set);
+        gfl_rowbox<1>(p1, out, nullptr, x, planes, C, Cx, H, W, r, eps, plane_set, s);
+        return launch_status();
+    }
     gfl_colscan_kernel<0, true><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, plane_set);
     gfl_colscan_kernel<0, false><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, plane_set);
     const int ncw = (W + GFL_CW - 1) / GFL_CW;
