@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "dce_tc.cuh"
 #include "dce_x3.cuh"
+#include "tcgen05.cuh"
 
 namespace b200 {
 
@@ -52,8 +53,9 @@ template <bool TANH>
 __global__ void __launch_bounds__(256, 2)
 dce_conv_f32_kernel(const float* __restrict__ srcA, int ca, const float* __restrict__ srcB, int cb,
                     float* __restrict__ dst, const float* __restrict__ wl, int cout, int H, int W) {
-    __shared__ __align__(16) float s_in[C_CS * 10 * C_HS];
-    __shared__ __align__(16) float s_w[C_CS * 9 * 32];
+    // two stages: the next chunk's halo tile and weights arrive by cp.async while this one is computed
+    __shared__ __align__(16) float s_in_all[2][C_CS * 10 * C_HS];
+    __shared__ __align__(16) float s_w_all[2][C_CS * 9 * 32];
     const int t = threadIdx.x;
     const int b = blockIdx.z;
     const int y0 = blockIdx.y * C_TH, x0 = blockIdx.x * C_TW;
@@ -72,29 +74,51 @@ dce_conv_f32_kernel(const float* __restrict__ srcA, int ca, const float* __restr
 #pragma unroll
         for (int o = 0; o < 4; ++o) acc[p][o] = make_float2(0.f, 0.f);
 
-    for (int c0 = 0; c0 < cin; c0 += C_CS) {
+    // staging map, the same for every chunk: warp k copies channel c0 + k, a lane the elements lane, lane + 32, ...
+    // of its 10 x 34 halo tile (offset -1 = outside the image: zero fill)
+    int goff[11];
+#pragma unroll
+    for (int i = 0; i < 11; ++i) {
+        const int e = lane + 32 * i;
+        const int rr = e / 34, cc = e - rr * 34;
+        const int yy = y0 - 1 + rr, xx = x0 - 1 + cc;
+        goff[i] = (e < 340 && yy >= 0 && yy < H && xx >= 0 && xx < W) ? yy * W + xx : -1;
+    }
+    auto stage = [&](int c0, int buf) {
         const int nvalid = min(C_CS, cin - c0);
-        __syncthreads();
-        for (int idx = t; idx < C_CS * 10 * 34; idx += 256) {
-            const int k = idx / 340;
-            const int rem = idx - k * 340;
-            const int rr = rem / 34, cc = rem - rr * 34;
-            const int yy = y0 - 1 + rr, xx = x0 - 1 + cc;
-            float v = 0.f;
-            if (k < nvalid && yy >= 0 && yy < H && xx >= 0 && xx < W) {
-                const int c = c0 + k;
-                const float* src = c < ca ? srcA + ((size_t)b * ca + c) * plane : srcB + ((size_t)b * cb + (c - ca)) * plane;
-                v = __ldg(src + (size_t)yy * W + xx);
+        const int c = c0 + warp;
+        const bool have = warp < nvalid;
+        const float* src = srcA;
+        if (have) src = c < ca ? srcA + ((size_t)b * ca + c) * plane : srcB + ((size_t)b * cb + (c - ca)) * plane;
+        const uint32_t sdst = tc::smem_u32(&s_in_all[buf][warp * 10 * C_HS]);
+#pragma unroll
+        for (int i = 0; i < 11; ++i) {
+            const int e = lane + 32 * i;
+            if (e < 340) {
+                const bool ok = have && goff[i] >= 0;
+                tc::cp_async4(sdst + 4 * (e + 2 * (e / 34)), ok ? src + goff[i] : src, ok);  // (e / 34) * 36 + e % 34
             }
-            s_in[(k * 10 + rr) * C_HS + cc] = v;
         }
-        {
-            const float4* wsrc = reinterpret_cast<const float4*>(wl + (size_t)c0 * 9 * 32);
-            float4* wdst = reinterpret_cast<float4*>(s_w);
-            const int n4 = nvalid * 9 * 32 / 4;
-            for (int i = t; i < n4; i += 256) wdst[i] = __ldg(wsrc + i);
+        const float* wsrc = wl + (size_t)c0 * 9 * 32;
+        const uint32_t wdst = tc::smem_u32(&s_w_all[buf][0]);
+        const int n4 = nvalid * 9 * 32 / 4;
+        for (int i = t; i < n4; i += 256) tc::cp_async16(wdst + 16 * i, wsrc + 4 * i, true);
+        tc::cp_async_commit();
+    };
+
+    stage(0, 0);
+    int it = 0;
+    for (int c0 = 0; c0 < cin; c0 += C_CS, ++it) {
+        const int nvalid = min(C_CS, cin - c0);
+        if (c0 + C_CS < cin) {
+            stage(c0 + C_CS, (it + 1) & 1);  // its buffer was released by the barrier that ended chunk it - 1
+            tc::cp_async_wait<1>();
+        } else {
+            tc::cp_async_wait<0>();
         }
         __syncthreads();
+        const float* s_in = s_in_all[it & 1];
+        const float* s_w = s_w_all[it & 1];
         if (active) {
 #pragma unroll 2
             for (int k = 0; k < nvalid; ++k) {
@@ -121,6 +145,7 @@ dce_conv_f32_kernel(const float* __restrict__ srcA, int ca, const float* __restr
                 }
             }
         }
+        __syncthreads();  // this chunk's buffer is free for the stage issued two iterations on
     }
 
     const int yy = y0 + r, xx = x0 + c4;
