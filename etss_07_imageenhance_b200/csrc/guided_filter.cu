@@ -11,7 +11,7 @@
 // running prefixes, no prefix plane stored | row pass: cumsum(3) of a row in shared memory, diff_y, and the stage's
 // arithmetic (A, b / the output) | the same three for A, b.  ~80 B per plane pixel instead of the ~250 B of the first
 // version (B200DCE_GF_FUSED=0: column scan, row-scan totals, row scan, A / b, ... as separate HBM round trips; kept
-// for A/B, bit-identical).  16 x 1080p: 2.6 ms (was 7.2), one frame 0.23 ms (was 0.56).
+// for A/B, bit-identical).  16 x 1080p: 2.1 ms (was 7.2), one frame 0.17 ms (was 0.56).
 #include <math.h>
 #include <stdlib.h>
 
@@ -249,10 +249,116 @@ __global__ void __launch_bounds__(256) gfl_coldiff_kernel(const float* __restric
     }
 }
 
+// The same pass for the window radii that occur (GCENet: radius 3 -> r = 1), with ONE running prefix: the rounded prefix
+// of row h + r is the one row h + 2r + 1 subtracts, so the last 2r + 1 rounded prefixes stay in a register ring (static
+// indices: the row loop is unrolled over whole turns of the ring) -- half the loads, additions and fp32 <-> fp64
+// conversions (16 lanes per SM) of the two-prefix form above; the same values.
+template <int MODE, int R>
+__global__ void __launch_bounds__(256) gfl_coldiff_ring_kernel(const float* __restrict__ s0, const float* __restrict__ s1,
+                                                               float* __restrict__ out, const double* __restrict__ tot,
+                                                               int C, int Cx, int H, int W, size_t map_stride) {
+    constexpr int NM = MODE == 0 ? 4 : 2;
+    constexpr int N = 2 * R + 1;                 // ring entries
+    constexpr int U = N >= 7 ? 1 : (N == 5 ? 2 : 3);  // ring turns per loop trip (7 .. 10 rows of loads in flight)
+    const int w = blockIdx.x * 256 + threadIdx.x;
+    if (w >= W) return;
+    const int pl = blockIdx.y, ch = blockIdx.z, planes = gridDim.y, nch = gridDim.z;
+    const size_t hw = (size_t)H * W;
+    const int px = MODE == 0 ? (pl / C) * Cx + (Cx == 1 ? 0 : pl % C) : pl;
+    const float* a = s0 + (size_t)px * hw + w;
+    const float* b = s1 + (size_t)pl * hw + w;
+    float* o = out + (size_t)pl * hw + w;
+    double base[NM], d[NM];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) base[m] = 0.0;
+    for (int c = 0; c < ch; ++c)
+#pragma unroll
+        for (int m = 0; m < NM; ++m) base[m] += tot[(((size_t)m * planes + pl) * nch + c) * W + w];
+    auto maps = [&](float av, float bv, float (&v)[NM]) {
+        v[0] = av, v[1] = bv;
+        if (MODE == 0) v[2 % NM] = __fmul_rn(av, bv), v[3 % NM] = __fmul_rn(av, av);
+    };
+    const int h0 = ch * GFL_CH, h1 = min(H, h0 + GFL_CH);
+    // ring[m][s] = rounded prefix through row h0 - R - 1 + s (slots of rows < 0 are never read)
+    float ring[NM][N];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) d[m] = base[m];
+#pragma unroll
+    for (int s2 = R; s2 >= 0; --s2) {  // downwards from the chunk base: P[j - 1] = P[j] - t[j], exact
+        const int j = h0 - R - 1 + s2;
+        float v[NM];
+        maps(a[(size_t)max(j, 0) * W], b[(size_t)max(j, 0) * W], v);
+#pragma unroll
+        for (int m = 0; m < NM; ++m) {
+            ring[m][s2] = (float)d[m];
+            if (j >= 0) d[m] -= (double)v[m];
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < NM; ++m) d[m] = base[m];
+#pragma unroll
+    for (int s2 = R + 1; s2 < N; ++s2) {  // upwards: rows h0 .. h0 + R - 1 (the prefix stops growing at row H - 1)
+        const int j = h0 - R - 1 + s2;
+        float v[NM];
+        maps(a[(size_t)min(j, H - 1) * W], b[(size_t)min(j, H - 1) * W], v);
+#pragma unroll
+        for (int m = 0; m < NM; ++m) {
+            if (j < H) d[m] += (double)v[m];
+            ring[m][s2] = (float)d[m];
+        }
+    }
+    for (int h = h0; h < h1; h += N * U) {
+        float la[N * U], lb[N * U];
+#pragma unroll
+        for (int k = 0; k < N * U; ++k) {  // rows past the end are read clamped and not added
+            const size_t lo = (size_t)min(h + k + R, H - 1) * W;
+            la[k] = a[lo], lb[k] = b[lo];
+        }
+#pragma unroll
+        for (int k = 0; k < N * U; ++k) {
+            const int i = h + k;
+            if (i >= h1) break;
+            float v[NM];
+            maps(la[k], lb[k], v);
+            const bool add_lead = i + R < H, has_lo = i - R - 1 >= 0;
+#pragma unroll
+            for (int m = 0; m < NM; ++m) {
+                if (add_lead) d[m] += (double)v[m];
+                const float hi = (float)d[m], lo = ring[m][k % N];
+                ring[m][k % N] = hi;
+                // box_filter.py:26-45: rows <= r take the prefix itself
+                o[m * map_stride + (size_t)i * W] = has_lo ? __fsub_rn(hi, lo) : hi;
+            }
+        }
+    }
+}
+template <int MODE>
+static void gfl_coldiff(const float* s0, const float* s1, float* out, const double* tot, int C, int Cx, int H, int W,
+                        int r, size_t map_stride, dim3 grid, cudaStream_t s) {
+    switch (r) {
+        case 1: gfl_coldiff_ring_kernel<MODE, 1><<<grid, 256, 0, s>>>(s0, s1, out, tot, C, Cx, H, W, map_stride); break;
+        case 2: gfl_coldiff_ring_kernel<MODE, 2><<<grid, 256, 0, s>>>(s0, s1, out, tot, C, Cx, H, W, map_stride); break;
+        case 3: gfl_coldiff_ring_kernel<MODE, 3><<<grid, 256, 0, s>>>(s0, s1, out, tot, C, Cx, H, W, map_stride); break;
+        case 4: gfl_coldiff_ring_kernel<MODE, 4><<<grid, 256, 0, s>>>(s0, s1, out, tot, C, Cx, H, W, map_stride); break;
+        default: gfl_coldiff_kernel<MODE><<<grid, 256, 0, s>>>(s0, s1, out, tot, C, Cx, H, W, r, map_stride);
+    }
+}
+
 // Row pass: one CTA per (image row, plane) runs cumsum(3) of the row's D1 values -- a lane sums its run of E contiguous
 // elements in double, a shuffle scan and eight warp totals give every run its exact base, the rounded prefixes go to
 // shared memory -- then takes diff_y from there and finishes the stage: MODE 0: the four window sums -> A, b;
 // MODE 1: box(A), box(b), x -> out.  No totals pass, no prefix plane in HBM.  grid (H, planes); 8 * 32 * E >= W
+// (tried: 512 threads with runs of 4 and every element converted to double once -- 0.90 instead of 0.71 ms)
+// RN(x / n) for a window count n (an integer <= 4096), rn = RN(1 / n): q = RN(x rn), the exact remainder x - n q by
+// FMA, one correction.  q + rem rn differs from x / n by < 2^-47 relative while x / n stays >= 2^-25 / n away from every
+// rounding boundary (x has 24 bits; n times a 25-bit midpoint never has), so the result is the IEEE quotient --
+// 3 instructions instead of the ~11 of the general division (reciprocal, range check, slow-path branch).  Tiny
+// dividends (the remainder would be subnormal) take the general path.
+__device__ __forceinline__ float gfl_div_count(float x, float n, float rn) {
+    if (fabsf(x) < 1e-25f) return __fdiv_rn(x, n);
+    const float q = __fmul_rn(x, rn);
+    return __fmaf_rn(__fmaf_rn(-q, n, x), rn, q);
+}
 __device__ __forceinline__ double gfl_shfl_up(double v, int o) {
     return __hiloint2double(__shfl_up_sync(0xffffffffu, __double2hiint(v), o),
                             __shfl_up_sync(0xffffffffu, __double2loint(v), o));
@@ -318,20 +424,29 @@ __global__ void __launch_bounds__(256) gfl_rowbox_kernel(const float* __restrict
     }
     __syncthreads();
     const long long hw = (long long)H * W;
+    const float nh = (float)(min(h + r, H - 1) - max(h - r, 0) + 1), n_in = nh * (float)(2 * r + 1);  // exact small integers
+    const float rn_in = __frcp_rn(n_in);
     for (int w = threadIdx.x; w < W; w += 256) {
-        const float n = gfl_count(h, w, H, W, r);
+        const bool inner = w > r && w < W - r;  // the window is whole and both prefixes exist
+        float n = n_in, rn = rn_in;
         float bx[NM];
+        if (inner) {
 #pragma unroll
-        for (int m = 0; m < NM; ++m) bx[m] = gfl_diff(srow + m * Wp, w, W, r, 1);
+            for (int m = 0; m < NM; ++m) bx[m] = __fsub_rn(srow[m * Wp + w + r], srow[m * Wp + w - r - 1]);
+        } else {
+            n = gfl_count(h, w, H, W, r), rn = __frcp_rn(n);
+#pragma unroll
+            for (int m = 0; m < NM; ++m) bx[m] = gfl_diff(srow + m * Wp, w, W, r, 1);
+        }
         if (MODE == 0) {
-            const float mean_x = __fdiv_rn(bx[0], n), mean_y = __fdiv_rn(bx[1], n);
-            const float cov = __fsub_rn(__fdiv_rn(bx[2 % NM], n), __fmul_rn(mean_x, mean_y));
-            const float var = __fsub_rn(__fdiv_rn(bx[3 % NM], n), __fmul_rn(mean_x, mean_x));
+            const float mean_x = gfl_div_count(bx[0], n, rn), mean_y = gfl_div_count(bx[1], n, rn);
+            const float cov = __fsub_rn(gfl_div_count(bx[2 % NM], n, rn), __fmul_rn(mean_x, mean_y));
+            const float var = __fsub_rn(gfl_div_count(bx[3 % NM], n, rn), __fmul_rn(mean_x, mean_x));
             const float a = __fdiv_rn(cov, __fadd_rn(var, eps));
             o0[row + w] = a;
             o1[row + w] = __fsub_rn(mean_y, __fmul_rn(a, mean_x));
         } else {
-            const float ma = __fdiv_rn(bx[0], n), mb = __fdiv_rn(bx[1], n);
+            const float ma = gfl_div_count(bx[0], n, rn), mb = gfl_div_count(bx[1], n, rn);
             const long long px = (long long)(pl / C) * Cx + (Cx == 1 ? 0 : pl % C);
             o0[row + w] = __fadd_rn(__fmul_rn(ma, x[px * hw + (long long)h * W + w]), mb);
         }
@@ -397,10 +512,10 @@ extern "C" int b200_guided_filter(const float* x, const float* y, float* out, in
     const char* fused = getenv("B200DCE_GF_FUSED");
     if (!fused || fused[0] != '0') {  // four passes + two totals passes; (grid.x = H, grid.y = planes)
         gfl_colscan_kernel<0, true><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, plane_set);
-        gfl_coldiff_kernel<0><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, r, plane_set);
+        gfl_coldiff<0>(x, y, p1, tot, C, Cx, H, W, r, plane_set, cgrid, s);
         gfl_rowbox<0>(p1, A, Bc, nullptr, planes, C, Cx, H, W, r, eps, plane_set, s);
         gfl_colscan_kernel<1, true><<<cgrid, 256, 0, s>>>(A, Bc, p1, tot, C, C, H, W, plane_set);
-        gfl_coldiff_kernel<1><<<cgrid, 256, 0, s>>>(A, Bc, p1, tot, C, C, H, W, r, plane_set);
+        gfl_coldiff<1>(A, Bc, p1, tot, C, C, H, W, r, plane_set, cgrid, s);
         gfl_rowbox<1>(p1, out, nullptr, x, planes, C, Cx, H, W, r, eps, plane_set, s);
         return launch_status();
     }
