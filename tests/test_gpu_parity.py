@@ -792,6 +792,21 @@ def test_guided_filter_shapes_vs_oracle(cuda_dev, B, C, Cx, H, W, radius):
     _gf_close(out, ref, "guided_filter")
 
 
+@pytest.mark.parametrize("B,C,Cx,H,W,radius", [(1, 3, 3, 300, 644, 3), (2, 2, 1, 90, 1022, 5), (1, 1, 1, 75, 2500, 9),
+                                               (1, 1, 1, 60, 4096, 21), (2, 3, 3, 33, 40, 7)])
+def test_guided_filter_fused_passes_are_bit_identical(cuda_dev, monkeypatch, B, C, Cx, H, W, radius):
+    """The four-pass form (running-prefix column pass, register ring for r <= 4, shared-memory row pass, short exact
+    division by the window count) against the first six-pass form (B200DCE_GF_FUSED=0): the same bits."""
+    g = torch.Generator().manual_seed(H * 7 + W)
+    x = torch.rand(B, Cx, H, W, generator=g).to(cuda_dev)
+    y = (torch.rand(B, C, H, W, generator=g) * 1.5 - 0.25).to(cuda_dev)
+    monkeypatch.setenv("B200DCE_GF_FUSED", "0")
+    ref = torch.ops.b200dce.guided_filter(x, y, radius, 1e-4)
+    monkeypatch.setenv("B200DCE_GF_FUSED", "1")
+    out = torch.ops.b200dce.guided_filter(x, y, radius, 1e-4)
+    assert torch.equal(out, ref)
+
+
 def test_guided_filter_rejects_what_the_reference_asserts(cuda_dev):
     x = torch.rand(1, 3, 9, 300, device=cuda_dev)
     with pytest.raises(ValueError, match="2 \\* radius"):   # guided_filter.py:126
