@@ -793,7 +793,7 @@ def test_guided_filter_shapes_vs_oracle(cuda_dev, B, C, Cx, H, W, radius):
 
 
 @pytest.mark.parametrize("B,C,Cx,H,W,radius", [(1, 3, 3, 300, 644, 3), (2, 2, 1, 90, 1022, 5), (1, 1, 1, 75, 2500, 9),
-                                               (1, 1, 1, 60, 4096, 21), (2, 3, 3, 33, 40, 7)])
+                                               (1, 1, 1, 60, 4096, 21), (2, 3, 3, 33, 40, 7), (1, 1, 1, 4096, 4096, 3)])
 def test_guided_filter_fused_passes_are_bit_identical(cuda_dev, monkeypatch, B, C, Cx, H, W, radius):
     """The four-pass form (running-prefix column pass, register ring for r <= 4, shared-memory row pass, short exact
     division by the window count) against the first six-pass form (B200DCE_GF_FUSED=0): the same bits."""
