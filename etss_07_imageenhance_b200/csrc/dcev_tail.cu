@@ -10,10 +10,12 @@
 //   box_filter(t) = diff_y(diff_x(t.cumsum(2)).cumsum(3)): ATen's CPU cumsum accumulates fp32 input in DOUBLE and
 //   rounds every prefix to fp32; the window sums are differences of those rounded prefixes (not exact window sums).
 //   Sums of <= 2^11 fp32 values >= 2^-19 are exact in double in any order, so the prefixes here equal ATen's.
-// Everything is HBM-bound streaming except the S x S coefficient stage (256 x 256 per frame: microseconds).
+// Everything is HBM-bound streaming except the S x S coefficient stage (256 x 256 per frame: three small launches of
+// guided_filter.cu, ~30 us for 16 frames).
 #include <math.h>
 
 #include "common.cuh"
+#include "guided_filter.cuh"
 
 namespace b200 {
 
@@ -22,102 +24,8 @@ constexpr int GF_R = 1;  // ZeroDCEV.filter_up(radius=1)
 
 __host__ __device__ inline size_t gf_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// diff_x / diff_y of box_filter.py on a prefix array `p` with stride `st`: window [i - r, i + r] clipped to the ends
-__device__ __forceinline__ float gf_diff(const float* p, int i, int n, int st) {
-    if (i <= GF_R) return p[(size_t)(i + GF_R) * st];
-    const float lo = p[(size_t)(i - GF_R - 1) * st];
-    const float hi = i < n - GF_R ? p[(size_t)(i + GF_R) * st] : p[(size_t)(n - 1) * st];
-    return __fsub_rn(hi, lo);
-}
-
-// Prefix planes of one of the four maps m (x, y, x*y, x*x) of one frame; grid (B, 4), 256 threads:
-//   phase 1 (thread = column, coalesced over the columns): P1 = cumsum down the rows
-//   phase 2 (thread = row): P2 = cumsum along the row of diff_x(P1); the warp brings 32 x 32 blocks of diff_x(P1)
-//           through shared memory (coalesced 128-byte rows in, conflict-free scan, coalesced rows out)
-__global__ void __launch_bounds__(256) dcev_gf_prefix_kernel(const float* __restrict__ x_lr, const float* __restrict__ y_lr,
-                                                             float* __restrict__ scratch, int S) {
-    __shared__ float tile[8][32][33];
-    const int f = blockIdx.x, m = blockIdx.y;
-    const size_t ss = (size_t)S * S;
-    const float* x = x_lr + f * ss;
-    const float* y = y_lr + f * ss;
-    float* p1 = scratch + ((size_t)f * 8 + m) * ss;
-    float* p2 = scratch + ((size_t)f * 8 + 4 + m) * ss;
-    auto value = [&](size_t o) {
-        const float xv = x[o];
-        if (m == 0) return xv;
-        if (m == 3) return __fmul_rn(xv, xv);
-        const float yv = y[o];
-        return m == 1 ? yv : __fmul_rn(xv, yv);
-    };
-    for (int w = threadIdx.x; w < S; w += blockDim.x) {
-        double acc = 0.0;
-        int h = 0;
-        for (; h + 8 <= S; h += 8) {  // eight independent loads in flight, the adds stay in order
-            float v[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = value((size_t)(h + k) * S + w);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                acc += (double)v[k];
-                p1[(size_t)(h + k) * S + w] = (float)acc;
-            }
-        }
-        for (; h < S; ++h) {
-            acc += (double)value((size_t)h * S + w);
-            p1[(size_t)h * S + w] = (float)acc;
-        }
-    }
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int r0 = warp * 32; r0 < S; r0 += 256) {  // this warp's 32 rows; lane = row in the scan, column in the copies
-        double acc = 0.0;
-        for (int c0 = 0; c0 < S; c0 += 32) {
-            const int w = c0 + lane;
-#pragma unroll 8
-            for (int r = 0; r < 32; ++r)
-                tile[warp][r][lane] = (r0 + r < S && w < S) ? gf_diff(p1 + w, r0 + r, S, S) : 0.f;
-            __syncwarp();
-            float o[32];
-#pragma unroll
-            for (int k = 0; k < 32; ++k) {
-                acc += (double)tile[warp][lane][k];
-                o[k] = (float)acc;
-            }
-            __syncwarp();
-#pragma unroll
-            for (int k = 0; k < 32; ++k) tile[warp][lane][k] = o[k];
-            __syncwarp();
-#pragma unroll 8
-            for (int r = 0; r < 32; ++r)
-                if (r0 + r < S && w < S) p2[(size_t)(r0 + r) * S + w] = tile[warp][r][lane];
-            __syncwarp();
-        }
-    }
-}
-
-// window sums = diff_y(P2), then the linear model of every window: A = cov / (var + eps), b = mean_y - A mean_x
-__global__ void __launch_bounds__(256) dcev_gf_ab_kernel(const float* __restrict__ scratch, float* __restrict__ A,
-                                                         float* __restrict__ Bc, int S, long long total) {
-    const size_t ss = (size_t)S * S;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int f = (int)(i / (long long)ss);
-        const size_t j = (size_t)(i - (long long)f * (long long)ss);
-        const int h = (int)(j / S), w = (int)(j - (size_t)h * S);
-        const int nh = min(h + GF_R, S - 1) - max(h - GF_R, 0) + 1, nw = min(w + GF_R, S - 1) - max(w - GF_R, 0) + 1;
-        const float n = (float)(nh * nw);  // box_filter of ones: exact
-        const float* p2 = scratch + ((size_t)f * 8 + 4) * ss;
-        float b[4];
-#pragma unroll
-        for (int m = 0; m < 4; ++m) b[m] = gf_diff(p2 + m * ss + (size_t)h * S, w, S, 1);
-        const float mean_x = __fdiv_rn(b[0], n), mean_y = __fdiv_rn(b[1], n);
-        const float cov = __fsub_rn(__fdiv_rn(b[2], n), __fmul_rn(mean_x, mean_y));
-        const float var = __fsub_rn(__fdiv_rn(b[3], n), __fmul_rn(mean_x, mean_x));
-        const float a = __fdiv_rn(cov, __fadd_rn(var, GF_EPS));
-        A[i] = a;
-        Bc[i] = __fsub_rn(mean_y, __fmul_rn(a, mean_x));
-    }
-}
+// The S x S coefficient stage (box filters of x, y, x*y, x*x as differences of rounded double-accumulated running sums,
+// then A = cov / (var + eps), b = mean_y - A mean_x) is guided_filter.cu's first stage: gfl_coefficients().
 
 // ---- bicubic upsample (ATen upsample_bicubic2d, align_corners=True, A = -0.75) -------------------------------------
 __device__ __forceinline__ float cubic1(float x) {  // |x| <= 1
@@ -247,18 +155,32 @@ __global__ void __launch_bounds__(256) dcev_gf_apply_kernel(const float* __restr
     if ((threadIdx.x & 31) == 0 && local_max > 0.f) atomicMax(fmax + f, __float_as_uint(local_max));
 }
 
+// enhanced /= the frame's maximum (IEEE division, as torch's); grid (blocks, B), 128-bit accesses when the frame allows
 __global__ void __launch_bounds__(256) dcev_normalise_kernel(float* __restrict__ out, const unsigned int* __restrict__ fmax,
-                                                             long long per_frame, long long total) {
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
-        out[i] = __fdiv_rn(out[i], __uint_as_float(fmax[i / per_frame]));
+                                                             long long per_frame) {
+    const float m = __uint_as_float(fmax[blockIdx.y]);
+    float* o = out + (long long)blockIdx.y * per_frame;
+    const long long step = (long long)gridDim.x * blockDim.x, i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if ((per_frame & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0) {
+        float4* o4 = reinterpret_cast<float4*>(o);
+        for (long long i = i0; i < (per_frame >> 2); i += step) {
+            float4 v = o4[i];
+            v.x = __fdiv_rn(v.x, m), v.y = __fdiv_rn(v.y, m), v.z = __fdiv_rn(v.z, m), v.w = __fdiv_rn(v.w, m);
+            o4[i] = v;
+        }
+    } else {
+        for (long long i = i0; i < per_frame; i += step) o[i] = __fdiv_rn(o[i], m);
+    }
 }
 
 }  // namespace b200
 
-// scratch: 8 S x S fp32 prefix planes + A + b per frame, one max word per frame
+// scratch: the four difference maps of the coefficient stage + A + b (B x S x S fp32 each), its chunk totals, one max word
+// per frame
 extern "C" size_t b200_dcev_tail_workspace_bytes(int B, int S) {
     if (B <= 0 || S <= 0) return 0;
-    return b200::gf_align_up((size_t)B * 10 * S * S * sizeof(float), 256) + b200::gf_align_up((size_t)B * 4, 256);
+    return 6 * b200::gf_align_up((size_t)B * S * S * sizeof(float), 256) +
+           b200::gf_align_up(b200::gfl_tot_doubles(B, S, S) * sizeof(double), 256) + b200::gf_align_up((size_t)B * 4, 256);
 }
 
 extern "C" int b200_dcev_tail(const float* image_rgb, const float* image_v, const float* image_v_lr,
@@ -269,31 +191,27 @@ extern "C" int b200_dcev_tail(const float* image_rgb, const float* image_v, cons
         return B200_ERR_NULL;
     if (B <= 0 || H <= 0 || W <= 0 || S <= 0) return B200_ERR_BAD_SHAPE;
     // FastGuidedFilter asserts h, w > 2 * radius + 1 (guided_filter.py:182)
-    if (S <= 2 * GF_R + 1 || B > 65535) return B200_ERR_UNSUPPORTED;
+    if (S <= 2 * GF_R + 1 || S > 4096 || B > 65535) return B200_ERR_UNSUPPORTED;
     if (workspace_bytes < b200_dcev_tail_workspace_bytes(B, S)) return B200_ERR_WORKSPACE;
     if ((reinterpret_cast<uintptr_t>(workspace) & 15u) != 0) return B200_ERR_MISALIGNED;
     cudaStream_t s = (cudaStream_t)stream;
-    const size_t ss = (size_t)S * S;
-    float* scratch = (float*)workspace;
-    float* A = scratch + (size_t)B * 8 * ss;
-    float* Bc = A + (size_t)B * ss;
-    unsigned int* fmax = (unsigned int*)((char*)workspace + gf_align_up((size_t)B * 10 * ss * sizeof(float), 256));
+    const size_t plane_set = gf_align_up((size_t)B * S * S * sizeof(float), 256) / sizeof(float);
+    float* d1 = (float*)workspace;  // 4 maps
+    float* A = d1 + 4 * plane_set;
+    float* Bc = A + plane_set;
+    double* tot = (double*)(Bc + plane_set);
+    unsigned int* fmax = (unsigned int*)((char*)tot + gf_align_up(gfl_tot_doubles(B, S, S) * sizeof(double), 256));
     if (cudaMemsetAsync(fmax, 0, (size_t)B * 4, s) != cudaSuccess) return B200_ERR_LAUNCH;
-    dcev_gf_prefix_kernel<<<dim3(B, 4), 256, 0, s>>>(image_v_lr, image_v_fixed_lr, scratch, S);
-    {
-        const long long tot = (long long)B * (long long)ss;
-        long long blk = (tot + 255) / 256;
-        if (blk > B200_NUM_SMS * 16) blk = B200_NUM_SMS * 16;
-        dcev_gf_ab_kernel<<<(unsigned)blk, 256, 0, s>>>(scratch, A, Bc, S, tot);
-    }
+    if (int rc = gfl_coefficients(image_v_lr, image_v_fixed_lr, A, Bc, B, S, S, GF_R, GF_EPS, d1, plane_set, tot, s)) return rc;
     // ATen area_pixel_compute_scale<float>(in, out, align_corners=true) = (in - 1) / (out - 1), 0 when out == 1
     const float sh = H > 1 ? (float)(S - 1) / (float)(H - 1) : 0.f;
     const float sw = W > 1 ? (float)(S - 1) / (float)(W - 1) : 0.f;
     dim3 grid((W + 255) / 256, (H + GF_ROWS - 1) / GF_ROWS, B);
     dcev_gf_apply_kernel<<<grid, 256, 0, s>>>(image_rgb, image_v, A, Bc, image_v_fixed, enhanced, fmax, H, W, S, sh, sw);
-    const long long per = 3LL * H * W, total = per * B;
-    long long blocks = (total + 255) / 256;
-    if (blocks > B200_NUM_SMS * 16) blocks = B200_NUM_SMS * 16;
-    dcev_normalise_kernel<<<(unsigned)blocks, 256, 0, s>>>(enhanced, fmax, per, total);
+    const long long per = 3LL * H * W;
+    long long blocks = (per / 4 + 255) / 256;
+    if (blocks > B200_NUM_SMS * 2) blocks = B200_NUM_SMS * 2;
+    if (blocks < 1) blocks = 1;
+    dcev_normalise_kernel<<<dim3((unsigned)blocks, B), 256, 0, s>>>(enhanced, fmax, per);
     return launch_status();
 }

@@ -16,6 +16,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "guided_filter.cuh"
 
 namespace b200 {
 
@@ -471,6 +472,18 @@ static void gfl_rowbox(const float* d1, float* o0, float* o1, const float* x, in
         gfl_launch_rowbox<MODE, 8>(d1, o0, o1, x, planes, C, Cx, H, W, r, eps, map_stride, s);
     else
         gfl_launch_rowbox<MODE, 16>(d1, o0, o1, x, planes, C, Cx, H, W, r, eps, map_stride, s);
+}
+
+// The filter's first stage alone -- A, b of every window of (x, y), planes of H x W -- for FastGuidedFilter's
+// low-resolution stage (dcev_tail.cu): d1 = 4 maps of `map_stride` floats, tot = gfl_tot_doubles() doubles.
+size_t gfl_tot_doubles(int planes, int H, int W) { return 4 * (size_t)planes * ((H + GFL_CH - 1) / GFL_CH) * W; }
+int gfl_coefficients(const float* x, const float* y, float* A, float* Bc, int planes, int H, int W, int r, float eps,
+                     float* d1, size_t map_stride, double* tot, cudaStream_t s) {
+    const dim3 cgrid((W + 255) / 256, planes, (H + GFL_CH - 1) / GFL_CH);
+    gfl_colscan_kernel<0, true><<<cgrid, 256, 0, s>>>(x, y, d1, tot, 1, 1, H, W, map_stride);
+    gfl_coldiff<0>(x, y, d1, tot, 1, 1, H, W, r, map_stride, cgrid, s);
+    gfl_rowbox<0>(d1, A, Bc, nullptr, planes, 1, 1, H, W, r, eps, map_stride, s);
+    return launch_status();
 }
 
 }  // namespace b200
