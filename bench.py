@@ -271,6 +271,26 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
         return {"workload": "C1 shape on GPU: zero_dce++ sf=1 1x3x512x512", "ms": ms,
                 "mp_s": 512 * 512 / 1e6 / (ms / 1e3)}
 
+    def f3_dcev():
+        m = P.ZeroDCEV(down_size=256).to(dev)
+        x = synth_frames_gpu(16, H, W, SEED + 5, dev)
+        ms = time_steps(lambda: m({"image": x}), 10, 3, dev)
+        return {"workload": "f3 ZeroDCE-V forward 16x3x1080x1920 (down_size 256: DCE-Net on 256x256, guided-filter "
+                            "upsample, HSV recomposition)", "ms": ms, "mp_s": x.numel() / 3 / 1e6 / (ms / 1e3)}
+
+    def f3_gce():
+        import torch
+        x = synth_frames_gpu(16, H, W, SEED + 6, dev)
+        adj = torch.rand(x.shape, device=dev) * 2 - 1
+        enh = torch.ops.b200dce.gce_curve(x, adj, 15, 2.6, False)[0]
+        ms_c = time_steps(lambda: torch.ops.b200dce.gce_curve(x, adj, 15, 2.6, False), 10, 3, dev)
+        ms_g = time_steps(lambda: torch.ops.b200dce.guided_filter(x, enh, 3, 1e-4), 10, 3, dev)
+        px = x.numel() / 3
+        return {"workload": "f3 GCENet post-network path 16x3x1080x1920: curve loop with the brightness attention map "
+                            "(15 iterations, gamma 2.6), then GuidedFilter(radius 3, eps 1e-4)",
+                "curve_ms": ms_c, "guided_filter_ms": ms_g, "curve_hbm_frac_36Bpx": px * 36 / (ms_c / 1e3) / 1e9 / hbm_peak,
+                "guided_filter_gbs_80B_per_plane_px": 3 * px * 80 / (ms_g / 1e3) / 1e9}
+
     guarded("c3_dcepp_4k_b8", c3)
     guarded("c3_dcepp_4k_b8_no_adjust", c3_noadj)
     guarded("c4_sci_1080p_b16", c4)
@@ -281,6 +301,8 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
     guarded("c2_dce_fp32_exact_1080p_b2", c2("fp32_exact", 2, 3))  # CUDA-core fp32 products
     guarded("c2_dce_bf16x3_mma_sync_1080p_b16", c2("bf16x3_mma", 16, 3))  # round-1 kernels, for the A/B
     guarded("c1_dcepp_sf1_512", sf1)
+    guarded("f3_dcev_1080p_b16", f3_dcev)
+    guarded("f3_gcenet_post_1080p_b16", f3_gce)
     return out
 
 
