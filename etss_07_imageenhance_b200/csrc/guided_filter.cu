@@ -11,7 +11,7 @@
 // running prefixes, no prefix plane stored | row pass: cumsum(3) of a row in shared memory, diff_y, and the stage's
 // arithmetic (A, b / the output) | the same three for A, b.  ~80 B per plane pixel instead of the ~250 B of the first
 // version (B200DCE_GF_FUSED=0: column scan, row-scan totals, row scan, A / b, ... as separate HBM round trips; kept
-// for A/B, bit-identical).  16 x 1080p: 2.1 ms (was 7.2), one frame 0.17 ms (was 0.56).
+// for A/B, bit-identical).  16 x 1080p: 1.9 ms (was 7.2), one frame 0.17 ms (was 0.56).
 #include <math.h>
 #include <stdlib.h>
 
@@ -68,8 +68,9 @@ __global__ void __launch_bounds__(256) gfl_colscan_kernel(const float* __restric
             if (!TOTALS) o[m * map_stride + off] = (float)acc[m];
         }
     };
-    const int h1 = min(H, (ch + 1) * GFL_CH);
-    int h = ch * GFL_CH;
+    const int chrows = gridDim.z == 1 ? H : GFL_CH;  // one chunk = the whole column
+    const int h1 = min(H, (ch + 1) * chrows);
+    int h = ch * chrows;
     for (; h + 8 <= h1; h += 8) {
         float av[8], bv[8];
 #pragma unroll
@@ -211,7 +212,8 @@ __global__ void __launch_bounds__(256) gfl_coldiff_kernel(const float* __restric
         v[0] = av, v[1] = bv;
         if (MODE == 0) v[2 % NM] = __fmul_rn(av, bv), v[3 % NM] = __fmul_rn(av, av);
     };
-    const int h0 = ch * GFL_CH, h1 = min(H, h0 + GFL_CH);
+    const int chrows = gridDim.z == 1 ? H : GFL_CH;  // one chunk = the whole column
+    const int h0 = ch * chrows, h1 = min(H, h0 + chrows);
     for (int k = h0; k < min(h0 + r, H); ++k) {  // lead = prefix through row h0 + r - 1
         float v[NM];
         maps(a[(size_t)k * W], b[(size_t)k * W], v);
@@ -279,7 +281,8 @@ __global__ void __launch_bounds__(256) gfl_coldiff_ring_kernel(const float* __re
         v[0] = av, v[1] = bv;
         if (MODE == 0) v[2 % NM] = __fmul_rn(av, bv), v[3 % NM] = __fmul_rn(av, av);
     };
-    const int h0 = ch * GFL_CH, h1 = min(H, h0 + GFL_CH);
+    const int chrows = gridDim.z == 1 ? H : GFL_CH;  // one chunk = the whole column
+    const int h0 = ch * chrows, h1 = min(H, h0 + chrows);
     // ring[m][s] = rounded prefix through row h0 - R - 1 + s (slots of rows < 0 are never read)
     float ring[NM][N];
 #pragma unroll
@@ -523,12 +526,16 @@ extern "C" int b200_guided_filter(const float* x, const float* y, float* out, in
     if (eb > B200_NUM_SMS * 32) eb = B200_NUM_SMS * 32;
     const dim3 cgrid((W + 255) / 256, planes, nch);
     const char* fused = getenv("B200DCE_GF_FUSED");
-    if (!fused || fused[0] != '0') {  // four passes + two totals passes; (grid.x = H, grid.y = planes)
-        gfl_colscan_kernel<0, true><<<cgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, plane_set);
-        gfl_coldiff<0>(x, y, p1, tot, C, Cx, H, W, r, plane_set, cgrid, s);
+    if (!fused || fused[0] != '0') {  // four passes (+ two totals passes when the columns are chunked)
+        // enough columns in flight (>= ~400 threads per SM, 18 loads each) to stream HBM without chunking: one chunk per
+        // column, no totals pass (B200DCE_GF_FUSED=2 / 3 force the chunks / one chunk: A/B aid)
+        const bool whole = fused ? fused[0] == '3' : (long long)planes * W >= 60000;  // 3 / 2: force one chunk / chunks
+        const dim3 fgrid = whole ? dim3(cgrid.x, cgrid.y, 1) : cgrid;
+        if (fgrid.z > 1) gfl_colscan_kernel<0, true><<<fgrid, 256, 0, s>>>(x, y, p1, tot, C, Cx, H, W, plane_set);
+        gfl_coldiff<0>(x, y, p1, tot, C, Cx, H, W, r, plane_set, fgrid, s);
         gfl_rowbox<0>(p1, A, Bc, nullptr, planes, C, Cx, H, W, r, eps, plane_set, s);
-        gfl_colscan_kernel<1, true><<<cgrid, 256, 0, s>>>(A, Bc, p1, tot, C, C, H, W, plane_set);
-        gfl_coldiff<1>(A, Bc, p1, tot, C, C, H, W, r, plane_set, cgrid, s);
+        if (fgrid.z > 1) gfl_colscan_kernel<1, true><<<fgrid, 256, 0, s>>>(A, Bc, p1, tot, C, C, H, W, plane_set);
+        gfl_coldiff<1>(A, Bc, p1, tot, C, C, H, W, r, plane_set, fgrid, s);
         gfl_rowbox<1>(p1, out, nullptr, x, planes, C, Cx, H, W, r, eps, plane_set, s);
         return launch_status();
     }

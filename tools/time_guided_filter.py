@@ -32,20 +32,26 @@ import os  # noqa: E402
 enh = torch.ops.b200dce.gce_curve(x, adj, 15, 2.6, False)[0]
 bad = 0
 for (b, c, cx, hh, ww, rad) in [(1, 3, 3, 1080, 1920, 3), (2, 3, 1, 67, 131, 3), (1, 1, 1, 17, 300, 7), (3, 3, 3, 40, 33, 5),
-                                (1, 2, 2, 300, 2500, 9), (1, 1, 1, 100, 4096, 21), (2, 3, 3, 200, 1022, 5)]:
+                                (1, 2, 2, 300, 2500, 9), (1, 1, 1, 100, 4096, 21), (2, 3, 3, 200, 1022, 5), (16, 3, 3, 300, 1920, 3), (8, 3, 1, 1080, 2500, 9)]:
     xs = torch.rand(b, cx, hh, ww, device=dev)
     ys = torch.rand(b, c, hh, ww, device=dev)
     res = []
-    for mode in ("0", "1"):
-        os.environ["B200DCE_GF_FUSED"] = mode
+    for mode in ("0", "2", ""):
+        if mode:
+            os.environ["B200DCE_GF_FUSED"] = mode
+        else:
+            os.environ.pop("B200DCE_GF_FUSED", None)
         res.append(torch.ops.b200dce.guided_filter(xs, ys, rad, 1e-4))
-    eq = torch.equal(res[0], res[1])
+    eq = torch.equal(res[0], res[1]) and torch.equal(res[0], res[2])
     bad += not eq
     print(f"{b}x{c}({cx})x{hh}x{ww} radius {rad}: four passes {'==' if eq else '!='} six passes"
           + ("" if eq else f" (max |d| {(res[0] - res[1]).abs().max().item():.3e})"), flush=True)
-for mode in ("0", "1"):
-    os.environ["B200DCE_GF_FUSED"] = mode
-    print(f"B200DCE_GF_FUSED={mode}: guided_filter {timed(lambda: torch.ops.b200dce.guided_filter(x, enh, 3, 1e-4)):.3f} ms", flush=True)
+for mode in ("0", "2", ""):
+    if mode:
+        os.environ["B200DCE_GF_FUSED"] = mode
+    else:
+        os.environ.pop("B200DCE_GF_FUSED", None)
+    print(f"B200DCE_GF_FUSED={mode or 'unset'}: guided_filter {timed(lambda: torch.ops.b200dce.guided_filter(x, enh, 3, 1e-4)):.3f} ms", flush=True)
 t_c = timed(lambda: torch.ops.b200dce.gce_curve(x, adj, 15, 2.6, False))
 t_g = timed(lambda: torch.ops.b200dce.guided_filter(x, enh, 3, 1e-4))
 px = F * H * W
