@@ -802,9 +802,10 @@ def test_guided_filter_fused_passes_are_bit_identical(cuda_dev, monkeypatch, B, 
     y = (torch.rand(B, C, H, W, generator=g) * 1.5 - 0.25).to(cuda_dev)
     monkeypatch.setenv("B200DCE_GF_FUSED", "0")
     ref = torch.ops.b200dce.guided_filter(x, y, radius, 1e-4)
-    monkeypatch.setenv("B200DCE_GF_FUSED", "1")
-    out = torch.ops.b200dce.guided_filter(x, y, radius, 1e-4)
-    assert torch.equal(out, ref)
+    for mode in ("1", "3"):   # chunked columns with totals passes / one chunk per column (large batches)
+        monkeypatch.setenv("B200DCE_GF_FUSED", mode)
+        out = torch.ops.b200dce.guided_filter(x, y, radius, 1e-4)
+        assert torch.equal(out, ref), mode
 
 
 def test_guided_filter_rejects_what_the_reference_asserts(cuda_dev):
