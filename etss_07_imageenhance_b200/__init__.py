@@ -9,6 +9,7 @@ Public surface (mirrors the reference for this path only):
   torch.ops.b200dce.*            custom ops over the C ABI (ops.py, include/b200dce.h)
   FramePipeline, shard_range     host-fed frame scheduler / multi-GPU frame sharding (sched.py)
   DceppBatchStream               device-resident batch stream: stage 1 of batch i+1 queued behind stage 2 of batch i
+  GraphedForward                 model(datapoint) of one input shape captured into a CUDA graph and replayed
 
 There is no CPU fallback: the kernels live in lib/libb200dce.so (build: `python -m
 etss_07_imageenhance_b200.build`); a missing library or a CPU tensor raises.
@@ -17,7 +18,7 @@ from . import ops  # registers torch.ops.b200dce.*
 from .models import (DSConv2d, DepthwiseSeparableConv2d, SCI_RE, RUAS_RE, ZeroDCE_RE, ZeroDCEV, ZeroDCEpp_RE, ZeroDCELoss,
                      remap_upstream_dcepp_keys)
 from .registry import MODELS, ModelFactory, register_into_mon
-from .sched import DceppBatchStream, FramePipeline, gather_max_ms, gather_objects, shard_range
+from .sched import DceppBatchStream, FramePipeline, GraphedForward, gather_max_ms, gather_objects, shard_range
 
 # Drop-in step: when `mon` imports in this interpreter, the B200 classes replace the reference's entries in
 # mon.MODELS (register(..., replace=True), src/mon/core/factory.py:300-328); without `mon` this is a no-op.
@@ -25,5 +26,5 @@ MON_REGISTERED = register_into_mon()
 
 __version__ = "0.2.0"
 __all__ = ["ops", "MODELS", "ModelFactory", "register_into_mon", "ZeroDCE_RE", "ZeroDCEV", "ZeroDCEpp_RE", "SCI_RE", "RUAS_RE", "DSConv2d",
-           "DepthwiseSeparableConv2d", "ZeroDCELoss", "remap_upstream_dcepp_keys", "FramePipeline", "DceppBatchStream", "shard_range",
+           "DepthwiseSeparableConv2d", "ZeroDCELoss", "remap_upstream_dcepp_keys", "FramePipeline", "DceppBatchStream", "GraphedForward", "shard_range",
            "gather_max_ms", "gather_objects"]

@@ -26,7 +26,7 @@ import torch
 
 from ._lib import PRECISIONS, check, lib
 
-__all__ = ["shard_range", "FramePipeline", "DceppBatchStream", "gather_max_ms", "gather_objects", "gpu_local_cpus",
+__all__ = ["shard_range", "FramePipeline", "DceppBatchStream", "GraphedForward", "gather_max_ms", "gather_objects", "gpu_local_cpus",
            "numa_local", "parse_cpulist"]
 
 
@@ -356,3 +356,55 @@ class DceppBatchStream:
         cur = torch.cuda.current_stream(self.device)
         cur.wait_stream(self.s_net)
         cur.wait_stream(self.s_apply)
+
+
+class GraphedForward:
+    """`model(datapoint)` for one fixed input shape, captured once into a CUDA graph and replayed.
+
+    For a loop that enhances one frame (or a small batch) at a time the forward is a few tens of microseconds of GPU
+    work behind ~100 us of Python / dispatcher time per call (`tools/time_graph.py`: one 1080p Zero-DCE++ frame, eager
+    98 us per call, replay 58 us).  The C layer never allocates, frees or synchronises and launches only on the
+    caller's stream, so the whole call captures; replays reuse the captured buffers:
+
+        g = GraphedForward(model, torch.empty(1, 3, 1080, 1920, device="cuda"))
+        out = g(frame)            # copies `frame` into the static input, replays, returns the static output dict
+
+    The returned tensors are overwritten by the next call (clone what must survive).  The packed weights are read at
+    capture time: call `recapture()` after `load_state_dict` or an in-place parameter edit (checked on every call
+    through the model's parameter key).  Results are bit-identical to the eager call."""
+
+    def __init__(self, model, example: torch.Tensor, warmup: int = 2):
+        if example.device.type != "cuda":
+            raise RuntimeError("GraphedForward needs a CUDA tensor (no CPU fallback)")
+        self.model = model
+        self.image = torch.empty_like(example).contiguous()
+        self.image.copy_(example)
+        self._warmup = int(warmup)
+        self.recapture()
+
+    def _key(self):
+        return tuple((p.data_ptr(), p._version) for p in self.model.parameters())
+
+    def recapture(self) -> None:
+        dev = self.image.device
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, self._warmup)):   # packs the weights, sizes the allocator's pools
+                self.model({"image": self.image})
+        torch.cuda.current_stream(dev).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            self.outputs = self.model({"image": self.image})
+        self._captured_key = self._key()
+
+    def __call__(self, image: Optional[torch.Tensor] = None) -> dict:
+        if self._key() != self._captured_key:
+            self.recapture()
+        if image is not None:
+            if image.shape != self.image.shape or image.dtype != self.image.dtype:
+                raise ValueError(f"GraphedForward was captured for {tuple(self.image.shape)} {self.image.dtype}, "
+                                 f"got {tuple(image.shape)} {image.dtype}")
+            self.image.copy_(image, non_blocking=True)
+        self.graph.replay()
+        return self.outputs

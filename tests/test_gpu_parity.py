@@ -814,3 +814,56 @@ def test_guided_filter_rejects_what_the_reference_asserts(cuda_dev):
         torch.ops.b200dce.guided_filter(x, x, 7, 1e-4)
     with pytest.raises(ValueError):                           # c_x == 1 or c_x == c_y (:124)
         torch.ops.b200dce.guided_filter(x[:, :2].contiguous(), x, 3, 1e-4)
+
+
+# ------------------------------------------------------------------ CUDA graphs (the C layer never allocates or syncs)
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kw,shape", [("zero_dce++_re", {"scale_factor": 12}, (2, 3, 240, 480)),
+                                           ("zero_dce_re", {"precision": "bf16"}, (1, 3, 96, 132)),
+                                           ("zero_dce_re", {"precision": "fp32"}, (1, 3, 96, 132))])
+def test_forward_replays_from_a_cuda_graph(cuda_dev, name, kw, shape):
+    """The forward captured once into a CUDA graph and replayed on new input contents gives the eager call's bits:
+    every launch of the path goes to the caller's stream, nothing allocates, frees or synchronises under the op."""
+    torch.manual_seed(5)
+    m = P.MODELS.build(config={"name": name, **kw}).to(cuda_dev)
+    for p in m.parameters():   # the reference init (N(0, 0.02)) leaves adjust ~ 0: make the curve maps visible
+        p.data.mul_(6.0)
+    x = O.synthetic_lowlight(*shape[:1], *shape[2:], seed=3).to(cuda_dev)
+    side = torch.cuda.Stream(device=cuda_dev)
+    side.wait_stream(torch.cuda.current_stream(cuda_dev))
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            m({"image": x})
+    torch.cuda.current_stream(cuda_dev).wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out = m({"image": x})
+    x2 = O.synthetic_lowlight(*shape[:1], *shape[2:], seed=4).to(cuda_dev)
+    x.copy_(x2)
+    graph.replay()
+    torch.cuda.synchronize(cuda_dev)
+    got = {k: v.clone() for k, v in out.items()}
+    ref = m({"image": x2})
+    assert torch.equal(got["enhanced"], ref["enhanced"]) and torch.equal(got["adjust"], ref["adjust"])
+
+
+@pytest.mark.gpu
+def test_graphed_forward_helper(cuda_dev):
+    """GraphedForward: replays give the eager call's bits, a shape change is refused, new weights re-capture."""
+    m = P.ZeroDCEpp_RE(scale_factor=12).to(cuda_dev)
+    for p in m.parameters():
+        p.data.mul_(6.0)
+    x1 = O.synthetic_lowlight(1, 240, 480, seed=11).to(cuda_dev)
+    x2 = O.synthetic_lowlight(1, 240, 480, seed=12).to(cuda_dev)
+    g = P.GraphedForward(m, x1)
+    for x in (x1, x2, x1):
+        got = {k: v.clone() for k, v in g(x).items()}
+        ref = m({"image": x})
+        assert list(got.keys()) == list(ref.keys())
+        assert all(torch.equal(got[k], ref[k]) for k in ref)
+    with pytest.raises(ValueError, match="captured for"):
+        g(torch.zeros(1, 3, 120, 480, device=cuda_dev))
+    with torch.no_grad():
+        m.e_conv7.pw_conv.weight.mul_(0.5)      # in-place edit: the parameter key changes, the next call re-captures
+    got = g(x2)["enhanced"].clone()
+    assert torch.equal(got, m({"image": x2})["enhanced"])

@@ -270,6 +270,8 @@ def test_forward_contract_errors_on_cpu():
         m({"image": torch.rand(1, 3, 8, 8)})
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         m(datapoint={"image": torch.rand(1, 3, 8, 8)})   # keyword form (core/thop.py:96-97)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        P.GraphedForward(m, torch.rand(1, 3, 24, 24))    # the graph helper does not run on the CPU either
     with pytest.raises(NotImplementedError):
         torch.ops.b200dce.curve_shared(torch.rand(1, 3, 4, 4), torch.rand(1, 3, 4, 4), 8)   # CUDA-only dispatch
     with pytest.raises(NotImplementedError):
