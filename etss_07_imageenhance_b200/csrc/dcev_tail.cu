@@ -95,14 +95,16 @@ __device__ __forceinline__ void recolor(float r, float g, float b, float v_new, 
     }
 }
 
-// Full resolution: image_v_fixed = clip(A_up * v + b_up), the recoloured pixel (not yet divided by the frame maximum)
-// and the frame maximum (non-negative floats order like their bit patterns).  Thread = column, CTA = 256 columns x
+// Full resolution, first pass: image_v_fixed = clip(A_up * v + b_up) and its maximum over the frame (non-negative floats
+// order like their bit patterns).  That maximum IS the maximum of the recoloured frame the reference divides by
+// (zero_dce_v.py:228-229): hsv_to_rgb hands one channel the new V unchanged and the other two V times a factor in
+// [0, 1] (p, q, t above; s and f lie in [0, 1]), so max(r, g, b) == V bit for bit -- the recoloured frame need not be
+// written, read back and rescaled.  Thread = column, CTA = 256 columns x
 // GF_ROWS rows: the column's four x taps are computed once, and the four x-interpolated source rows of A and b are
 // kept while consecutive output rows fall between the same source rows (every ~4 rows change at 256 -> 1080).
 constexpr int GF_ROWS = 32;
-__global__ void __launch_bounds__(256) dcev_gf_apply_kernel(const float* __restrict__ rgb, const float* __restrict__ v,
-                                                            const float* __restrict__ A, const float* __restrict__ Bc,
-                                                            float* __restrict__ v_fixed, float* __restrict__ out,
+__global__ void __launch_bounds__(256) dcev_gf_apply_kernel(const float* __restrict__ v, const float* __restrict__ A,
+                                                            const float* __restrict__ Bc, float* __restrict__ v_fixed,
                                                             unsigned int* __restrict__ fmax, int H, int W, int S,
                                                             float sh, float sw) {
     const int f = blockIdx.z, x = blockIdx.x * 256 + threadIdx.x;
@@ -142,12 +144,7 @@ __global__ void __launch_bounds__(256) dcev_gf_apply_kernel(const float* __restr
             const size_t p = (size_t)y * W + x;
             const float vf = fminf(fmaxf(__fadd_rn(__fmul_rn(ua, v[f * hw + p]), ub), 0.f), 1.f);
             v_fixed[f * hw + p] = vf;
-            float ro, go, bo;
-            recolor(rgb[(f * 3 + 0) * hw + p], rgb[(f * 3 + 1) * hw + p], rgb[(f * 3 + 2) * hw + p], vf, ro, go, bo);
-            out[(f * 3 + 0) * hw + p] = ro;
-            out[(f * 3 + 1) * hw + p] = go;
-            out[(f * 3 + 2) * hw + p] = bo;
-            local_max = fmaxf(local_max, fmaxf(fmaxf(ro, go), bo));
+            local_max = fmaxf(local_max, vf);
         }
     }
 #pragma unroll
@@ -155,21 +152,39 @@ __global__ void __launch_bounds__(256) dcev_gf_apply_kernel(const float* __restr
     if ((threadIdx.x & 31) == 0 && local_max > 0.f) atomicMax(fmax + f, __float_as_uint(local_max));
 }
 
-// enhanced /= the frame's maximum (IEEE division, as torch's); grid (blocks, B), 128-bit accesses when the frame allows
-__global__ void __launch_bounds__(256) dcev_normalise_kernel(float* __restrict__ out, const unsigned int* __restrict__ fmax,
-                                                             long long per_frame) {
-    const float m = __uint_as_float(fmax[blockIdx.y]);
-    float* o = out + (long long)blockIdx.y * per_frame;
+// Second pass: enhanced = hsv_to_rgb(H, S of the input, V = image_v_fixed) / the frame's maximum (IEEE division, as
+// torch's).  grid (blocks, B); four pixels per thread with 128-bit accesses when the frame allows.
+__global__ void __launch_bounds__(256) dcev_recolor_kernel(const float* __restrict__ rgb, const float* __restrict__ v_fixed,
+                                                           float* __restrict__ out, const unsigned int* __restrict__ fmax,
+                                                           long long hw, int vec) {
+    const long long f = blockIdx.y;
+    const float m = __uint_as_float(fmax[f]);
+    const float* r = rgb + f * 3 * hw;
+    const float* vf = v_fixed + f * hw;
+    float* o = out + f * 3 * hw;
     const long long step = (long long)gridDim.x * blockDim.x, i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if ((per_frame & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0) {
-        float4* o4 = reinterpret_cast<float4*>(o);
-        for (long long i = i0; i < (per_frame >> 2); i += step) {
-            float4 v = o4[i];
-            v.x = __fdiv_rn(v.x, m), v.y = __fdiv_rn(v.y, m), v.z = __fdiv_rn(v.z, m), v.w = __fdiv_rn(v.w, m);
-            o4[i] = v;
+    if (vec) {
+        for (long long i = i0; i < (hw >> 2); i += step) {
+            const float4 r4 = reinterpret_cast<const float4*>(r)[i], g4 = reinterpret_cast<const float4*>(r + hw)[i],
+                         b4 = reinterpret_cast<const float4*>(r + 2 * hw)[i], v4 = reinterpret_cast<const float4*>(vf)[i];
+            float4 ro, go, bo;
+            recolor(r4.x, g4.x, b4.x, v4.x, ro.x, go.x, bo.x);
+            recolor(r4.y, g4.y, b4.y, v4.y, ro.y, go.y, bo.y);
+            recolor(r4.z, g4.z, b4.z, v4.z, ro.z, go.z, bo.z);
+            recolor(r4.w, g4.w, b4.w, v4.w, ro.w, go.w, bo.w);
+            ro.x = __fdiv_rn(ro.x, m), ro.y = __fdiv_rn(ro.y, m), ro.z = __fdiv_rn(ro.z, m), ro.w = __fdiv_rn(ro.w, m);
+            go.x = __fdiv_rn(go.x, m), go.y = __fdiv_rn(go.y, m), go.z = __fdiv_rn(go.z, m), go.w = __fdiv_rn(go.w, m);
+            bo.x = __fdiv_rn(bo.x, m), bo.y = __fdiv_rn(bo.y, m), bo.z = __fdiv_rn(bo.z, m), bo.w = __fdiv_rn(bo.w, m);
+            reinterpret_cast<float4*>(o)[i] = ro;
+            reinterpret_cast<float4*>(o + hw)[i] = go;
+            reinterpret_cast<float4*>(o + 2 * hw)[i] = bo;
         }
     } else {
-        for (long long i = i0; i < per_frame; i += step) o[i] = __fdiv_rn(o[i], m);
+        for (long long i = i0; i < hw; i += step) {
+            float ro, go, bo;
+            recolor(r[i], r[hw + i], r[2 * hw + i], vf[i], ro, go, bo);
+            o[i] = __fdiv_rn(ro, m), o[hw + i] = __fdiv_rn(go, m), o[2 * hw + i] = __fdiv_rn(bo, m);
+        }
     }
 }
 
@@ -207,11 +222,12 @@ extern "C" int b200_dcev_tail(const float* image_rgb, const float* image_v, cons
     const float sh = H > 1 ? (float)(S - 1) / (float)(H - 1) : 0.f;
     const float sw = W > 1 ? (float)(S - 1) / (float)(W - 1) : 0.f;
     dim3 grid((W + 255) / 256, (H + GF_ROWS - 1) / GF_ROWS, B);
-    dcev_gf_apply_kernel<<<grid, 256, 0, s>>>(image_rgb, image_v, A, Bc, image_v_fixed, enhanced, fmax, H, W, S, sh, sw);
-    const long long per = 3LL * H * W;
-    long long blocks = (per / 4 + 255) / 256;
-    if (blocks > B200_NUM_SMS * 2) blocks = B200_NUM_SMS * 2;
-    if (blocks < 1) blocks = 1;
-    dcev_normalise_kernel<<<dim3((unsigned)blocks, B), 256, 0, s>>>(enhanced, fmax, per);
+    dcev_gf_apply_kernel<<<grid, 256, 0, s>>>(image_v, A, Bc, image_v_fixed, fmax, H, W, S, sh, sw);
+    const long long hw = (long long)H * W;
+    const int vec = (hw & 3) == 0 && ((reinterpret_cast<uintptr_t>(image_rgb) | reinterpret_cast<uintptr_t>(image_v_fixed) |
+                                       reinterpret_cast<uintptr_t>(enhanced)) & 15u) == 0;
+    long long blocks = ((vec ? hw / 4 : hw) + 255) / 256;
+    if (blocks > B200_NUM_SMS * 4) blocks = B200_NUM_SMS * 4;
+    dcev_recolor_kernel<<<dim3((unsigned)blocks, B), 256, 0, s>>>(image_rgb, image_v_fixed, enhanced, fmax, hw, vec);
     return launch_status();
 }

@@ -43,5 +43,5 @@ t_core = timed(lambda: m.forward_core({"image": x}))
 t_tail = timed(lambda: torch.ops.b200dce.dcev_tail(x, core["image_v"], core["image_v_lr"], core["image_v_fixed_lr"]))
 t_all = timed(lambda: m({"image": x}))
 px = F * H * W
-print(f"{F} x {H} x {W}, S = {S}: core {t_core:.3f} ms, tail {t_tail:.3f} ms ({px * 44 / t_tail / 1e6:.0f} GB/s on 44 B/px: "
-      f"x 12, v 4, v_fixed 4, rgb 12 written + 12 read-modify-written), forward {t_all:.3f} ms = {px / t_all / 1e3:.0f} MP/s")
+print(f"{F} x {H} x {W}, S = {S}: core {t_core:.3f} ms, tail {t_tail:.3f} ms ({px * 36 / t_tail / 1e6:.0f} GB/s on 36 B/px: "
+      f"v 4 in, v_fixed 4 out | rgb 12 + v_fixed 4 in, enhanced 12 out), forward {t_all:.3f} ms = {px / t_all / 1e3:.0f} MP/s")

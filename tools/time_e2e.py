@@ -11,11 +11,11 @@ dev = torch.device("cuda:0")
 m = P.ZeroDCEpp_RE(scale_factor=12).to(dev)
 hin = torch.rand(F, 3, H, W).mul_(0.4).pin_memory()
 hout = torch.empty(F, 3, H, W).pin_memory()
-for wire in ("f32", "u8"):
+for wire in (sys.argv[1:] or ("f32", "u8")):
     if wire == "u8":
         hin8 = (hin.permute(0, 2, 3, 1) * 255).to(torch.uint8).contiguous().pin_memory()
         hout8 = torch.empty_like(hin8).pin_memory()
-    for chunk, slots in ((1, 2), (1, 3), (1, 4), (1, 6), (2, 2), (2, 3), (2, 4), (2, 6), (4, 2), (4, 3), (4, 4), (8, 2)):
+    for chunk, slots in ((1, 2), (1, 3), (1, 4), (1, 6), (2, 2), (2, 3), (2, 4), (2, 6), (4, 2), (4, 3), (4, 4), (4, 6), (4, 8), (2, 8), (8, 2), (8, 4)):
         pipe = P.FramePipeline(m, frames_per_chunk=chunk, H=H, W=W, wire=wire, slots=slots)
         a, b = (hin, hout) if wire == "f32" else (hin8, hout8)
         for _ in range(2):
