@@ -150,27 +150,41 @@ __global__ void __launch_bounds__(256) gce_curve_kernel(const float* __restrict_
         }
 #pragma unroll
         for (int k = 0; k < V; ++k) bam[k] = powf(__fsub_rn(1.f, fmaxf(fmaxf(e[0][k], e[1][k]), e[2][k])), gamma);
-        if (VEC) {  // two pixels per instruction on the packed fp32 pipe: the same roundings as gce_step
+        if (VEC) {  // two pixels per instruction on the packed fp32 pipe: the same roundings as gce_step; the six
+                    // (pixel pair, channel) chains advance together, one iteration at a time (a chain alone is five
+                    // dependent operations per iteration)
+            float2 ev[2][3], b2[2][3], d2[2][3], av[2][3], bm[2], omb[2];
 #pragma unroll
-            for (int k = 0; k < V; k += 2) {
-                const float2 bm = make_float2(bam[k], bam[k + 1]);
-                const float2 omb = make_float2(__fsub_rn(1.f, bm.x), __fsub_rn(1.f, bm.y));
+            for (int k = 0; k < 2; ++k) {
+                bm[k] = make_float2(bam[2 * k], bam[2 * k + 1]);
+                omb[k] = make_float2(__fsub_rn(1.f, bm[k].x), __fsub_rn(1.f, bm[k].y));
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    float2 ev = make_float2(e[c][k], e[c][k + 1]), b2 = make_float2(0.f, 0.f), d2 = b2;
-                    const float2 av = make_float2(a[c][k], a[c][k + 1]);
-                    for (int i = 0; i < iters; ++i) {
-                        b2 = __fmul2_rn(ev, omb);
-                        d2 = __fmul2_rn(ev, bm);
-                        // rn(d*d - d) as rn(rn(d*d) + (-1)*d): the FFMA2 by -1 rounds once
-                        const float2 q = __ffma2_rn(d2, make_float2(-1.f, -1.f), __fmul2_rn(d2, d2));
-                        ev = __fadd2_rn(__fadd2_rn(b2, d2), __fmul2_rn(av, q));
-                    }
-                    e[c][k] = ev.x, e[c][k + 1] = ev.y;
-                    br[c][k] = b2.x, br[c][k + 1] = b2.y;
-                    dk[c][k] = d2.x, dk[c][k + 1] = d2.y;
+                    ev[k][c] = make_float2(e[c][2 * k], e[c][2 * k + 1]);
+                    av[k][c] = make_float2(a[c][2 * k], a[c][2 * k + 1]);
+                    b2[k][c] = d2[k][c] = make_float2(0.f, 0.f);
                 }
             }
+            for (int i = 0; i < iters; ++i) {
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        b2[k][c] = __fmul2_rn(ev[k][c], omb[k]);
+                        d2[k][c] = __fmul2_rn(ev[k][c], bm[k]);
+                        // rn(d*d - d) as rn(rn(d*d) + (-1)*d): the FFMA2 by -1 rounds once
+                        const float2 q = __ffma2_rn(d2[k][c], make_float2(-1.f, -1.f), __fmul2_rn(d2[k][c], d2[k][c]));
+                        ev[k][c] = __fadd2_rn(__fadd2_rn(b2[k][c], d2[k][c]), __fmul2_rn(av[k][c], q));
+                    }
+            }
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    e[c][2 * k] = ev[k][c].x, e[c][2 * k + 1] = ev[k][c].y;
+                    br[c][2 * k] = b2[k][c].x, br[c][2 * k + 1] = b2[k][c].y;
+                    dk[c][2 * k] = d2[k][c].x, dk[c][2 * k + 1] = d2[k][c].y;
+                }
         } else {
             const float omb = __fsub_rn(1.f, bam[0]);
 #pragma unroll
