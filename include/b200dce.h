@@ -246,7 +246,8 @@ int b200_dcev_core(const float* image_rgb, const float* packed, float* image_v, 
  * sums are differences of fp32-rounded prefixes accumulated in double, repeated here exactly -- A = cov / (var + eps) is
  * ill-conditioned in flat windows), bicubic align_corners=True resize of A and b as ATen does it; the HSV conversions
  * are kornia's (src/mon/core/image/color.py:169-190,262-277 delegate to it) restated from their published form.
- * The reference runs with batch 1 only: a batch is B batch-1 calls (per-frame maximum).  S > 3. */
+ * The reference runs with batch 1 only: a batch is B batch-1 calls (per-frame maximum).  3 < S <= 4096
+ * (B200_ERR_UNSUPPORTED otherwise). */
 size_t b200_dcev_tail_workspace_bytes(int B, int S);
 int b200_dcev_tail(const float* image_rgb, const float* image_v, const float* image_v_lr, const float* image_v_fixed_lr,
                    float* image_v_fixed, float* enhanced, int B, int H, int W, int S, void* workspace,
