@@ -291,6 +291,29 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
                 "curve_ms": ms_c, "guided_filter_ms": ms_g, "curve_hbm_frac_36Bpx": px * 36 / (ms_c / 1e3) / 1e9 / hbm_peak,
                 "guided_filter_gbs_80B_per_plane_px": 3 * px * 80 / (ms_g / 1e3) / 1e9}
 
+    def c5_single():
+        import torch
+        m = P.ZeroDCEpp_RE(scale_factor=12).to(dev)
+        x = synth_frames_gpu(1, H, W, SEED + 7, dev)
+
+        def wall(fn, n=300):
+            for _ in range(20):
+                fn()
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            for _ in range(n):
+                fn()
+            torch.cuda.synchronize(dev)
+            return (time.perf_counter() - t0) / n * 1e6
+
+        eager = wall(lambda: m({"image": x}))
+        g = P.GraphedForward(m, x)
+        replay = wall(lambda: g())
+        same = torch.equal(g()["enhanced"], m({"image": x})["enhanced"])
+        return {"workload": "C5 one 1080p frame per call, zero_dce++ sf=12: wall clock per call, device kept busy",
+                "eager_us_per_call": eager, "graph_replay_us_per_call": replay, "frames_per_s_replay": 1e6 / replay,
+                "mp_s_replay": H * W / replay, "bit_identical": bool(same)}
+
     guarded("c3_dcepp_4k_b8", c3)
     guarded("c3_dcepp_4k_b8_no_adjust", c3_noadj)
     guarded("c4_sci_1080p_b16", c4)
@@ -301,6 +324,7 @@ def extras(P, O, dev, hbm_peak, tc_peak) -> dict:
     guarded("c2_dce_fp32_exact_1080p_b2", c2("fp32_exact", 2, 3))  # CUDA-core fp32 products
     guarded("c2_dce_bf16x3_mma_sync_1080p_b16", c2("bf16x3_mma", 16, 3))  # round-1 kernels, for the A/B
     guarded("c1_dcepp_sf1_512", sf1)
+    guarded("c5_dcepp_1080p_b1_per_call", c5_single)
     guarded("f3_dcev_1080p_b16", f3_dcev)
     guarded("f3_gcenet_post_1080p_b16", f3_gce)
     return out
