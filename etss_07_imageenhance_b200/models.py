@@ -206,7 +206,8 @@ class _EnhancementModel(nn.Module):
 
     # ---- packed-weight cache: rebuilt when any parameter's storage / version / device changes
     def _params_key(self, tensors) -> tuple:
-        return tuple((t.data_ptr(), t._version, str(t.device)) for t in tensors)
+        # (a move to another device changes the pointer too: str(t.device) per tensor cost 10 us per call here)
+        return tuple([t.data_ptr() for t in tensors] + [t._version for t in tensors])
 
     def _image(self, datapoint: dict) -> torch.Tensor:
         self.assert_datapoint(datapoint)
@@ -221,6 +222,9 @@ class _EnhancementModel(nn.Module):
         if torch.is_grad_enabled() and x.requires_grad:
             raise NotImplementedError("the B200 drop-in is inference-only; call under torch.no_grad()")
         return x
+
+
+_E_CONVS = tuple(f"e_conv{i}" for i in range(1, 8))
 
 
 def _init_conv_weights(module: nn.Module) -> None:
@@ -277,8 +281,8 @@ class ZeroDCE_RE(_EnhancementModel):
 
     def packed_weights(self) -> torch.Tensor:
         prec = PRECISIONS[self.precision]
-        ws = [c.weight for c in self._convs()]
-        bs = [c.bias for c in self._convs()]
+        ps = [self._modules[n]._parameters for n in _E_CONVS]   # dictionary reads instead of nn.Module.__getattr__
+        ws, bs = [d["weight"] for d in ps], [d["bias"] for d in ps]
         key = (prec, self.num_iters) + self._params_key(ws + bs)
         if self._packed is None or self._packed_key != key:
             self._packed = torch.ops.b200dce.dce_pack([w.detach() for w in ws], [b.detach() for b in bs],
@@ -348,8 +352,8 @@ class ZeroDCEV(_EnhancementModel):
             _init_conv_weights(self)
 
     def packed_weights(self) -> torch.Tensor:
-        convs = [getattr(self, f"e_conv{i}") for i in range(1, 8)]
-        ws, bs = [c.weight for c in convs], [c.bias for c in convs]
+        ps = [self._modules[n]._parameters for n in _E_CONVS]   # dictionary reads instead of nn.Module.__getattr__
+        ws, bs = [d["weight"] for d in ps], [d["bias"] for d in ps]
         key = (self.num_iters,) + self._params_key(ws + bs)
         if self._packed is None or self._packed_key != key:
             self._packed = torch.ops.b200dce.dcev_pack([w.detach() for w in ws], [b.detach() for b in bs],
@@ -430,9 +434,11 @@ class ZeroDCEpp_RE(_EnhancementModel):
         return int(sf)
 
     def packed_weights(self) -> torch.Tensor:
-        L = self._layers()
-        ts = [m.dw_conv.weight for m in L] + [m.dw_conv.bias for m in L] + \
-             [m.pw_conv.weight for m in L] + [m.pw_conv.bias for m in L]
+        # straight dictionary reads: nn.Module.__getattr__ on 7 x 2 submodules x 2 parameters cost ~10 us per call
+        mods = self._modules
+        dw = [mods[n]._modules["dw_conv"]._parameters for n in _E_CONVS]
+        pw = [mods[n]._modules["pw_conv"]._parameters for n in _E_CONVS]
+        ts = [d["weight"] for d in dw] + [d["bias"] for d in dw] + [d["weight"] for d in pw] + [d["bias"] for d in pw]
         key = self._params_key(ts)
         if self._packed is None or self._packed_key != key:
             d = [t.detach() for t in ts]

@@ -362,8 +362,8 @@ class GraphedForward:
     """`model(datapoint)` for one fixed input shape, captured once into a CUDA graph and replayed.
 
     For a loop that enhances one frame (or a small batch) at a time the forward is a few tens of microseconds of GPU
-    work behind ~100 us of Python / dispatcher time per call (`tools/time_graph.py`: one 1080p Zero-DCE++ frame, eager
-    98 us per call, replay 58 us).  The C layer never allocates, frees or synchronises and launches only on the
+    work behind 60-70 us of Python / dispatcher time per call (`tools/time_graph.py`: one 1080p Zero-DCE++ frame, eager
+    73 us per call, replay 59 us).  The C layer never allocates, frees or synchronises and launches only on the
     caller's stream, so the whole call captures; replays reuse the captured buffers:
 
         g = GraphedForward(model, torch.empty(1, 3, 1080, 1920, device="cuda"))
